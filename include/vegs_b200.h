@@ -1,0 +1,199 @@
+/*
+ * vegs_b200.h — C ABI of libvegs_b200.so: the B200 (sm_100a) Gaussian-splatting hot path of VEGS.
+ *
+ * Plain C: pointers and sizes only, no torch / C++ types.  Every pointer is a DEVICE pointer owned
+ * by the caller unless its name ends in `_host` (then it is a host pointer; pinned memory if the
+ * copy is to be asynchronous).  Nullable pointers mean "not provided", exactly as the reference
+ * binding does for shs / colors_precomp / scales / rotations / cov3D_precomp
+ * (reference: submodules/diff_gaussian_rasterization/rasterize_points.cu:36-134 and
+ * diff_gaussian_rasterization/__init__.py:221-231).
+ *
+ * Every function returns 0 on success and a non-zero VEGS_E* code on failure; nothing throws or
+ * aborts across the ABI.  vegs_last_error() returns a thread-local message for the last failure.
+ * The library never allocates device memory: all state and scratch buffers are passed in, sized by
+ * the *_bytes() queries below.  `stream` is a cudaStream_t passed as void*.
+ *
+ * All paths cited below are relative to the reference tree (deepshwang/vegs).
+ */
+#ifndef VEGS_B200_H_INCLUDED
+#define VEGS_B200_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VEGS_ABI_VERSION 1
+
+enum {
+    VEGS_OK = 0,
+    VEGS_EINVAL = 1,   /* bad argument (null pointer, bad size, inconsistent options) */
+    VEGS_ECUDA = 2,    /* a CUDA call or kernel failed; see vegs_last_error() */
+    VEGS_ESIZE = 3     /* a caller-provided buffer is too small */
+};
+
+/* Tile size of the rasterizer: 16x16 pixels (reference cuda_rasterizer/config.h:15-17). */
+#define VEGS_TILE 16
+
+/*
+ * Forward arguments.  Replaces the 19 positional arguments of `_C.rasterize_gaussians`
+ * (rasterize_points.h:17-38, rasterize_points.cu:36-134) and the three growable byte tensors
+ * geomBuffer / binningBuffer / imgBuffer (rasterize_points.cu:80-85).
+ */
+typedef struct VegsForwardArgs {
+    /* sizes */
+    int32_t P;            /* number of Gaussians */
+    int32_t D;            /* active SH degree (0..3) */
+    int32_t M;            /* SH coefficients stored per Gaussian (sh.size(1)); 0 if shs == NULL */
+    int32_t W, H;         /* image size in pixels */
+    /* inputs */
+    const float* background;     /* [3] */
+    const float* means3D;        /* [P,3] */
+    const float* shs;            /* [P,M,3] or NULL */
+    const float* colors_precomp; /* [P,3] or NULL */
+    const float* opacities;      /* [P] */
+    const float* scales;         /* [P,3] or NULL */
+    const float* rotations;      /* [P,4] (r,x,y,z) or NULL */
+    const float* cov3D_precomp;  /* [P,6] or NULL */
+    const float* viewmatrix;     /* [16], transposed storage (scene/cameras.py:76) */
+    const float* projmatrix;     /* [16], transposed storage, full view*proj */
+    const float* campos;         /* [3] */
+    float scale_modifier;
+    float tan_fovx, tan_fovy;
+    int32_t prefiltered;
+    int32_t debug;               /* non-zero: synchronise and check after every stage */
+    /* outputs (rasterize_points.cu:69-76); every element is written by the kernels */
+    float* out_color;     /* [3,H,W] */
+    float* out_depth;     /* [1,H,W] */
+    float* out_cov_quat;  /* [4,H,W] planes (w,x,y,z) */
+    float* out_cov_scale; /* [3,H,W] */
+    float* out_alpha;     /* [1,H,W] */
+    int32_t* radii;       /* [P] */
+    /* state kept for the backward pass (caller keeps these alive, as ctx.save_for_backward does) */
+    void* geom;           /* vegs_geom_bytes(P) */
+    void* img;            /* vegs_img_bytes(W,H) */
+    void* binning;        /* vegs_binning_bytes(R); only needed by vegs_forward_render */
+    /* scratch, free to release when the forward returns */
+    void* scratch;        /* vegs_scratch_bytes(P) */
+    void* bin_scratch;    /* vegs_bin_scratch_bytes(R,W,H); only needed by vegs_forward_render */
+    /* host word that receives num_rendered (asynchronously on `stream`; pinned memory) */
+    int32_t* num_rendered_host;
+} VegsForwardArgs;
+
+/*
+ * Backward arguments.  Replaces the 28 positional arguments of `_C.rasterize_gaussians_backward`
+ * (rasterize_points.h:40-71, rasterize_points.cu:136-240).  dL_dout_cov_quat / dL_dout_cov_scale
+ * are accepted and ignored: in the reference their contribution is overwritten before it is
+ * returned (cuda_rasterizer/backward.cu:624-647 vs :322-325,:340-341).
+ */
+typedef struct VegsBackwardArgs {
+    int32_t P, D, M, W, H;
+    int32_t R;                    /* num_rendered of the matching forward */
+    const float* background;
+    const float* means3D;
+    const float* shs;
+    const float* colors_precomp;
+    const float* scales;
+    const float* rotations;
+    const float* cov3D_precomp;
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* campos;
+    float scale_modifier;
+    float tan_fovx, tan_fovy;
+    int32_t debug;
+    const int32_t* radii;         /* [P] from the forward */
+    const float* out_alpha;       /* [1,H,W] from the forward */
+    /* cotangents of the five image outputs; NULL means zero */
+    const float* dL_dout_color;     /* [3,H,W] */
+    const float* dL_dout_depth;     /* [1,H,W] */
+    const float* dL_dout_cov_quat;  /* [4,H,W]  (ignored, see above) */
+    const float* dL_dout_cov_scale; /* [3,H,W]  (ignored, see above) */
+    const float* dL_dout_alpha;     /* [1,H,W] */
+    /* state from the forward */
+    const void* geom;
+    const void* img;
+    const void* binning;
+    /* scratch: packed per-Gaussian blend-stage accumulators, vegs_bwd_scratch_bytes(P) */
+    void* bwd_scratch;
+    /* outputs; every element is written (zeros for Gaussians with radii == 0); any may be NULL */
+    float* dL_dmeans3D;       /* [P,3] */
+    float* dL_dmeans2D;       /* [P,3]  (x,y scaled by 0.5*W, 0.5*H; z = 0) */
+    float* dL_dsh;            /* [P,M,3] */
+    float* dL_dcolors;        /* [P,3]  gradient w.r.t. the per-Gaussian RGB (colors_precomp) */
+    float* dL_dopacity;       /* [P] */
+    float* dL_dscales;        /* [P,3] */
+    float* dL_drotations;     /* [P,4] */
+    float* dL_dcov3D;         /* [P,6] */
+} VegsBackwardArgs;
+
+/* Library / ABI identification. */
+int vegs_abi_version(void);
+const char* vegs_last_error(void);
+
+/* Buffer sizes (bytes).  R = num_rendered. */
+size_t vegs_geom_bytes(int32_t P);
+size_t vegs_scratch_bytes(int32_t P);
+size_t vegs_img_bytes(int32_t W, int32_t H);
+size_t vegs_binning_bytes(int64_t R);
+size_t vegs_bin_scratch_bytes(int64_t R, int32_t W, int32_t H);
+size_t vegs_bwd_scratch_bytes(int32_t P);
+
+/*
+ * Forward, stage 1: per-Gaussian preprocess, depth sort, tile-count scan.
+ * Replaces FORWARD::preprocess + InclusiveSum + the num_rendered read-back
+ * (cuda_rasterizer/rasterizer_impl.cu:253-286).  Enqueues an asynchronous copy of num_rendered
+ * into args->num_rendered_host; the caller synchronises `stream`, reads it, allocates
+ * binning / bin_scratch, and calls vegs_forward_render.
+ */
+int vegs_forward_prepare(const VegsForwardArgs* args, void* stream);
+
+/*
+ * Forward, stage 2: tile-instance emission, tile sort, tile ranges, front-to-back compositing.
+ * Replaces duplicateWithKeys + SortPairs + identifyTileRanges + FORWARD::render
+ * (cuda_rasterizer/rasterizer_impl.cu:288-350).
+ */
+int vegs_forward_render(const VegsForwardArgs* args, int32_t num_rendered, void* stream);
+
+/*
+ * Backward: blend-stage gradients (warp-reduced atomics) then the per-Gaussian stage.
+ * Replaces CudaRasterizer::Rasterizer::backward (cuda_rasterizer/rasterizer_impl.cu:356-481).
+ */
+int vegs_backward(const VegsBackwardArgs* args, void* stream);
+
+/*
+ * markVisible: present[i] = (view * p_i).z > 0.2.  Replaces `_C.mark_visible`
+ * (rasterize_points.cu:242-261, cuda_rasterizer/rasterizer_impl.cu:54-66,141-153).
+ */
+int vegs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
+                      const float* projmatrix, uint8_t* present, void* stream);
+
+/*
+ * distCUDA2: out[i] = mean of the three smallest squared distances from point i to other points.
+ * Replaces `simple_knn._C.distCUDA2` (submodules/simple-knn/spatial.cu:15-26,
+ * simple_knn.cu:185-221).  `workspace` must hold vegs_dist2_workspace_bytes(P) bytes.
+ */
+size_t vegs_dist2_workspace_bytes(int32_t P);
+int vegs_dist2(int32_t P, const float* points, float* out, void* workspace, size_t workspace_bytes,
+               void* stream);
+
+/*
+ * Test / parity support: re-express the binning state in the reference's format
+ * (cuda_rasterizer/rasterizer_impl.cu:70-111,116-138): point_list_keys[R] = (tile << 32) | depth
+ * bits, point_list[R], ranges[T] (uint2), tiles_touched[P], depths[P], means2D[P,2].  Any output
+ * pointer may be NULL.  Not on the hot path.
+ */
+int vegs_export_state(const VegsForwardArgs* args, int32_t num_rendered, uint64_t* point_list_keys,
+                      uint32_t* point_list, uint32_t* ranges, uint32_t* tiles_touched,
+                      float* depths, float* means2D, float* conic_opacity, float* rgb,
+                      uint32_t* n_contrib, void* stream);
+
+/* Number of kernels launched by this library in this process so far (bench bookkeeping). */
+uint64_t vegs_kernel_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VEGS_B200_H_INCLUDED */

@@ -1,0 +1,247 @@
+"""Shared helpers for the parity tests: run the same seeded inputs through
+  * ours      — vegs_b200 (CUDA, through the C ABI via the drop-in Python modules)
+  * oracle    — oracle/ (CPU restatement of the reference algorithm)
+  * reference — the reference's own CUDA extension from baseline/_ref, when it is importable
+and compare.  Nothing here reads /root/reference.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+REF_DIR = os.path.join(ROOT, "baseline", "_ref")
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+
+
+def special_gaussians():
+    """Hand-made Gaussians appended to seeded scenes to hit the reference's edge cases
+    (SURVEY.md §8c): near-plane straddlers, far off-screen (empty tile rectangle), exact depth
+    ties inside a tile (duplicates), and an opaque stack that saturates a pixel (T < 1e-4)."""
+    rows = []
+    unit_q = [1.0, 0.0, 0.0, 0.0]
+    def add(xyz, scale=(0.05, 0.05, 0.05), q=unit_q, op=0.9):
+        rows.append((xyz, scale, q, op))
+    # camera 0 sits at (10, 0, 1.55) looking +x
+    add((10.19, 0.0, 1.55)); add((10.21, 0.05, 1.50)); add((10.2, 0.0, 1.55))
+    add((9.0, 0.0, 1.55))                                   # behind the camera
+    add((30.0, 200.0, 1.0)); add((30.0, -200.0, 1.0))       # far outside the image: empty rect
+    for _ in range(6):
+        add((25.0, 1.0, 1.2), scale=(0.2, 0.2, 0.2), op=0.8)  # exact duplicates: depth ties
+    for k in range(12):
+        add((18.0 + 0.01 * k, -1.0, 1.4), scale=(0.3, 0.3, 0.3), op=0.99)  # saturating stack
+    add((40.0, 0.0, 1.55), scale=(3.0, 3.0, 3.0), op=0.5)   # very large splat: many tiles
+    add((22.0, 0.5, 1.0), scale=(1e-5, 0.1, 0.1), q=[0.9999999, 0.0, 0.0003, 0.0])  # near-identity quat: lerp branch
+    add((22.0, 0.8, 1.0), scale=(0.1, 0.1, 0.1), q=[0.5, 0.5, 0.5, 0.5])
+    n = len(rows)
+    means = torch.tensor([r[0] for r in rows], dtype=torch.float32)
+    scales = torch.tensor([r[1] for r in rows], dtype=torch.float32)
+    rots = torch.tensor([r[2] for r in rows], dtype=torch.float32)
+    rots = rots / rots.norm(dim=1, keepdim=True)
+    opac = torch.tensor([[r[3]] for r in rows], dtype=torch.float32)
+    g = torch.Generator().manual_seed(3)
+    shs = torch.randn(n, 16, 3, generator=g) * 0.05
+    shs[:, 0, :] = (torch.rand(n, 3, generator=g) - 0.5) / 0.28209479177387814
+    return dict(means3D=means, scales=scales, rotations=rots, opacities=opac, shs=shs)
+
+
+def scene_with_specials(P: int, seed: int = 7):
+    from vegs_b200 import synth
+    sc = synth.make_scene(P, seed=seed)
+    sp = special_gaussians()
+    return {k: torch.cat([sc[k], sp[k]], 0).contiguous() for k in sc}
+
+
+def np_cotangents(W, H, seed=11):
+    """numpy RandomState is stable across versions, so cotangents need not be stored."""
+    rs = np.random.RandomState(seed)
+    return dict(color=rs.standard_normal((3, H, W)).astype(np.float32),
+                depth=rs.standard_normal((1, H, W)).astype(np.float32),
+                cov_quat=rs.standard_normal((4, H, W)).astype(np.float32),
+                cov_scale=rs.standard_normal((3, H, W)).astype(np.float32),
+                alpha=rs.standard_normal((1, H, W)).astype(np.float32))
+
+
+# ------------------------------------------------------------------------------------ ours
+def run_ours(scene, cam, *, sh_degree=3, bg=(0.0, 0.0, 0.0), scale_modifier=1.0, mode="sh",
+             cot=None, device="cuda", want_state=True):
+    """Forward (+ backward when `cot` is given) through vegs_b200 on the GPU.
+    mode: "sh" | "colors" (colors_precomp) | "cov3d" (cov3D_precomp)."""
+    import vegs_b200.diff_gaussian_rasterization as dgr
+    dev = torch.device(device)
+    t = {k: v.to(dev).clone().requires_grad_(True) for k, v in scene.items()}
+    bg_t = torch.tensor(bg, dtype=torch.float32, device=dev)
+    rs = dgr.GaussianRasterizationSettings(
+        image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=bg_t,
+        scale_modifier=scale_modifier, viewmatrix=cam.viewmatrix.to(dev),
+        projmatrix=cam.projmatrix.to(dev), sh_degree=sh_degree, campos=cam.campos.to(dev),
+        prefiltered=False, debug=False)
+    out = {}
+    if want_state:
+        empty = torch.Tensor([])
+        sh = t["shs"] if mode != "colors" else empty
+        colors = t["colors"] if mode == "colors" else empty
+        scales = t["scales"] if mode != "cov3d" else empty
+        rots = t["rotations"] if mode != "cov3d" else empty
+        cov = t["cov3D"] if mode == "cov3d" else empty
+        with torch.no_grad():
+            res = dgr._forward_impl(bg_t, t["means3D"], colors, t["opacities"], scales, rots,
+                                    scale_modifier, cov, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
+                                    rs.tanfovy, cam.H, cam.W, sh, sh_degree, rs.campos, False,
+                                    False, keep_scratch=True)
+        st = res[6]
+        out["state"] = {k: (v.cpu().numpy() if torch.is_tensor(v) else v)
+                        for k, v in dgr.export_state(st, res[5]).items()}
+    rast = dgr.GaussianRasterizer(rs)
+    means2D = torch.zeros_like(t["means3D"], requires_grad=True)
+    kw = dict(means3D=t["means3D"], means2D=means2D, opacities=t["opacities"])
+    if mode == "colors":
+        kw["colors_precomp"] = t["colors"]
+    else:
+        kw["shs"] = t["shs"]
+    if mode == "cov3d":
+        kw["cov3D_precomp"] = t["cov3D"]
+    else:
+        kw["scales"] = t["scales"]; kw["rotations"] = t["rotations"]
+    color, depth, quat, scale, alpha, radii = rast(**kw)
+    out.update(color=color.detach().cpu().numpy(), depth=depth.detach().cpu().numpy(),
+               cov_quat=quat.detach().cpu().numpy(), cov_scale=scale.detach().cpu().numpy(),
+               alpha=alpha.detach().cpu().numpy(), radii=radii.cpu().numpy())
+    if cot is not None:
+        c = {k: torch.as_tensor(v).to(dev) for k, v in cot.items()}
+        loss = ((color * c["color"]).sum() + (depth * c["depth"]).sum() + (quat * c["cov_quat"]).sum()
+                + (scale * c["cov_scale"]).sum() + (alpha * c["alpha"]).sum())
+        loss.backward()
+        g = dict(means3D=t["means3D"].grad, means2D=means2D.grad, opacities=t["opacities"].grad)
+        if mode == "colors":
+            g["colors_precomp"] = t["colors"].grad
+        else:
+            g["sh"] = t["shs"].grad
+        if mode == "cov3d":
+            g["cov3D"] = t["cov3D"].grad
+        else:
+            g["scales"] = t["scales"].grad; g["rotations"] = t["rotations"].grad
+        out["grads"] = {k: v.detach().cpu().numpy() for k, v in g.items()}
+    return out
+
+
+# ---------------------------------------------------------------------------------- oracle
+def run_oracle(scene, cam, *, sh_degree=3, bg=(0.0, 0.0, 0.0), scale_modifier=1.0, mode="sh",
+               cot=None):
+    from oracle import oracle
+    kw = dict(means3D=scene["means3D"], opacities=scene["opacities"], viewmatrix=cam.viewmatrix,
+              projmatrix=cam.projmatrix, campos=cam.campos, bg=np.asarray(bg, np.float32), W=cam.W,
+              H=cam.H, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, sh_degree=sh_degree,
+              scale_modifier=scale_modifier)
+    if mode == "colors":
+        kw["colors_precomp"] = scene["colors"]
+    else:
+        kw["shs"] = scene["shs"]
+    if mode == "cov3d":
+        kw["cov3D_precomp"] = scene["cov3D"]
+    else:
+        kw["scales"] = scene["scales"]; kw["rotations"] = scene["rotations"]
+    f = oracle.forward(**kw)
+    if cot is not None:
+        f["grads"] = oracle.backward(f, grad_color=cot["color"], grad_depth=cot["depth"],
+                                     grad_alpha=cot["alpha"])
+    return f
+
+
+# ------------------------------------------------------------------------------- reference
+def reference_available() -> bool:
+    return os.path.isdir(os.path.join(REF_DIR, "diff_gaussian_rasterization"))
+
+
+def import_reference():
+    """Import the reference's own extension modules from baseline/_ref under private names so
+    they cannot shadow (or be shadowed by) vegs_b200's drop-in modules."""
+    import importlib.util
+    mods = {}
+    for name, sub in (("diff_gaussian_rasterization", "__init__.py"),):
+        path = os.path.join(REF_DIR, name, sub)
+        spec = importlib.util.spec_from_file_location(
+            "_ref_" + name, path, submodule_search_locations=[os.path.join(REF_DIR, name)])
+        m = importlib.util.module_from_spec(spec)
+        sys.modules["_ref_" + name] = m
+        spec.loader.exec_module(m)
+        mods[name] = m
+    import glob
+    so = glob.glob(os.path.join(REF_DIR, "simple_knn", "_C*.so"))
+    if so:
+        # the extension's init symbol is PyInit__C, so the module must be named _C
+        spec = importlib.util.spec_from_file_location("_C", so[0])
+        m = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(m)
+        mods["simple_knn_C"] = m
+    return mods
+
+
+def run_reference(scene, cam, *, sh_degree=3, bg=(0.0, 0.0, 0.0), scale_modifier=1.0, mode="sh",
+                  cot=None, device="cuda"):
+    """The reference's CUDA rasterizer on the same inputs, with its opaque buffers decoded."""
+    import refdecode
+    ref = import_reference()["diff_gaussian_rasterization"]
+    dev = torch.device(device)
+    t = {k: v.to(dev).clone().requires_grad_(True) for k, v in scene.items()}
+    bg_t = torch.tensor(bg, dtype=torch.float32, device=dev)
+    view, proj, campos = cam.viewmatrix.to(dev), cam.projmatrix.to(dev), cam.campos.to(dev)
+    empty = torch.Tensor([])
+    sh = t["shs"] if mode != "colors" else empty
+    colors = t["colors"] if mode == "colors" else empty
+    scales = t["scales"] if mode != "cov3d" else empty
+    rots = t["rotations"] if mode != "cov3d" else empty
+    cov = t["cov3D"] if mode == "cov3d" else empty
+    P = t["means3D"].shape[0]
+    with torch.no_grad():
+        res = ref._C.rasterize_gaussians(bg_t, t["means3D"], colors, t["opacities"], scales, rots,
+                                         scale_modifier, cov, view, proj, cam.tanfovx, cam.tanfovy,
+                                         cam.H, cam.W, sh, sh_degree, campos, False, False)
+    R, color, depth, quat, scale, alpha, radii, geomB, binB, imgB = res
+    torch.cuda.synchronize()
+    out = dict(num_rendered=int(R), color=color.cpu().numpy(), depth=depth.cpu().numpy(),
+               cov_quat=quat.cpu().numpy(), cov_scale=scale.cpu().numpy(), alpha=alpha.cpu().numpy(),
+               radii=radii.cpu().numpy())
+    out.update(refdecode.decode_geom(geomB, P))
+    out.update(refdecode.decode_binning(binB, int(R)))
+    out.update(refdecode.decode_img(imgB, cam.W, cam.H))
+    if cot is not None:
+        c = {k: torch.as_tensor(v).to(dev) for k, v in cot.items()}
+        with torch.no_grad():
+            g = ref._C.rasterize_gaussians_backward(
+                bg_t, t["means3D"], quat, scale, radii, colors, scales, rots, scale_modifier, cov,
+                view, proj, cam.tanfovx, cam.tanfovy, c["color"], c["depth"], c["cov_quat"],
+                c["cov_scale"], c["alpha"], sh, sh_degree, campos, geomB, int(R), binB, imgB, alpha,
+                False)
+        torch.cuda.synchronize()
+        names = ["means2D", "colors_precomp", "opacities", "means3D", "cov3D", "sh", "scales", "rotations"]
+        out["grads"] = {n: x.cpu().numpy() for n, x in zip(names, g)}
+    return out
+
+
+# ------------------------------------------------------------------------------ comparisons
+def assert_bit_equal(a, b, what):
+    a = np.ascontiguousarray(a); b = np.ascontiguousarray(b)
+    assert a.shape == b.shape, f"{what}: shape {a.shape} vs {b.shape}"
+    if a.dtype.kind == "f":
+        a = a.view(np.uint32 if a.itemsize == 4 else np.uint64)
+        b = b.view(np.uint32 if b.itemsize == 4 else np.uint64)
+    bad = np.flatnonzero(a.reshape(-1) != b.reshape(-1))
+    assert bad.size == 0, f"{what}: {bad.size} of {a.size} elements differ (first at {bad[:5]})"
+
+
+def grad_close(g, g_ref, what, rtol=1e-4):
+    """‖g − g_ref‖∞ ≤ rtol · ‖g_ref‖∞ per tensor (SURVEY.md §8c parity contract)."""
+    g = np.asarray(g, np.float64).reshape(-1); g_ref = np.asarray(g_ref, np.float64).reshape(-1)
+    assert g.shape == g_ref.shape, f"{what}: shape"
+    assert np.isfinite(g).all(), f"{what}: non-finite values"
+    scale = max(np.abs(g_ref).max(), 1e-20)
+    err = np.abs(g - g_ref).max() / scale
+    assert err <= rtol, f"{what}: max-norm relative error {err:.3e} > {rtol}"
+    return err

@@ -1,0 +1,284 @@
+// distCUDA2: mean of the three smallest squared distances from every point to the other points.
+//
+// Replaces SimpleKNN::knn (reference submodules/simple-knn/simple_knn.cu:45-221, spatial.cu:15-26).
+//
+// The result is the exact 3-NN answer, so any exact search gives the reference's values; what is
+// pinned is the float arithmetic of a distance, d = fma(dz,dz, fma(dx,dx, dy*dy)) with
+// d* = other - self (SASS of the reference's boxMeanDist), and the final (b0 + b1 + b2) / 3.0f on
+// the ascending triple.
+//
+// Search structure (built per call, no host synchronisation, no allocation):
+//   1. bounding box by atomic min/max on order-preserving integer images of the floats
+//   2. 30-bit Morton codes, radix sort (sort.cu), points gathered into sorted order
+//   3. three levels of AABBs over runs of 32 / 1024 / 32768 consecutive sorted points
+//   4. one thread per point (in sorted order, so a warp's 32 queries are neighbours and traverse
+//      the same boxes): seed the bound with the +-3 sorted neighbours as the reference does, then
+//      descend L3 -> L2 -> L1 -> points, pruning a box when its distance exceeds the current third
+//      best.  The box distance uses the same fma order on component-wise smaller magnitudes, so it
+//      never exceeds the computed distance of a point inside the box: pruning is exact in float.
+// The reference tests every one of the P/1024 boxes from every thread (3.5e10 tests at 6 M points).
+// Roofline: latency / L2-gather bound; algorithmic HBM bytes 16 per point.
+#include <algorithm>
+#include <cfloat>
+#include "common.cuh"
+
+namespace vegs {
+
+namespace {
+
+constexpr int kFan = 32;
+
+struct KnnView {
+    uint32_t* bbox;  // 6 ordered-uint words: min xyz, max xyz
+    uint32_t *codes0, *codes1, *idx0, *idx1;
+    uint32_t *hist, *rowtot;
+    float4* pts;   // sorted points (x, y, z, original index bits)
+    float4* box1;  // 2 float4 per box: min, max
+    float4* box2;
+    float4* box3;
+    size_t bytes;
+};
+
+KnnView knn_view(void* base, int P) {
+    KnnView v;
+    char* cur = reinterpret_cast<char*>(base);
+    const size_t n = (size_t)(P > 0 ? P : 1);
+    const size_t n1 = div_up(n, kFan), n2 = div_up(n1, kFan), n3 = div_up(n2, kFan);
+    v.bbox = carve<uint32_t>(cur, 8);
+    v.codes0 = carve<uint32_t>(cur, n);
+    v.codes1 = carve<uint32_t>(cur, n);
+    v.idx0 = carve<uint32_t>(cur, n);
+    v.idx1 = carve<uint32_t>(cur, n);
+    v.hist = carve<uint32_t>(cur, (size_t)kRadix * div_up(n, kSortTile));
+    v.rowtot = carve<uint32_t>(cur, kRadix);
+    v.pts = carve<float4>(cur, n);
+    v.box1 = carve<float4>(cur, 2 * n1);
+    v.box2 = carve<float4>(cur, 2 * n2);
+    v.box3 = carve<float4>(cur, 2 * n3);
+    v.bytes = (size_t)(cur - reinterpret_cast<char*>(base));
+    return v;
+}
+
+__device__ __forceinline__ uint32_t f2ord(float f) {
+    const uint32_t b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(uint32_t u) {
+    return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+
+__global__ void bbox_init_kernel(uint32_t* bbox) {
+    if (threadIdx.x < 3) bbox[threadIdx.x] = 0xffffffffu;
+    else if (threadIdx.x < 6) bbox[threadIdx.x] = 0u;
+}
+
+__global__ void __launch_bounds__(256) bbox_kernel(int P, const float* __restrict__ pts,
+                                                   uint32_t* __restrict__ bbox) {
+    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < P; i += gridDim.x * 256) {
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            const float v = pts[3 * (size_t)i + k];
+            mn[k] = fminf(mn[k], v);
+            mx[k] = fmaxf(mx[k], v);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[k] = fminf(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+            mx[k] = fmaxf(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            atomicMin(&bbox[k], f2ord(mn[k]));
+            atomicMax(&bbox[3 + k], f2ord(mx[k]));
+        }
+    }
+}
+
+__device__ __forceinline__ uint32_t spread10(uint32_t x) {
+    x = (x | (x << 16)) & 0x030000FFu;
+    x = (x | (x << 8)) & 0x0300F00Fu;
+    x = (x | (x << 4)) & 0x030C30C3u;
+    x = (x | (x << 2)) & 0x09249249u;
+    return x;
+}
+
+__global__ void __launch_bounds__(256) morton_kernel(int P, const float* __restrict__ pts,
+                                                     const uint32_t* __restrict__ bbox,
+                                                     uint32_t* __restrict__ codes) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= P) return;
+    uint32_t q[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const float lo = ord2f(bbox[k]), hi = ord2f(bbox[3 + k]);
+        const float ext = hi - lo;
+        float t = ext > 0.f ? (pts[3 * (size_t)i + k] - lo) / ext : 0.f;
+        t = fminf(fmaxf(t, 0.f), 1.f);
+        q[k] = (uint32_t)(t * 1023.0f);
+    }
+    codes[i] = spread10(q[0]) | (spread10(q[1]) << 1) | (spread10(q[2]) << 2);
+}
+
+__global__ void __launch_bounds__(256) gather_points_kernel(int P, const float* __restrict__ pts,
+                                                            const uint32_t* __restrict__ order,
+                                                            float4* __restrict__ sorted) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= P) return;
+    const uint32_t g = order[i];
+    sorted[i] = make_float4(pts[3 * (size_t)g], pts[3 * (size_t)g + 1], pts[3 * (size_t)g + 2],
+                            __uint_as_float(g));
+}
+
+// One warp per output box: AABB of up to 32 children (points when kLeaf, else child boxes).
+template <bool kLeaf>
+__global__ void __launch_bounds__(256) build_boxes_kernel(uint32_t n_in, const float4* __restrict__ in,
+                                                          uint32_t n_out, float4* __restrict__ out) {
+    const uint32_t w = (blockIdx.x * 256u + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (w >= n_out) return;
+    const uint32_t c = w * kFan + lane;
+    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    if (c < n_in) {
+        if (kLeaf) {
+            const float4 p = in[c];
+            mn[0] = mx[0] = p.x; mn[1] = mx[1] = p.y; mn[2] = mx[2] = p.z;
+        } else {
+            const float4 a = in[2 * (size_t)c], b = in[2 * (size_t)c + 1];
+            mn[0] = a.x; mn[1] = a.y; mn[2] = a.z;
+            mx[0] = b.x; mx[1] = b.y; mx[2] = b.z;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[k] = fminf(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+            mx[k] = fmaxf(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+        }
+    }
+    if (lane == 0) {
+        out[2 * (size_t)w] = make_float4(mn[0], mn[1], mn[2], 0.f);
+        out[2 * (size_t)w + 1] = make_float4(mx[0], mx[1], mx[2], 0.f);
+    }
+}
+
+__device__ __forceinline__ float point_dist2(const float4& self, const float4& other) {
+    const float dx = __fsub_rn(other.x, self.x);
+    const float dy = __fsub_rn(other.y, self.y);
+    const float dz = __fsub_rn(other.z, self.z);
+    return __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+}
+
+// Lower bound (in the same float arithmetic) of point_dist2 to any point inside the box.
+__device__ __forceinline__ float box_dist2(const float4& p, const float4& mn, const float4& mx) {
+    float dx = 0.f, dy = 0.f, dz = 0.f;
+    if (p.x < mn.x || p.x > mx.x) dx = fminf(fabsf(__fsub_rn(mn.x, p.x)), fabsf(__fsub_rn(mx.x, p.x)));
+    if (p.y < mn.y || p.y > mx.y) dy = fminf(fabsf(__fsub_rn(mn.y, p.y)), fabsf(__fsub_rn(mx.y, p.y)));
+    if (p.z < mn.z || p.z > mx.z) dz = fminf(fabsf(__fsub_rn(mn.z, p.z)), fabsf(__fsub_rn(mx.z, p.z)));
+    return __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+}
+
+__device__ __forceinline__ void update3(float best[3], float d) {
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+        if (best[j] > d) {
+            const float t = best[j];
+            best[j] = d;
+            d = t;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(128)
+knn3_kernel(uint32_t P, const float4* __restrict__ pts, const float4* __restrict__ box1,
+            uint32_t n1, const float4* __restrict__ box2, uint32_t n2,
+            const float4* __restrict__ box3, uint32_t n3, float* __restrict__ out) {
+    const uint32_t i = blockIdx.x * 128u + threadIdx.x;
+    if (i >= P) return;
+    const float4 self = pts[i];
+    float best[3] = {FLT_MAX, FLT_MAX, FLT_MAX};
+    {
+        const uint32_t lo = i >= 3 ? i - 3 : 0u;
+        const uint32_t hi = min(P - 1, i + 3);
+        for (uint32_t k = lo; k <= hi; k++)
+            if (k != i) update3(best, point_dist2(self, pts[k]));
+    }
+    // The seed only provides the pruning bound; the full search recounts every point once.
+    float bound = best[2];
+    best[0] = best[1] = best[2] = FLT_MAX;
+    for (uint32_t b3 = 0; b3 < n3; b3++) {
+        if (box_dist2(self, box3[2 * b3], box3[2 * b3 + 1]) > fminf(bound, best[2])) continue;
+        const uint32_t e2 = min(n2, (b3 + 1) * kFan);
+        for (uint32_t b2 = b3 * kFan; b2 < e2; b2++) {
+            if (box_dist2(self, box2[2 * b2], box2[2 * b2 + 1]) > fminf(bound, best[2])) continue;
+            const uint32_t e1 = min(n1, (b2 + 1) * kFan);
+            for (uint32_t b1 = b2 * kFan; b1 < e1; b1++) {
+                if (box_dist2(self, box1[2 * (size_t)b1], box1[2 * (size_t)b1 + 1]) >
+                    fminf(bound, best[2]))
+                    continue;
+                const uint32_t e0 = min(P, (b1 + 1) * kFan);
+                for (uint32_t k = b1 * kFan; k < e0; k++)
+                    if (k != i) update3(best, point_dist2(self, pts[k]));
+            }
+        }
+    }
+    out[__float_as_uint(self.w)] = (best[0] + best[1] + best[2]) / 3.0f;
+}
+
+}  // namespace
+
+}  // namespace vegs
+
+extern "C" size_t vegs_dist2_workspace_bytes(int32_t P) {
+    return vegs::knn_view(nullptr, P).bytes + 256;
+}
+
+extern "C" int vegs_dist2(int32_t P, const float* points, float* out, void* workspace,
+                          size_t workspace_bytes, void* stream_) {
+    using namespace vegs;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    if (P < 0 || (P > 0 && (!points || !out || !workspace))) {
+        set_error("vegs_dist2: bad argument");
+        return VEGS_EINVAL;
+    }
+    if (P == 0) return VEGS_OK;
+    if (workspace_bytes < vegs_dist2_workspace_bytes(P)) {
+        set_error("vegs_dist2: workspace too small (%zu < %zu)", workspace_bytes,
+                  vegs_dist2_workspace_bytes(P));
+        return VEGS_ESIZE;
+    }
+    void* base = reinterpret_cast<void*>(align_up(reinterpret_cast<uintptr_t>(workspace)));
+    const KnnView v = knn_view(base, P);
+    const uint32_t n = (uint32_t)P;
+    const uint32_t n1 = div_up(n, kFan), n2 = div_up(n1, kFan), n3 = div_up(n2, kFan);
+
+    bbox_init_kernel<<<1, 32, 0, stream>>>(v.bbox);
+    VEGS_LAUNCH_CHECK("bbox_init", stream, false);
+    const int bb = (int)std::min<uint32_t>(div_up(n, 256), 148u * 8u);
+    bbox_kernel<<<bb, 256, 0, stream>>>(P, points, v.bbox);
+    VEGS_LAUNCH_CHECK("bbox", stream, false);
+    morton_kernel<<<div_up(n, 256), 256, 0, stream>>>(P, points, v.bbox, v.codes0);
+    VEGS_LAUNCH_CHECK("morton", stream, false);
+    bool second = false;
+    int rc = radix_sort_pairs(v.codes0, v.idx0, v.codes1, v.idx1, true, n, 30, v.hist, v.rowtot,
+                              false, &second, stream, false);
+    if (rc) return rc;
+    const uint32_t* order = second ? v.idx1 : v.idx0;
+    gather_points_kernel<<<div_up(n, 256), 256, 0, stream>>>(P, points, order, v.pts);
+    VEGS_LAUNCH_CHECK("gather_points", stream, false);
+    build_boxes_kernel<true><<<div_up((uint64_t)n1 * 32, 256), 256, 0, stream>>>(n, v.pts, n1, v.box1);
+    VEGS_LAUNCH_CHECK("build_boxes1", stream, false);
+    build_boxes_kernel<false><<<div_up((uint64_t)n2 * 32, 256), 256, 0, stream>>>(n1, v.box1, n2, v.box2);
+    VEGS_LAUNCH_CHECK("build_boxes2", stream, false);
+    build_boxes_kernel<false><<<div_up((uint64_t)n3 * 32, 256), 256, 0, stream>>>(n2, v.box2, n3, v.box3);
+    VEGS_LAUNCH_CHECK("build_boxes3", stream, false);
+    knn3_kernel<<<div_up(n, 128), 128, 0, stream>>>(n, v.pts, v.box1, n1, v.box2, n2, v.box3, n3, out);
+    VEGS_LAUNCH_CHECK("knn3", stream, false);
+    return VEGS_OK;
+}

@@ -1,0 +1,399 @@
+"""Drop-in replacement for VEGS's `diff_gaussian_rasterization` Python module.
+
+Same names, argument order, return order and error behaviour as the reference module
+(submodules/diff_gaussian_rasterization/diff_gaussian_rasterization/__init__.py):
+
+    GaussianRasterizationSettings   (:181-193)
+    GaussianRasterizer.forward      (:211-244)  -> color, depth, cov_quat, cov_scale, alpha, radii
+    GaussianRasterizer.markVisible  (:200-209)
+    rasterize_gaussians / _RasterizeGaussians (:21-179)
+
+Underneath, torch is used only for device memory, streams and autograd bookkeeping; the work is
+done by the hand-written sm_100a kernels in libvegs_b200.so through its C ABI
+(include/vegs_b200.h).  There is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import NamedTuple
+
+import torch
+import torch.nn as nn
+
+from .. import _lib
+
+_lib.load()  # fail at import time if the CUDA library is missing
+
+_pinned = {}
+
+
+def _pinned_word(device: torch.device, stream) -> torch.Tensor:
+    key = (device.index, stream.cuda_stream)
+    t = _pinned.get(key)
+    if t is None:
+        t = torch.zeros(1, dtype=torch.int32).pin_memory()
+        _pinned[key] = t
+    return t
+
+
+def _ptr(t):
+    """Device pointer of a tensor, or NULL for None / empty tensors (the reference's convention:
+    empty `torch.Tensor([])` stands for "not provided", __init__.py:221-231)."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _dev_f32(t: torch.Tensor, device: torch.device, name: str) -> torch.Tensor:
+    if t is None or t.numel() == 0:
+        return t
+    if t.dtype != torch.float32:
+        raise TypeError(f"{name} must be float32, got {t.dtype}")
+    if t.device != device:
+        t = t.to(device)
+    return t.contiguous()
+
+
+def cpu_deep_copy_tuple(input_tuple):
+    return tuple(item.cpu().clone() if isinstance(item, torch.Tensor) else item
+                 for item in input_tuple)
+
+
+class _State:
+    """What the forward keeps for the backward (the counterpart of the reference's geomBuffer /
+    binningBuffer / imgBuffer) plus, when requested for tests, the forward-only scratch."""
+    __slots__ = ("P", "D", "M", "W", "H", "R", "geom", "img", "binning", "scratch", "bin_scratch",
+                 "args")
+
+
+def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier,
+                  cov3Ds_precomp, viewmatrix, projmatrix, tanfovx, tanfovy, image_height,
+                  image_width, sh, degree, campos, prefiltered, debug, keep_scratch=False):
+    lib = _lib.load()
+    if means3D.dim() != 2 or means3D.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if not means3D.is_cuda:
+        raise RuntimeError("means3D must be a CUDA tensor: this rasterizer has no CPU path")
+    device = means3D.device
+    P = int(means3D.shape[0])
+    H, W = int(image_height), int(image_width)
+    f32 = dict(dtype=torch.float32, device=device)
+
+    st = _State()
+    st.P, st.D, st.W, st.H, st.R = P, int(degree), W, H, 0
+    st.M = int(sh.shape[1]) if (sh is not None and sh.numel() != 0) else 0
+    st.geom = st.img = st.binning = st.scratch = st.bin_scratch = None
+    st.args = None
+
+    if P == 0:
+        # reference: outputs stay at their zero fill, nothing is launched (rasterize_points.cu:88)
+        z = lambda c: torch.zeros((c, H, W), **f32)
+        radii = torch.zeros((0,), dtype=torch.int32, device=device)
+        return z(3), z(1), z(4), z(3), z(1), radii, st
+
+    with torch.cuda.device(device):
+        stream = torch.cuda.current_stream(device)
+        means3D = _dev_f32(means3D, device, "means3D")
+        opacities = _dev_f32(opacities, device, "opacities")
+        sh = _dev_f32(sh, device, "shs")
+        colors_precomp = _dev_f32(colors_precomp, device, "colors_precomp")
+        scales = _dev_f32(scales, device, "scales")
+        rotations = _dev_f32(rotations, device, "rotations")
+        cov3Ds_precomp = _dev_f32(cov3Ds_precomp, device, "cov3D_precomp")
+        bg = _dev_f32(bg, device, "bg")
+        viewmatrix = _dev_f32(viewmatrix, device, "viewmatrix")
+        projmatrix = _dev_f32(projmatrix, device, "projmatrix")
+        campos = _dev_f32(campos, device, "campos")
+
+        out_color = torch.empty((3, H, W), **f32)
+        out_depth = torch.empty((1, H, W), **f32)
+        out_quat = torch.empty((4, H, W), **f32)
+        out_scale = torch.empty((3, H, W), **f32)
+        out_alpha = torch.empty((1, H, W), **f32)
+        radii = torch.empty((P,), dtype=torch.int32, device=device)
+
+        u8 = dict(dtype=torch.uint8, device=device)
+        st.geom = torch.empty(lib.vegs_geom_bytes(P), **u8)
+        st.img = torch.empty(lib.vegs_img_bytes(W, H), **u8)
+        st.scratch = torch.empty(lib.vegs_scratch_bytes(P), **u8)
+        word = _pinned_word(device, stream)
+
+        a = _lib.VegsForwardArgs()
+        a.P, a.D, a.M, a.W, a.H = P, st.D, st.M, W, H
+        a.background = _ptr(bg)
+        a.means3D = _ptr(means3D)
+        a.shs = _ptr(sh)
+        a.colors_precomp = _ptr(colors_precomp)
+        a.opacities = _ptr(opacities)
+        a.scales = _ptr(scales)
+        a.rotations = _ptr(rotations)
+        a.cov3D_precomp = _ptr(cov3Ds_precomp)
+        a.viewmatrix = _ptr(viewmatrix)
+        a.projmatrix = _ptr(projmatrix)
+        a.campos = _ptr(campos)
+        a.scale_modifier = float(scale_modifier)
+        a.tan_fovx, a.tan_fovy = float(tanfovx), float(tanfovy)
+        a.prefiltered, a.debug = int(bool(prefiltered)), int(bool(debug))
+        a.out_color, a.out_depth = out_color.data_ptr(), out_depth.data_ptr()
+        a.out_cov_quat, a.out_cov_scale = out_quat.data_ptr(), out_scale.data_ptr()
+        a.out_alpha, a.radii = out_alpha.data_ptr(), radii.data_ptr()
+        a.geom, a.img, a.scratch = st.geom.data_ptr(), st.img.data_ptr(), st.scratch.data_ptr()
+        a.num_rendered_host = word.data_ptr()
+
+        sp = C.c_void_p(stream.cuda_stream)
+        _lib.check(lib.vegs_forward_prepare(C.byref(a), sp), "vegs_forward_prepare")
+        stream.synchronize()  # the one host sync of the forward (reference: rasterizer_impl.cu:286)
+        R = int(word.item())
+        st.R = R
+        if R > 0:
+            st.binning = torch.empty(lib.vegs_binning_bytes(R), **u8)
+            st.bin_scratch = torch.empty(lib.vegs_bin_scratch_bytes(R, W, H), **u8)
+            a.binning, a.bin_scratch = st.binning.data_ptr(), st.bin_scratch.data_ptr()
+        _lib.check(lib.vegs_forward_render(C.byref(a), R, sp), "vegs_forward_render")
+        if keep_scratch:
+            st.args = a
+            # keep the inputs alive for as long as the args struct may be used
+            st.args._keep = (bg, means3D, sh, colors_precomp, opacities, scales, rotations,
+                             cov3Ds_precomp, viewmatrix, projmatrix, campos, out_color, out_depth,
+                             out_quat, out_scale, out_alpha, radii)
+        else:
+            st.scratch = None
+            st.bin_scratch = None
+    return out_color, out_depth, out_quat, out_scale, out_alpha, radii, st
+
+
+def export_state(st: _State, radii: torch.Tensor):
+    """Test support: the binning / geometry state in the reference's formats (see
+    vegs_export_state in include/vegs_b200.h).  Needs a state made with keep_scratch=True."""
+    lib = _lib.load()
+    if st.args is None:
+        raise RuntimeError("export_state needs a forward run with keep_scratch=True")
+    device = radii.device
+    P, W, H, R = st.P, st.W, st.H, st.R
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    out = {
+        "point_list_keys": torch.zeros(max(R, 1), dtype=torch.int64, device=device),
+        "point_list": torch.zeros(max(R, 1), dtype=torch.int32, device=device),
+        "ranges": torch.zeros((T, 2), dtype=torch.int32, device=device),
+        "tiles_touched": torch.zeros(P, dtype=torch.int32, device=device),
+        "depths": torch.zeros(P, dtype=torch.float32, device=device),
+        "means2D": torch.zeros((P, 2), dtype=torch.float32, device=device),
+        "conic_opacity": torch.zeros((P, 4), dtype=torch.float32, device=device),
+        "rgb": torch.zeros((P, 3), dtype=torch.float32, device=device),
+        "n_contrib": torch.zeros((H, W), dtype=torch.int32, device=device),
+    }
+    with torch.cuda.device(device):
+        stream = torch.cuda.current_stream(device)
+        rc = lib.vegs_export_state(
+            C.byref(st.args), R, out["point_list_keys"].data_ptr(), out["point_list"].data_ptr(),
+            out["ranges"].data_ptr(), out["tiles_touched"].data_ptr(), out["depths"].data_ptr(),
+            out["means2D"].data_ptr(), out["conic_opacity"].data_ptr(), out["rgb"].data_ptr(),
+            out["n_contrib"].data_ptr(), C.c_void_p(stream.cuda_stream))
+        _lib.check(rc, "vegs_export_state")
+        stream.synchronize()
+    out["point_list_keys"] = out["point_list_keys"][:R]
+    out["point_list"] = out["point_list"][:R]
+    out["num_rendered"] = R
+    return out
+
+
+def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotations,
+                   scale_modifier, cov3Ds_precomp, viewmatrix, projmatrix, tanfovx, tanfovy,
+                   grad_color, grad_depth, grad_cov_quat, grad_cov_scale, grad_alpha, sh, campos,
+                   out_alpha, opacities_shape, debug):
+    lib = _lib.load()
+    device = means3D.device
+    P, M = st.P, st.M
+    f32 = dict(dtype=torch.float32, device=device)
+    have_sh = sh is not None and sh.numel() != 0
+    have_sr = scales is not None and scales.numel() != 0
+    have_cov = cov3Ds_precomp is not None and cov3Ds_precomp.numel() != 0
+
+    if P == 0:
+        e = lambda *s: torch.zeros(s, **f32)
+        return (e(0, 3), e(0, 3), e(0, M, 3) if have_sh else None, None if have_sh else e(0, 3),
+                torch.zeros(opacities_shape, **f32), e(0, 3) if have_sr else None,
+                e(0, 4) if have_sr else None, e(0, 6) if have_cov else None)
+
+    with torch.cuda.device(device):
+        stream = torch.cuda.current_stream(device)
+        g = lambda t, n: _dev_f32(t, device, n) if t is not None else None
+        grad_color, grad_depth = g(grad_color, "grad_color"), g(grad_depth, "grad_depth")
+        grad_alpha = g(grad_alpha, "grad_alpha")
+        grad_cov_quat, grad_cov_scale = g(grad_cov_quat, "grad_cov_quat"), g(grad_cov_scale, "grad_cov_scale")
+        bg = _dev_f32(bg, device, "bg")
+        viewmatrix = _dev_f32(viewmatrix, device, "viewmatrix")
+        projmatrix = _dev_f32(projmatrix, device, "projmatrix")
+        campos = _dev_f32(campos, device, "campos")
+        means3D = _dev_f32(means3D, device, "means3D")
+        sh = _dev_f32(sh, device, "shs")
+        colors_precomp = _dev_f32(colors_precomp, device, "colors_precomp")
+        scales = _dev_f32(scales, device, "scales")
+        rotations = _dev_f32(rotations, device, "rotations")
+        cov3Ds_precomp = _dev_f32(cov3Ds_precomp, device, "cov3D_precomp")
+
+        dmeans3D = torch.empty((P, 3), **f32)
+        dmeans2D = torch.empty((P, 3), **f32)
+        dopac = torch.empty(opacities_shape, **f32)
+        dsh = torch.empty((P, M, 3), **f32) if have_sh else None
+        dcolors = None if have_sh else torch.empty((P, 3), **f32)
+        dscales = torch.empty((P, 3), **f32) if have_sr else None
+        drots = torch.empty((P, 4), **f32) if have_sr else None
+        dcov = torch.empty((P, 6), **f32) if have_cov else None
+        bwd_scratch = torch.empty(lib.vegs_bwd_scratch_bytes(P), dtype=torch.uint8, device=device)
+
+        b = _lib.VegsBackwardArgs()
+        b.P, b.D, b.M, b.W, b.H, b.R = P, st.D, M, st.W, st.H, st.R
+        b.background = _ptr(bg)
+        b.means3D = _ptr(means3D)
+        b.shs = _ptr(sh)
+        b.colors_precomp = _ptr(colors_precomp)
+        b.scales = _ptr(scales)
+        b.rotations = _ptr(rotations)
+        b.cov3D_precomp = _ptr(cov3Ds_precomp)
+        b.viewmatrix, b.projmatrix, b.campos = _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos)
+        b.scale_modifier = float(scale_modifier)
+        b.tan_fovx, b.tan_fovy = float(tanfovx), float(tanfovy)
+        b.debug = int(bool(debug))
+        b.radii, b.out_alpha = radii.data_ptr(), out_alpha.data_ptr()
+        b.dL_dout_color, b.dL_dout_depth = _ptr(grad_color), _ptr(grad_depth)
+        b.dL_dout_cov_quat, b.dL_dout_cov_scale = _ptr(grad_cov_quat), _ptr(grad_cov_scale)
+        b.dL_dout_alpha = _ptr(grad_alpha)
+        b.geom, b.img = st.geom.data_ptr(), st.img.data_ptr()
+        b.binning = st.binning.data_ptr() if st.binning is not None else None
+        b.bwd_scratch = bwd_scratch.data_ptr()
+        b.dL_dmeans3D, b.dL_dmeans2D = dmeans3D.data_ptr(), dmeans2D.data_ptr()
+        b.dL_dsh = _ptr(dsh)
+        b.dL_dcolors = _ptr(dcolors)
+        b.dL_dopacity = dopac.data_ptr()
+        b.dL_dscales, b.dL_drotations = _ptr(dscales), _ptr(drots)
+        b.dL_dcov3D = _ptr(dcov)
+        _lib.check(lib.vegs_backward(C.byref(b), C.c_void_p(stream.cuda_stream)), "vegs_backward")
+    return dmeans3D, dmeans2D, dsh, dcolors, dopac, dscales, drots, dcov
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                        cov3Ds_precomp, raster_settings):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales,
+                                     rotations, cov3Ds_precomp, raster_settings)
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                cov3Ds_precomp, raster_settings):
+        rs = raster_settings
+        args = (rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier,
+                cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
+                rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered,
+                rs.debug)
+        if rs.debug:
+            cpu_args = cpu_deep_copy_tuple(args)  # copy them before they can be corrupted
+            try:
+                color, depth, cov_quat, cov_scale, alpha, radii, st = _forward_impl(*args)
+            except Exception as ex:
+                torch.save(cpu_args, "snapshot_fw.dump")
+                print("\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.")
+                raise ex
+        else:
+            color, depth, cov_quat, cov_scale, alpha, radii, st = _forward_impl(*args)
+
+        ctx.raster_settings = rs
+        ctx.state = st
+        ctx.num_rendered = st.R
+        ctx.opacities_shape = tuple(opacities.shape)
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh,
+                              alpha)
+        ctx.mark_non_differentiable(radii)
+        return color, depth, cov_quat, cov_scale, alpha, radii
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_out_depth, grad_out_cov_quat, grad_out_cov_scale,
+                 grad_out_alpha, _):
+        rs = ctx.raster_settings
+        colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, alpha = ctx.saved_tensors
+        args = (ctx.state, rs.bg, means3D, radii, colors_precomp, scales, rotations,
+                rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
+                rs.tanfovy, grad_out_color, grad_out_depth, grad_out_cov_quat, grad_out_cov_scale,
+                grad_out_alpha, sh, rs.campos, alpha, ctx.opacities_shape, rs.debug)
+        if rs.debug:
+            cpu_args = cpu_deep_copy_tuple(args[1:])
+            try:
+                grads = _backward_impl(*args)
+            except Exception as ex:
+                torch.save(cpu_args, "snapshot_bw.dump")
+                print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
+                raise ex
+        else:
+            grads = _backward_impl(*args)
+        (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales,
+         grad_rotations, grad_cov3Ds_precomp) = grads
+        return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities,
+                grad_scales, grad_rotations, grad_cov3Ds_precomp, None)
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        """Boolean mask of the points in front of the near plane (view z > 0.2)."""
+        lib = _lib.load()
+        with torch.no_grad():
+            rs = self.raster_settings
+            if not positions.is_cuda:
+                raise RuntimeError("positions must be a CUDA tensor: there is no CPU path")
+            device = positions.device
+            P = int(positions.shape[0])
+            visible = torch.zeros((P,), dtype=torch.bool, device=device)
+            if P != 0:
+                pos = _dev_f32(positions, device, "positions")
+                view = _dev_f32(rs.viewmatrix, device, "viewmatrix")
+                proj = _dev_f32(rs.projmatrix, device, "projmatrix")
+                with torch.cuda.device(device):
+                    stream = torch.cuda.current_stream(device)
+                    rc = lib.vegs_mark_visible(P, pos.data_ptr(), view.data_ptr(), proj.data_ptr(),
+                                               visible.data_ptr(), C.c_void_p(stream.cuda_stream))
+                    _lib.check(rc, "vegs_mark_visible")
+        return visible
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None,
+                rotations=None, cov3D_precomp=None):
+        raster_settings = self.raster_settings
+
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+
+        if shs is None:
+            shs = torch.Tensor([])
+        if colors_precomp is None:
+            colors_precomp = torch.Tensor([])
+        if scales is None:
+            scales = torch.Tensor([])
+        if rotations is None:
+            rotations = torch.Tensor([])
+        if cov3D_precomp is None:
+            cov3D_precomp = torch.Tensor([])
+
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales,
+                                   rotations, cov3D_precomp, raster_settings)
