@@ -1,0 +1,341 @@
+#!/usr/bin/env python
+"""bench.py — forward+backward views/s through GaussianRasterizer at LiDAR density.
+
+Workload (BASELINE.json config 3): 6 M Gaussians, 1408x376, a step = one 8-view batch of the
+synthetic drive split round-robin over the ranks (strong scaling: the batch is fixed), per view a
+forward and a backward through the drop-in GaussianRasterizer with a loss on colour + covariance
+maps, local gradient accumulation, per-view densification statistics, then one all-reduce
+(vegs_b200/dist.py).  `--impl reference` runs the same step with the reference's own CUDA
+extension from baseline/_ref (falls back to the CPU oracle port when that cannot be imported).
+
+One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for how each field is obtained.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "fwd+bwd views/s @6M Gaussians 1408x376"
+UNIT = "views/s"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "200", "-i", str(gpu_index)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush(); self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if sm:
+            out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                   "samples": len(sm)}
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        return out
+
+
+def load_rasterizer(impl: str):
+    """(module, kind): the GaussianRasterizer implementation under test."""
+    if impl == "ours":
+        import vegs_b200.diff_gaussian_rasterization as m
+        return m, "vegs_b200"
+    import util
+    if util.reference_available():
+        try:
+            return util.import_reference()["diff_gaussian_rasterization"], "reference-cuda"
+        except Exception as ex:  # noqa: BLE001
+            sys.stderr.write(f"reference extension not importable: {ex}\n")
+    return None, "oracle-port"
+
+
+class Workload:
+    def __init__(self, args, device, rank, world):
+        from vegs_b200 import synth, dist as vdist
+        self.synth, self.vdist = synth, vdist
+        self.device, self.rank, self.world = device, rank, world
+        self.P, self.n_views = args.P, args.views
+        sc = synth.make_scene(args.P, seed=7)
+        self.params = {k: v.to(device).requires_grad_(True) for k, v in sc.items()}
+        self.cams = [synth.make_camera(k, scale=args.scale, device=device) for k in range(args.views)]
+        self.W, self.H = self.cams[0].W, self.cams[0].H
+        g = torch.Generator().manual_seed(123)
+        H, W = self.H, self.W
+        # per-view step inputs: target image, quaternion-map weights, scale-map weights (10 planes)
+        self.host_targets = [torch.rand(10, H, W, generator=g).pin_memory() for _ in range(args.views)]
+        self.dev_targets = [t.to(device) for t in self.host_targets]
+        self.bg = torch.zeros(3, device=device)
+        self.my_views = vdist.shard_views(args.views, rank, world)
+        self.flat = None
+        self.h2d_bytes = sum(self.host_targets[v].numel() * 4 for v in range(args.views))
+
+    def settings(self, mod, cam):
+        return mod.GaussianRasterizationSettings(
+            image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=self.bg,
+            scale_modifier=1.0, viewmatrix=cam.viewmatrix, projmatrix=cam.projmatrix, sh_degree=3,
+            campos=cam.campos, prefiltered=False, debug=False)
+
+    def step(self, mod, resident: bool):
+        """One optimisation step's rasterizer work: local views fwd+bwd, stats, all-reduce."""
+        p = self.params
+        for t in p.values():
+            t.grad = None
+        stats = self.vdist.DensificationStats(self.P, self.device)
+        total = torch.zeros((), device=self.device)
+        for v in self.my_views:
+            tgt = self.dev_targets[v] if resident else self.host_targets[v].to(self.device, non_blocking=True)
+            means2D = torch.zeros_like(p["means3D"], requires_grad=True)
+            rast = mod.GaussianRasterizer(self.settings(mod, self.cams[v]))
+            color, depth, quat, scale, alpha, radii = rast(
+                means3D=p["means3D"], means2D=means2D, opacities=p["opacities"], shs=p["shs"],
+                scales=p["scales"], rotations=p["rotations"])
+            loss = (color - tgt[0:3]).abs().mean() + 0.05 * ((quat * tgt[3:7]).sum(0).abs().mean()
+                                                             + (scale * tgt[7:10]).sum(0).abs().mean())
+            loss.backward()
+            stats.add_view(means2D.grad, radii)
+            total = total + loss.detach()
+        if self.world > 1:
+            self.flat = self.vdist.allreduce_step(p, stats, flat=self.flat)
+        if not resident:
+            return float(total.item())   # device -> host read of the step's result
+        return total
+
+
+def timed(fn, steps, warmup, device, world):
+    import torch.distributed as dist
+    for _ in range(warmup):
+        fn()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize(device)
+    if world > 1:
+        dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=device)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item())
+
+
+def kernel_groups(prof):
+    """Per-view milliseconds of each stage group from the library's event profile."""
+    groups = {"preprocess_fwd": ["preprocess_fwd"],
+              "binning": ["radix_hist", "radix_rowscan", "radix_scatter", "tile_count", "tile_spine", "emit",
+                          "tile_ranges", "memset_ranges", "num_rendered_d2h"],
+              "composite_fwd": ["composite_fwd"],
+              "composite_bwd": ["composite_bwd", "memset_bwd_acc"],
+              "preprocess_bwd": ["preprocess_bwd"]}
+    return {g: sum(prof.get(n, (0.0, 0))[0] for n in names) for g, names in groups.items()}
+
+
+def workload_stats(wl, mod):
+    """P, V, R, R_f, Npix for view 0 .. n-1 (mean), from the library's exported state."""
+    import vegs_b200.diff_gaussian_rasterization as dgr
+    Vs, Rs, Rfs = [], [], []
+    p = wl.params
+    for cam in wl.cams[:2]:
+        with torch.no_grad():
+            res = dgr._forward_impl(wl.bg, p["means3D"], torch.Tensor([]), p["opacities"], p["scales"],
+                                    p["rotations"], 1.0, torch.Tensor([]), cam.viewmatrix, cam.projmatrix,
+                                    cam.tanfovx, cam.tanfovy, cam.H, cam.W, p["shs"], 3, cam.campos, False,
+                                    False, keep_scratch=True)
+        st = dgr.export_state(res[6], res[5])
+        gx, gy = (cam.W + 15) // 16, (cam.H + 15) // 16
+        nc = st["n_contrib"].to(torch.int64)
+        pad = torch.zeros((gy * 16, gx * 16), dtype=torch.int64, device=nc.device)
+        pad[:cam.H, :cam.W] = nc
+        tmax = pad.view(gy, 16, gx, 16).amax(dim=(1, 3)).reshape(-1)
+        rl = (st["ranges"][:, 1] - st["ranges"][:, 0]).to(torch.int64)
+        rf = torch.minimum(rl, 256 * ((tmax + 255) // 256)).sum()
+        Vs.append(int((res[5] > 0).sum())); Rs.append(int(st["num_rendered"])); Rfs.append(int(rf))
+        del res, st
+    return dict(P=wl.P, V=float(np.mean(Vs)), R=float(np.mean(Rs)), R_f=float(np.mean(Rfs)), Npix=wl.W * wl.H)
+
+
+def algorithmic_bytes(s):
+    """SURVEY.md §8(d) per-view byte model."""
+    P, V, R, Rf, N = s["P"], s["V"], s["R"], s["R_f"], s["Npix"]
+    return {"preprocess_fwd": 20 * P + 299 * V, "binning": 44 * R, "composite_fwd": 56 * Rf + 52 * N,
+            "composite_bwd": 72 * Rf + 72 * N + 80 * V, "preprocess_bwd": 307 * V + 284 * P}
+
+
+def cpu_baseline_oracle(args, n_views_sample=1):
+    """The oracle port (CPU restatement of the reference algorithm) timed on the host cores on a
+    bounded sample of the same workload: `n_views_sample` views of the same scene."""
+    import util
+    from oracle import oracle
+    from vegs_b200 import synth
+    sc = synth.make_scene(args.P, seed=7)
+    t_total = 0.0
+    for k in range(n_views_sample):
+        cam = synth.make_camera(k, scale=args.scale)
+        cot = util.np_cotangents(cam.W, cam.H)
+        t0 = time.time()
+        f = util.run_oracle(sc, cam, cot=cot)
+        t_total += time.time() - t0
+        del f
+    return dict(value=n_views_sample / t_total, unit=UNIT, cores=oracle.num_threads(), kind="port",
+                sample=f"{n_views_sample} view(s) fwd+bwd of the {args.P}-Gaussian scene at "
+                       f"{int(1408 * args.scale)}x{int(376 * args.scale)}, oracle/vegs_oracle.c with OpenMP")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--P", type=int, default=6_000_000)
+    ap.add_argument("--views", type=int, default=8)
+    ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    mod, kind = load_rasterizer(args.impl)
+    if args.impl == "reference" and mod is None:
+        # no CUDA reference on this box: time the CPU port, rank 0 only
+        if rank != 0:
+            return
+        cb = cpu_baseline_oracle(args, n_views_sample=max(1, min(args.steps, 3)))
+        line = dict(metric=METRIC, value=cb["value"], unit=UNIT, n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
+                    ms_per_step=1000.0 * args.views / cb["value"], higher_is_better=True, scaling="strong",
+                    vs_baseline=None, dtype="f32", data="synthetic", impl="reference",
+                    config=dict(workload=f"{args.P} Gaussians, {args.views}-view batch, CPU oracle port"),
+                    cpu_baseline=cb, e2e=dict(value=cb["value"], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                    gpu_launches=0)
+        print(json.dumps(line)); return
+
+    assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU path)"
+    device = torch.device("cuda", local_rank)
+    torch.cuda.set_device(device)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+    from vegs_b200 import _lib
+    wl = Workload(args, device, rank, world)
+
+    launches0 = _lib.launch_count()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ms = timed(lambda: wl.step(mod, True), args.steps, args.warmup, device, world)
+    clocks = sampler.stop() if sampler else None
+    launches = (_lib.launch_count() - launches0) * args.steps // (args.steps + args.warmup)
+    ms_step = ms / args.steps
+    value = args.views / (ms_step / 1000.0)
+
+    ms_e2e = timed(lambda: wl.step(mod, False), args.steps, 1, device, world)
+    e2e_value = args.views / (ms_e2e / args.steps / 1000.0)
+
+    line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
+                ms_per_step=ms_step, higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32",
+                data="synthetic",
+                config=dict(workload=f"LiDAR-dense street scene, {args.P} Gaussians SH-3, {args.views}-view batch at "
+                                     f"{wl.W}x{wl.H} split round-robin over {world} GPU(s), fwd+bwd through "
+                                     "GaussianRasterizer + grad/densification-stat all-reduce (BASELINE config 3)",
+                            P=args.P, views_per_step=args.views, image=[wl.W, wl.H], parallelism=f"view-parallel x{world}",
+                            l2="inputs (1.4 GB of parameters per view) exceed the 126 MB L2; no explicit flush",
+                            impl=kind),
+                e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=wl.h2d_bytes * len(wl.my_views) // args.views * world,
+                         d2h_bytes_per_step=4 * world),
+                gpu_launches=int(launches) if args.impl == "ours" else 0, clocks=clocks)
+    if args.impl == "reference":
+        line["impl"] = "reference"
+        line["cpu_baseline"] = dict(value=value, unit=UNIT, cores=0, kind="reference",
+                                    sample="the reference's own CUDA extension (baseline/_ref, unmodified) on the GPU: "
+                                           "the reference has no CPU implementation of this path")
+    if rank == 0 and args.impl == "ours":
+        # ---- roofline leg: per-kernel CUDA-event times from the library, byte model of SURVEY §8d
+        peak, peak_src = peaks()
+        _lib.profile_enable(True)
+        wl.step(mod, True)
+        torch.cuda.synchronize(device)
+        prof = _lib.profile_collect()
+        _lib.profile_enable(False)
+        nv = max(1, len(wl.my_views))
+        groups = {k: v / nv for k, v in kernel_groups(prof).items()}
+        stats = workload_stats(wl, mod)
+        bts = algorithmic_bytes(stats)
+        dom = max(groups, key=groups.get)
+        per = {}
+        for k in groups:
+            gbs = bts[k] / (groups[k] * 1e-3) / 1e9 if groups[k] > 0 else 0.0
+            per[k] = dict(ms_per_view=groups[k], algorithmic_bytes=bts[k], gbs=gbs, frac=gbs / peak)
+        line["roofline"] = dict(bound="hbm", kernel=dom, achieved=per[dom]["gbs"], peak=peak, unit="GB/s",
+                                frac=per[dom]["frac"], traffic=None, peak_source=peak_src,
+                                how="CUDA events recorded by the library after every launch on the launching stream, "
+                                    "one extra step after the timed region")
+        line["kernels"] = per
+        line["kernel_ms_per_view_raw"] = {k: v[0] / nv for k, v in prof.items()}
+        line["workload_stats"] = stats
+        view_bytes = sum(bts.values())
+        line["view_roofline"] = dict(algorithmic_bytes=view_bytes, ms_per_view=ms_step / nv,
+                                     frac=view_bytes / (ms_step / nv * 1e-3) / 1e9 / peak)
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline_oracle(args, 1)
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

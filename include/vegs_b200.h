@@ -193,6 +193,14 @@ int vegs_export_state(const VegsForwardArgs* args, int32_t num_rendered, uint64_
 /* Number of kernels launched by this library in this process so far (bench bookkeeping). */
 uint64_t vegs_kernel_launch_count(void);
 
+/*
+ * Measurement support (bench.py's roofline leg): while enabled, a CUDA event is recorded on the
+ * launching stream after every kernel; vegs_profile_collect synchronises those events and writes
+ * one text line per kernel name, "name total_ms launches\n", into buf, then forgets them.
+ */
+void vegs_profile_enable(int32_t on);
+int vegs_profile_collect(char* buf, size_t buf_bytes);
+
 #ifdef __cplusplus
 }
 #endif

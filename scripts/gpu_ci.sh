@@ -1,0 +1,31 @@
+#!/bin/bash
+# One GPU-box session: smoke, GPU tests in separate processes (a CUDA fault in one group must not
+# hide the others), golden-vector generation from the reference extension, a short bench.
+# Usage: gpurun --timeout 1500 -- 'bash scripts/gpu_ci.sh [stage ...]'
+set -u
+mkdir -p gpurun_out
+cd "$(dirname "$0")/.."
+stages=${@:-smoke tests golden bench_small}
+nvidia-smi --query-gpu=name,memory.total,clocks.max.sm --format=csv > gpurun_out/gpu.txt 2>&1
+nproc >> gpurun_out/gpu.txt
+for s in $stages; do
+  case $s in
+    smoke)
+      timeout 600 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" | tee -a gpurun_out/summary.txt ;;
+    tests)
+      for grp in "dist2" "mark_visible or edge or debug" "against_oracle or modes or deterministic" "golden" "reference_live" "full_size"; do
+        name=$(echo "$grp" | tr ' ' '_')
+        timeout 900 python -m pytest tests -m gpu -q -k "$grp" -p no:cacheprovider > "gpurun_out/pytest_${name}.log" 2>&1
+        echo "pytest[$grp] rc=$? $(tail -1 gpurun_out/pytest_${name}.log)" | tee -a gpurun_out/summary.txt
+      done ;;
+    golden)
+      timeout 600 python tests/golden/make_golden.py gpurun_out/golden > gpurun_out/golden.log 2>&1; echo "golden rc=$?" | tee -a gpurun_out/summary.txt ;;
+    bench_small)
+      timeout 600 python bench.py --P 1000000 --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/bench_small.json 2> gpurun_out/bench_small.err; echo "bench_small rc=$?" | tee -a gpurun_out/summary.txt
+      timeout 600 python bench.py --impl reference --P 1000000 --steps 2 --warmup 1 > gpurun_out/bench_small_ref.json 2> gpurun_out/bench_small_ref.err; echo "bench_small_ref rc=$?" | tee -a gpurun_out/summary.txt ;;
+    bench)
+      timeout 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?" | tee -a gpurun_out/summary.txt
+      timeout 900 python bench.py --impl reference > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "bench_ref rc=$?" | tee -a gpurun_out/summary.txt ;;
+  esac
+done
+cat gpurun_out/summary.txt

@@ -73,6 +73,8 @@ SIGNATURES = {
                              C.c_void_p]),
     "vegs_export_state": (C.c_int, [C.POINTER(VegsForwardArgs), C.c_int32] + [C.c_void_p] * 10),
     "vegs_kernel_launch_count": (C.c_uint64, []),
+    "vegs_profile_enable": (None, [C.c_int32]),
+    "vegs_profile_collect": (C.c_int, [C.c_char_p, C.c_size_t]),
 }
 
 _lib = None
@@ -109,3 +111,18 @@ def check(rc: int, what: str) -> None:
 
 def launch_count() -> int:
     return int(load().vegs_kernel_launch_count())
+
+
+def profile_enable(on: bool) -> None:
+    load().vegs_profile_enable(1 if on else 0)
+
+
+def profile_collect() -> dict:
+    """{kernel name: (total_ms, launches)} since profiling was enabled / last collected."""
+    buf = C.create_string_buffer(1 << 16)
+    check(load().vegs_profile_collect(buf, len(buf)), "vegs_profile_collect")
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, ms, n = line.split()
+        out[name] = (float(ms), int(n))
+    return out

@@ -6,6 +6,11 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
 #include "common.cuh"
 
 namespace vegs {
@@ -21,6 +26,23 @@ void set_error(const char* fmt, ...) {
 }
 
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+// ---- optional per-kernel timing with CUDA events on the launching stream (bench.py's roofline
+// leg).  When enabled, an event is recorded after every launch; a kernel's time is the interval
+// from the previous event of the same entry-point call to its own.
+struct ProfEvent { const char* name; cudaEvent_t ev; };
+static std::atomic<bool> g_prof_on{false};
+static std::mutex g_prof_mu;
+static std::vector<ProfEvent> g_prof_events;
+
+void prof_mark(const char* name, cudaStream_t stream) {
+    if (!g_prof_on.load(std::memory_order_relaxed)) return;
+    cudaEvent_t ev;
+    if (cudaEventCreate(&ev) != cudaSuccess) return;
+    cudaEventRecord(ev, stream);
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    g_prof_events.push_back({name, ev});
+}
 
 static int tile_bits(int T) {
     int b = 0;
@@ -51,6 +73,40 @@ using namespace vegs;
 extern "C" int vegs_abi_version(void) { return VEGS_ABI_VERSION; }
 extern "C" const char* vegs_last_error(void) { return g_error; }
 extern "C" uint64_t vegs_kernel_launch_count(void) { return g_launches.load(); }
+
+extern "C" void vegs_profile_enable(int32_t on) { g_prof_on.store(on != 0); }
+
+extern "C" int vegs_profile_collect(char* buf, size_t buf_bytes) {
+    std::vector<ProfEvent> evs;
+    {
+        std::lock_guard<std::mutex> lk(g_prof_mu);
+        evs.swap(g_prof_events);
+    }
+    std::map<std::string, std::pair<double, long>> acc;
+    cudaError_t err = cudaSuccess;
+    for (size_t i = 0; i < evs.size(); i++) {
+        if (err == cudaSuccess) err = cudaEventSynchronize(evs[i].ev);
+        if (err == cudaSuccess && i > 0 && std::string(evs[i].name) != "__start") {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, evs[i - 1].ev, evs[i].ev) == cudaSuccess) {
+                auto& e = acc[evs[i].name];
+                e.first += ms;
+                e.second += 1;
+            }
+        }
+    }
+    for (auto& e : evs) cudaEventDestroy(e.ev);
+    if (err != cudaSuccess) { set_error("profile collect: %s", cudaGetErrorString(err)); return VEGS_ECUDA; }
+    std::string out;
+    char line[256];
+    for (auto& kv : acc) {
+        snprintf(line, sizeof(line), "%s %.6f %ld\n", kv.first.c_str(), kv.second.first, kv.second.second);
+        out += line;
+    }
+    if (!buf || buf_bytes < out.size() + 1) { set_error("profile buffer too small"); return VEGS_ESIZE; }
+    memcpy(buf, out.c_str(), out.size() + 1);
+    return VEGS_OK;
+}
 
 extern "C" size_t vegs_geom_bytes(int32_t P) { return geom_view(nullptr, P).bytes + 256; }
 extern "C" size_t vegs_scratch_bytes(int32_t P) { return scratch_view(nullptr, P).bytes + 256; }
@@ -95,6 +151,7 @@ extern "C" int vegs_forward_prepare(const VegsForwardArgs* a, void* stream_) {
     const GeomView g = geom_view(aligned(a->geom), a->P);
     const ScratchView s = scratch_view(aligned(a->scratch), a->P);
 
+    prof_mark("__start", stream);
     rc = launch_preprocess_fwd(*a, g, s, stream);
     if (rc) return rc;
     bool second = false;
@@ -107,6 +164,7 @@ extern "C" int vegs_forward_prepare(const VegsForwardArgs* a, void* stream_) {
     if (rc) return rc;
     VEGS_CUDA_OK(cudaMemcpyAsync(a->num_rendered_host, g.counters, sizeof(int32_t),
                                  cudaMemcpyDeviceToHost, stream));
+    prof_mark("num_rendered_d2h", stream);
     return VEGS_OK;
 }
 
@@ -134,6 +192,7 @@ extern "C" int vegs_forward_render(const VegsForwardArgs* a, int32_t num_rendere
     b.point_list = nullptr;
     b.bytes = 0;
     const uint32_t* sorted_keys = nullptr;
+    prof_mark("__start", stream);
     if (R > 0) {
         b = bin_view(aligned(a->binning), R);
         const BinScratchView bs = bin_scratch_view(aligned(a->bin_scratch), R);
@@ -181,7 +240,9 @@ extern "C" int vegs_backward(const VegsBackwardArgs* a, void* stream_) {
     b.bytes = 0;
     if (a->R > 0) b = bin_view(aligned(a->binning), a->R);
     float4* acc = reinterpret_cast<float4*>(aligned(a->bwd_scratch));
+    prof_mark("__start", stream);
     VEGS_CUDA_OK(cudaMemsetAsync(acc, 0, (size_t)a->P * 48, stream));
+    prof_mark("memset_bwd_acc", stream);
     if (a->R > 0) {
         rc = launch_composite_bwd(*a, g, im, b, acc, stream);
         if (rc) return rc;

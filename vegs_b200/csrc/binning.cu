@@ -218,6 +218,7 @@ int launch_emit(int P, const uint32_t* order, const uint2* rect, const uint32_t*
 int launch_tile_ranges(uint32_t R, const uint32_t* tkeys_sorted, uint2* ranges, int T,
                        cudaStream_t stream, bool debug) {
     VEGS_CUDA_OK(cudaMemsetAsync(ranges, 0, (size_t)T * sizeof(uint2), stream));
+    prof_mark("memset_ranges", stream);
     if (R > 0) {
         tile_ranges_kernel<<<div_up(R, 256), 256, 0, stream>>>(R, tkeys_sorted, ranges);
         VEGS_LAUNCH_CHECK("tile_ranges", stream, debug);

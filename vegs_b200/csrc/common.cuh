@@ -161,6 +161,7 @@ static inline BinScratchView bin_scratch_view(void* base, int64_t R) {
 // ---------------------------------------------------------------- error handling (host)
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
+void prof_mark(const char* name, cudaStream_t stream);
 
 #define VEGS_CUDA_OK(expr)                                                              \
     do {                                                                                \
@@ -177,6 +178,7 @@ void count_launch(int n = 1);
 #define VEGS_LAUNCH_CHECK(name, stream, debug)                                          \
     do {                                                                                \
         vegs::count_launch();                                                           \
+        vegs::prof_mark(name, stream);                                                  \
         cudaError_t _e = cudaGetLastError();                                            \
         if (_e == cudaSuccess && (debug)) _e = cudaStreamSynchronize(stream);           \
         if (_e != cudaSuccess) {                                                        \
