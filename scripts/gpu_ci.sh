@@ -26,6 +26,15 @@ for s in $stages; do
     bench)
       timeout 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?" | tee -a gpurun_out/summary.txt
       timeout 900 python bench.py --impl reference > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "bench_ref rc=$?" | tee -a gpurun_out/summary.txt ;;
+    ncu)
+      # launch list (cold-cache, serialised: compare shares) and one full capture of the top kernels;
+      # the same command must have exited 0 without ncu first
+      CMD="python bench.py --P 6000000 --views 2 --steps 1 --warmup 1 --no-cpu-baseline"
+      timeout 600 $CMD > gpurun_out/ncu_plain.log 2>&1 &&
+      timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
+      echo "ncu launches rc=$?" | tee -a gpurun_out/summary.txt
+      timeout 900 ncu --set full --clock-control none --import-source on -k regex:'composite_(fwd|bwd)_kernel' -s 2 -c 2 -o gpurun_out/prof_composite $CMD > gpurun_out/ncu_full.log 2>&1
+      echo "ncu full rc=$?" | tee -a gpurun_out/summary.txt ;;
   esac
 done
 cat gpurun_out/summary.txt
