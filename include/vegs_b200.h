@@ -180,6 +180,29 @@ int vegs_dist2(int32_t P, const float* points, float* out, void* workspace, size
                void* stream);
 
 /*
+ * distCUDA2 for callers that cannot allocate device memory.  It has no counterpart in the
+ * reference (whose knn allocates and frees temporaries on every call, simple_knn.cu:187-220).
+ *
+ * Meant for hosts where cudaMalloc / cudaFree are not an option: an application that gives this
+ * library a fixed memory budget and keeps all allocation to itself, or a latency-sensitive loop
+ * that cannot tolerate the device-wide serialisation those calls cause.  The caller passes only
+ * the input points and the output array; the scratch for the search structure is a
+ * VEGS_DIST2_NOALLOC_SCRATCH_BYTES array built into the library image, which every GPU that loads
+ * the library keeps resident until the process exits.  That is why the point count is limited:
+ * more than VEGS_DIST2_NOALLOC_MAX_POINTS points are refused with VEGS_ESIZE (use vegs_dist2).
+ *
+ * The first call on each device looks up the array's device address (a one-time set-up with that
+ * device current); make that first call before starting any stream capture.  No call allocates or
+ * frees memory.  All calls on a device share the one array, and it keeps whatever the previous
+ * call left in it; nothing in it needs to be zero on entry, but two calls whose kernels overlap on
+ * the GPU (different streams, or different host threads) race on it and give wrong results — run
+ * them one after another.
+ */
+#define VEGS_DIST2_NOALLOC_MAX_POINTS 131072
+#define VEGS_DIST2_NOALLOC_SCRATCH_BYTES (6u << 20)
+int vegs_dist2_noalloc(int32_t P, const float* points, float* out, void* stream);
+
+/*
  * Test / parity support: re-express the binning state in the reference's format
  * (cuda_rasterizer/rasterizer_impl.cu:70-111,116-138): point_list_keys[R] = (tile << 32) | depth
  * bits, point_list[R], ranges[T] (uint2), tiles_touched[P], depths[P], means2D[P,2].  Any output

@@ -71,6 +71,7 @@ SIGNATURES = {
     "vegs_dist2_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "vegs_dist2": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
                              C.c_void_p]),
+    "vegs_dist2_noalloc": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "vegs_export_state": (C.c_int, [C.POINTER(VegsForwardArgs), C.c_int32] + [C.c_void_p] * 10),
     "vegs_kernel_launch_count": (C.c_uint64, []),
     "vegs_profile_enable": (None, [C.c_int32]),

@@ -20,6 +20,7 @@
 // Roofline: latency / L2-gather bound; algorithmic HBM bytes 16 per point.
 #include <algorithm>
 #include <cfloat>
+#include <mutex>
 #include "common.cuh"
 
 namespace vegs {
@@ -281,4 +282,68 @@ extern "C" int vegs_dist2(int32_t P, const float* points, float* out, void* work
     knn3_kernel<<<div_up(n, 128), 128, 0, stream>>>(n, v.pts, v.box1, n1, v.box2, n2, v.box3, n3, out);
     VEGS_LAUNCH_CHECK("knn3", stream, false);
     return VEGS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// vegs_dist2_noalloc: distCUDA2 for callers that must not allocate device memory.
+//
+// Who this is for: code that runs where cudaMalloc / cudaFree are off limits — a host application
+// that hands this library a fixed memory budget and owns every allocation itself, or a real-time /
+// latency-sensitive loop where cudaMalloc and cudaFree are unacceptable because they serialise with
+// all work on the device.  Such a caller still passes its own input and output arrays; what it
+// cannot provide is the search structure's scratch memory, so that lives in the array below.
+//
+// The scratch is one file-scope __device__ array.  It is part of the library image: every GPU that
+// loads libvegs_b200.so holds these bytes from load until the process exits, whether or not this
+// entry point is ever called, which is why the size (and so the largest point count) is modest.
+// In host code the array's name is only a handle for the runtime, not an address the GPU can use;
+// the device address is looked up once per device with cudaGetSymbolAddress and then passed to the
+// kernels like any other workspace pointer.
+constexpr int32_t kNoAllocMaxPoints = VEGS_DIST2_NOALLOC_MAX_POINTS;
+constexpr size_t kNoAllocScratchBytes = 6u << 20;  // 6 MiB >= vegs_dist2_workspace_bytes(131072)
+static __device__ __align__(256) unsigned char g_dist2_noalloc_scratch[kNoAllocScratchBytes];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[kMaxDevices] = {nullptr};
+}  // namespace
+
+extern "C" int vegs_dist2_noalloc(int32_t P, const float* points, float* out, void* stream_) {
+    using namespace vegs;
+    if (P < 0 || (P > 0 && (!points || !out))) {
+        set_error("vegs_dist2_noalloc: bad argument");
+        return VEGS_EINVAL;
+    }
+    if (P > kNoAllocMaxPoints) {
+        set_error("vegs_dist2_noalloc: %d points exceed the built-in scratch (at most %d points); "
+                  "use vegs_dist2 with a caller-provided workspace", P, kNoAllocMaxPoints);
+        return VEGS_ESIZE;
+    }
+    if (P == 0) return VEGS_OK;
+    int dev = -1;
+    VEGS_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) {
+        set_error("vegs_dist2_noalloc: device ordinal %d not supported", dev);
+        return VEGS_EINVAL;
+    }
+    void* scratch = nullptr;
+    {
+        // Set-up, once per device, with that device current (it is: we just asked which one is).
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (g_noalloc_ptr[dev] == nullptr) {
+            void* p = nullptr;
+            VEGS_CUDA_OK(cudaGetSymbolAddress(&p, g_dist2_noalloc_scratch));
+            g_noalloc_ptr[dev] = p;
+        }
+        scratch = g_noalloc_ptr[dev];
+    }
+    if (vegs_dist2_workspace_bytes(P) > kNoAllocScratchBytes) {
+        set_error("vegs_dist2_noalloc: internal error, scratch array too small for %d points", P);
+        return VEGS_ESIZE;
+    }
+    // Nothing in the scratch has to start at zero: the first kernel re-initialises the bounding-box
+    // words and every other region is fully written before it is read, so the previous call's
+    // contents are harmless.  The existing entry point does the rest; it allocates nothing.
+    return vegs_dist2(P, points, out, scratch, kNoAllocScratchBytes, stream_);
 }
