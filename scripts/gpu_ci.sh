@@ -13,7 +13,7 @@ for s in $stages; do
     smoke)
       timeout 600 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" | tee -a gpurun_out/summary.txt ;;
     tests)
-      for grp in "dist2" "mark_visible or edge or debug" "against_oracle or modes or deterministic" "golden" "reference_live" "full_size"; do
+      for grp in "dist2 and not noalloc" "mark_visible or edge or debug" "against_oracle or modes or deterministic" "golden" "reference_live" "full_size" "noalloc"; do
         name=$(echo "$grp" | tr ' ' '_')
         timeout 900 python -m pytest tests -m gpu -q -k "$grp" -p no:cacheprovider > "gpurun_out/pytest_${name}.log" 2>&1
         echo "pytest[$grp] rc=$? $(tail -1 gpurun_out/pytest_${name}.log)" | tee -a gpurun_out/summary.txt
@@ -26,6 +26,8 @@ for s in $stages; do
     bench)
       timeout 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?" | tee -a gpurun_out/summary.txt
       timeout 900 python bench.py --impl reference > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "bench_ref rc=$?" | tee -a gpurun_out/summary.txt ;;
+    configs)
+      timeout 1200 python scripts/bench_configs.py > gpurun_out/configs.json 2> gpurun_out/configs.err; echo "configs rc=$?" | tee -a gpurun_out/summary.txt ;;
     ncu)
       # launch list (cold-cache, serialised: compare shares) and one full capture of the top kernels;
       # the same command must have exited 0 without ncu first

@@ -1,0 +1,110 @@
+"""CPU tests of the view-parallel step (vegs_b200/dist.py) with the gloo backend, world size 2:
+the all-reduced gradients and densification statistics of a sharded step equal those of the same
+views processed by one rank.  The rasterizer itself needs a GPU, so a stand-in per-view function
+with the same signature of results (gradients per Gaussian, radii, screen-space gradient) is used:
+what is under test is the sharding, packing and reduction logic."""
+import os
+import socket
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from vegs_b200 import dist as vdist
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _make_params(P, M=4, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    shapes = dict(means3D=(P, 3), shs=(P, M, 3), opacities=(P, 1), scales=(P, 3), rotations=(P, 4))
+    return {k: torch.randn(*s, generator=g).requires_grad_(True) for k, s in shapes.items()}
+
+
+def _fake_view(params, v):
+    """Deterministic stand-in for one view's forward+backward: a loss that touches every parameter,
+    a radii vector with culled entries, and a screen-space gradient."""
+    P = params["means3D"].shape[0]
+    g = torch.Generator().manual_seed(100 + v)
+    w = {k: torch.randn(*t.shape, generator=g) for k, t in params.items()}
+    loss = sum((params[k] * w[k]).sum() * (v + 1) for k in params)
+    loss.backward()
+    radii = torch.randint(0, 5, (P,), generator=g, dtype=torch.int32)
+    view_grad = torch.randn(P, 3, generator=g)
+    return radii, view_grad
+
+
+def _run_views(params, views):
+    stats = vdist.DensificationStats(params["means3D"].shape[0], "cpu")
+    for t in params.values():
+        t.grad = None
+    for v in views:
+        radii, vg = _fake_view(params, v)
+        stats.add_view(vg, radii)
+    return stats
+
+
+def _worker(rank, world, port, P, n_views, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    params = _make_params(P)
+    stats = _run_views(params, vdist.shard_views(n_views, rank, world))
+    flat = vdist.allreduce_step(params, stats)
+    assert flat.numel() == vdist.flat_size(params)
+    if rank == 0:
+        torch.save(dict(grads={k: v.grad.clone() for k, v in params.items()},
+                        accum=stats.xyz_gradient_accum.clone(), denom=stats.denom.clone(),
+                        maxr=stats.max_radii2D.clone()), out)
+    dist.destroy_process_group()
+
+
+def test_shard_views_round_robin():
+    assert vdist.shard_views(8, 0, 1) == list(range(8))
+    assert vdist.shard_views(8, 1, 2) == [1, 3, 5, 7]
+    assert vdist.shard_views(8, 3, 8) == [3]
+    assert sorted(sum((vdist.shard_views(8, r, 4) for r in range(4)), [])) == list(range(8))
+
+
+def test_densification_stats_follow_reference():
+    """train.py:300-301 and scene/gaussian_model.py:411-413."""
+    st = vdist.DensificationStats(4, "cpu")
+    radii = torch.tensor([0, 3, 7, 0], dtype=torch.int32)
+    vg = torch.tensor([[3.0, 4.0, 9.0], [6.0, 8.0, 9.0], [0.0, 1.0, 9.0], [1.0, 1.0, 1.0]])
+    st.add_view(vg, radii)
+    st.add_view(vg, torch.tensor([2, 1, 0, 0], dtype=torch.int32))
+    assert st.max_radii2D.tolist() == [2.0, 3.0, 7.0, 0.0]
+    assert st.denom.view(-1).tolist() == [1.0, 2.0, 1.0, 0.0]
+    assert torch.allclose(st.xyz_gradient_accum.view(-1), torch.tensor([5.0, 20.0, 1.0, 0.0]))
+
+
+def test_pack_unpack_roundtrip():
+    params = _make_params(50)
+    stats = _run_views(params, [0, 1])
+    ref = {k: v.grad.clone() for k, v in params.items()}
+    accum, denom = stats.xyz_gradient_accum.clone(), stats.denom.clone()
+    flat = vdist.pack(params, stats)
+    assert flat.numel() == 50 * (3 + 12 + 1 + 3 + 4 + 2)
+    vdist.unpack(flat, params, stats)
+    for k in params:
+        assert torch.equal(params[k].grad, ref[k])
+    assert torch.equal(stats.xyz_gradient_accum, accum) and torch.equal(stats.denom, denom)
+
+
+def test_two_rank_step_equals_single_rank(tmp_path):
+    P, n_views = 200, 8
+    out = str(tmp_path / "r0.pt")
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, P, n_views, out), nprocs=2, join=True)
+    got = torch.load(out)
+    params = _make_params(P)
+    stats = _run_views(params, list(range(n_views)))
+    for k in params:
+        assert torch.allclose(got["grads"][k], params[k].grad, rtol=1e-5, atol=1e-5), k
+    assert torch.allclose(got["accum"], stats.xyz_gradient_accum, rtol=1e-6, atol=1e-6)
+    assert torch.equal(got["denom"], stats.denom)
+    assert torch.equal(got["maxr"], stats.max_radii2D)

@@ -211,7 +211,7 @@ extern "C" int vegs_forward_render(const VegsForwardArgs* a, int32_t num_rendere
         if (rc) return rc;
         sorted_keys = second ? k1 : k0;
     }
-    rc = launch_tile_ranges(R, sorted_keys, im.ranges, T, stream, debug);
+    rc = launch_tile_ranges(R, sorted_keys, im.ranges, im.tile_order, T, stream, debug);
     if (rc) return rc;
     return launch_composite_fwd(*a, g, s, im, b, stream);
 }

@@ -193,6 +193,35 @@ tile_ranges_kernel(uint32_t R, const uint32_t* __restrict__ tkeys, uint2* __rest
     if (i == R - 1) ranges[cur].y = R;
 }
 
+// Tiles ordered by list length, longest first (33 log2 buckets, order inside a bucket arbitrary).
+// The compositing kernels take their tile from this table so the few very long lists of a
+// LiDAR-density scene start first instead of becoming the tail of the launch.
+__global__ void __launch_bounds__(1024)
+tile_order_kernel(const uint2* __restrict__ ranges, uint32_t T, uint32_t* __restrict__ order) {
+    __shared__ uint32_t s_cnt[33];
+    __shared__ uint32_t s_cur[33];
+    if (threadIdx.x < 33) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    for (uint32_t t = threadIdx.x; t < T; t += 1024) {
+        const uint2 r = ranges[t];
+        const uint32_t len = r.y - r.x;
+        const uint32_t key = len ? (uint32_t)__clz(len) : 32u;   // small key = long list
+        atomicAdd(&s_cnt[key], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t run = 0;
+        for (int k = 0; k < 33; k++) { s_cur[k] = run; run += s_cnt[k]; }
+    }
+    __syncthreads();
+    for (uint32_t t = threadIdx.x; t < T; t += 1024) {
+        const uint2 r = ranges[t];
+        const uint32_t len = r.y - r.x;
+        const uint32_t key = len ? (uint32_t)__clz(len) : 32u;
+        order[atomicAdd(&s_cur[key], 1u)] = t;
+    }
+}
+
 }  // namespace
 
 int launch_tile_count(int P, const uint32_t* order, const uint2* rect, uint32_t* chunksum,
@@ -215,14 +244,16 @@ int launch_emit(int P, const uint32_t* order, const uint2* rect, const uint32_t*
     return VEGS_OK;
 }
 
-int launch_tile_ranges(uint32_t R, const uint32_t* tkeys_sorted, uint2* ranges, int T,
-                       cudaStream_t stream, bool debug) {
+int launch_tile_ranges(uint32_t R, const uint32_t* tkeys_sorted, uint2* ranges,
+                       uint32_t* tile_order, int T, cudaStream_t stream, bool debug) {
     VEGS_CUDA_OK(cudaMemsetAsync(ranges, 0, (size_t)T * sizeof(uint2), stream));
     prof_mark("memset_ranges", stream);
     if (R > 0) {
         tile_ranges_kernel<<<div_up(R, 256), 256, 0, stream>>>(R, tkeys_sorted, ranges);
         VEGS_LAUNCH_CHECK("tile_ranges", stream, debug);
     }
+    tile_order_kernel<<<1, 1024, 0, stream>>>(ranges, (uint32_t)T, tile_order);
+    VEGS_LAUNCH_CHECK("tile_order", stream, debug);
     return VEGS_OK;
 }
 

@@ -11,13 +11,14 @@
 //                                hist, rowtot, chunk sums
 //   img     (kept for backward)  n_contrib      : uint32[W*H]
 //                                ranges         : uint2[T]
+//                                tile_order     : uint32[T]   tiles, longest list first
 //   binning (kept for backward)  point_list     : uint32[R]
 //   bin_scratch (forward only)   tile keys ping-pong, value ping, hist
 //
 // Record contents (only written for Gaussians with radii > 0):
 //   recA = { mean2D.x, mean2D.y, conic.a, conic.b }
-//   recB = { conic.c, opacity, depth(view z), rgb.r }
-//   recC = { rgb.g, rgb.b, sin(theta), unused }            theta = acos(rot.r)
+//   recB = { conic.c, opacity, tau, depth(view z) }        tau = log(255*opacity) + 0.01
+//   recC = { rgb.r, rgb.g, rgb.b, sin(theta) }             theta = acos(rot.r)
 //   recD = { scale.x, scale.y, scale.z, rot.r }            raw kernel inputs (no modifier)
 //   recE = { rot.x, rot.y, rot.z, theta }
 #pragma once
@@ -70,6 +71,7 @@ struct ScratchView {
 struct ImgView {
     uint32_t* n_contrib;
     uint2* ranges;
+    uint32_t* tile_order;
     size_t bytes;
 };
 
@@ -132,6 +134,7 @@ static inline ImgView img_view(void* base, int W, int H) {
     size_t T = (size_t)((W + kTile - 1) / kTile) * ((H + kTile - 1) / kTile);
     v.n_contrib = carve<uint32_t>(cur, npix ? npix : 1);
     v.ranges = carve<uint2>(cur, T ? T : 1);
+    v.tile_order = carve<uint32_t>(cur, T ? T : 1);
     v.bytes = (size_t)(cur - reinterpret_cast<char*>(base));
     return v;
 }
@@ -214,8 +217,8 @@ int launch_tile_count(int P, const uint32_t* order, const uint2* rect, uint32_t*
 int launch_emit(int P, const uint32_t* order, const uint2* rect, const uint32_t* chunksum,
                 int grid_x, uint32_t* tkeys, uint32_t* tvals, uint32_t R, cudaStream_t stream,
                 bool debug);
-int launch_tile_ranges(uint32_t R, const uint32_t* tkeys_sorted, uint2* ranges, int T,
-                       cudaStream_t stream, bool debug);
+int launch_tile_ranges(uint32_t R, const uint32_t* tkeys_sorted, uint2* ranges,
+                       uint32_t* tile_order, int T, cudaStream_t stream, bool debug);
 
 // composite_fwd.cu
 int launch_composite_fwd(const VegsForwardArgs& a, const GeomView& g, const ScratchView& s,

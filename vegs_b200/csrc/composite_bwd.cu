@@ -12,7 +12,10 @@
 //   * the traversal starts at the tile's deepest contributor (max of n_contrib over the tile)
 //     instead of at the end of the tile's list: entries behind it are skipped by every pixel in
 //     the reference too (backward.cu:561-563), it just fetches them first;
-//   * records are staged with double-buffered cp.async like the forward;
+//   * records are staged with double-buffered cp.async like the forward, each warp owns an 8x4
+//     pixel block and visits only the entries whose alpha >= 1/255 region overlaps it (same
+//     conservative mask as the forward, composite_common.cuh), exp() is skipped below the
+//     threshold, and tiles are taken longest-list-first;
 //   * the quaternion / scale-map cotangents are not propagated: the reference accumulates them
 //     into buffers that its next kernel overwrites (backward.cu:624-647 vs :322-325,:340-341), so
 //     its returned gradients do not contain them.
@@ -20,17 +23,11 @@
 //   [0..1] dL/dmean2D.xy  [2..4] dL/dconic (xx, xy, yy)  [5] dL/dopacity  [6..8] dL/drgb
 //   [9] dL/ddepth  [10..11] unused
 #include "common.cuh"
+#include "composite_common.cuh"
 
 namespace vegs {
 
 namespace {
-
-__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
-    const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem_src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 __device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b),
@@ -49,7 +46,8 @@ constexpr int kAccStride = 11;  // 10 values + "touched" flag; odd stride -> con
 struct BwdParams {
     const uint2* ranges;
     const uint32_t* point_list;
-    int W, H;
+    const uint32_t* tile_order;
+    int W, H, gx;
     const float4 *recA, *recB, *recC;
     const float* bg;
     const float* out_alpha;
@@ -65,11 +63,14 @@ __global__ void __launch_bounds__(kTilePix) composite_bwd_kernel(const BwdParams
     __shared__ int sId[2][kTilePix];
     __shared__ float sAcc[kTilePix * kAccStride];
     __shared__ uint32_t sMax[kTilePix / 32];
+    __shared__ uint32_t sMask[kTilePix];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
-    const int px = blockIdx.x * kTile + (tid & (kTile - 1));
-    const int py = blockIdx.y * kTile + (tid >> 4);
+    const uint32_t tile = p.tile_order[blockIdx.x];
+    const int tile_x = (int)(tile % (uint32_t)p.gx), tile_y = (int)(tile / (uint32_t)p.gx);
+    const int X0 = tile_x * kTile, Y0 = tile_y * kTile;
+    const int px = X0 + (warp & 1) * 8 + (lane & 7);
+    const int py = Y0 + (warp >> 1) * 4 + (lane >> 3);
     const bool inside = px < p.W && py < p.H;
     const float pixfx = (float)px, pixfy = (float)py;
     const size_t npix = (size_t)p.W * p.H;
@@ -143,16 +144,23 @@ __global__ void __launch_bounds__(kTilePix) composite_bwd_kernel(const BwdParams
         }
         const int st = b & 1;
         const int cnt = min(kTilePix, n - b * kTilePix);
-        for (int j = 0; j < cnt; j++) {
+        sMask[tid] = (tid < cnt) ? block_mask(sA[st][tid], sB[st][tid], X0, Y0) : 0u;
+        __syncthreads();
+        for (int c0 = 0; c0 < cnt; c0 += 32) {
+          uint32_t bits = __ballot_sync(0xffffffffu, (sMask[c0 + lane] >> warp) & 1u);
+          while (bits) {
+            const int j = c0 + __ffs(bits) - 1;
+            bits &= bits - 1;
             const uint32_t e = (uint32_t)entry_of(b, j);
             bool active = inside && (e < last_contributor);
             const float4 a = sA[st][j];   // x, y, conic.a, conic.b
-            const float4 bb = sB[st][j];  // conic.c, opacity, depth, r
+            const float4 bb = sB[st][j];  // conic.c, opacity, tau, depth
             const float dx = __fsub_rn(a.x, pixfx);
             const float dy = __fsub_rn(a.y, pixfy);
             const float sum = __fmaf_rn(__fmul_rn(a.z, dx), dx, __fmul_rn(__fmul_rn(bb.x, dy), dy));
             const float power = __fmaf_rn(sum, -0.5f, -__fmul_rn(__fmul_rn(a.w, dx), dy));
             if (power > 0.0f) active = false;
+            if (power < -bb.z) active = false;   // alpha < 1/255 with margin
             float G = 0.f, alpha = 0.f;
             if (active) {
                 G = expf(power);
@@ -164,22 +172,22 @@ __global__ void __launch_bounds__(kTilePix) composite_bwd_kernel(const BwdParams
             float g_mx = 0.f, g_my = 0.f, g_cxx = 0.f, g_cxy = 0.f, g_cyy = 0.f, g_op = 0.f;
             float g_c0 = 0.f, g_c1 = 0.f, g_c2 = 0.f, g_dep = 0.f;
             if (active) {
-                const float4 c = sC[st][j];  // g, b, -, -
+                const float4 c = sC[st][j];  // r, g, b, -
                 T = T / (1.0f - alpha);
                 const float w = alpha * T;
                 float dL_dalpha = 0.0f;
                 accum_rec0 = last_alpha * last_c0 + (1.f - last_alpha) * accum_rec0;
                 accum_rec1 = last_alpha * last_c1 + (1.f - last_alpha) * accum_rec1;
                 accum_rec2 = last_alpha * last_c2 + (1.f - last_alpha) * accum_rec2;
-                last_c0 = bb.w; last_c1 = c.x; last_c2 = c.y;
-                dL_dalpha += (bb.w - accum_rec0) * dpix0;
-                dL_dalpha += (c.x - accum_rec1) * dpix1;
-                dL_dalpha += (c.y - accum_rec2) * dpix2;
+                last_c0 = c.x; last_c1 = c.y; last_c2 = c.z;
+                dL_dalpha += (c.x - accum_rec0) * dpix0;
+                dL_dalpha += (c.y - accum_rec1) * dpix1;
+                dL_dalpha += (c.z - accum_rec2) * dpix2;
                 g_c0 = w * dpix0; g_c1 = w * dpix1; g_c2 = w * dpix2;
 
                 accum_red = last_alpha * last_depth + (1.f - last_alpha) * accum_red;
-                last_depth = bb.z;
-                dL_dalpha += (bb.z - accum_red) * dpix_depth;
+                last_depth = bb.w;
+                dL_dalpha += (bb.w - accum_red) * dpix_depth;
                 g_dep = w * dpix_depth;
 
                 accum_rea = last_alpha + (1.f - last_alpha) * accum_rea;
@@ -215,6 +223,7 @@ __global__ void __launch_bounds__(kTilePix) composite_bwd_kernel(const BwdParams
                 atomicAdd(s + 9, g_dep);
                 s[10] = 1.0f;
             }
+          }
         }
         __syncthreads();  // all warps' shared-memory accumulation for this batch is complete
         if (tid < cnt) {
@@ -239,15 +248,17 @@ int launch_composite_bwd(const VegsBackwardArgs& a, const GeomView& g, const Img
     BwdParams p;
     p.ranges = im.ranges;
     p.point_list = b.point_list;
+    p.tile_order = im.tile_order;
     p.W = a.W; p.H = a.H;
+    p.gx = (a.W + kTile - 1) / kTile;
     p.recA = g.recA; p.recB = g.recB; p.recC = g.recC;
     p.bg = a.background;
     p.out_alpha = a.out_alpha;
     p.n_contrib = im.n_contrib;
     p.dL_dcolor = a.dL_dout_color; p.dL_ddepth = a.dL_dout_depth; p.dL_dalpha = a.dL_dout_alpha;
     p.acc = acc;
-    const dim3 grid((a.W + kTile - 1) / kTile, (a.H + kTile - 1) / kTile, 1);
-    composite_bwd_kernel<<<grid, kTilePix, 0, stream>>>(p);
+    const int T = p.gx * ((a.H + kTile - 1) / kTile);
+    composite_bwd_kernel<<<T, kTilePix, 0, stream>>>(p);
     VEGS_LAUNCH_CHECK("composite_bwd", stream, a.debug);
     return VEGS_OK;
 }

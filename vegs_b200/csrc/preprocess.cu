@@ -250,9 +250,12 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_fwd_kernel(const PrePa
         }
         const float theta = acosf(d4.w);
         e4.w = theta;
+        // tau: a pixel can only reach alpha >= 1/255 where power >= -tau (margin 0.01 covers the
+        // rounding of exp and of the product); used to skip exp() and to cull per pixel block
+        const float tau = logf(255.0f * opacity) + 0.01f;
         p.recA[idx] = make_float4(pix_x, pix_y, conic.x, conic.y);
-        p.recB[idx] = make_float4(conic.z, opacity, depth, rgb.x);
-        p.recC[idx] = make_float4(rgb.y, rgb.z, sinf(theta), 0.0f);
+        p.recB[idx] = make_float4(conic.z, opacity, tau, depth);
+        p.recC[idx] = make_float4(rgb.x, rgb.y, rgb.z, sinf(theta));
         p.recD[idx] = d4;
         p.recE[idx] = e4;
         p.clamped[idx] = (uint8_t)clampbits;
