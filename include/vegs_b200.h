@@ -213,6 +213,14 @@ int vegs_export_state(const VegsForwardArgs* args, int32_t num_rendered, uint64_
                       float* depths, float* means2D, float* conic_opacity, float* rgb,
                       uint32_t* n_contrib, void* stream);
 
+/*
+ * Diagnostics: SM cycles / 1024 each tile's CTA spent in the forward / backward compositing
+ * kernel of the last call that used `img` (device arrays of T = ceil(W/16)*ceil(H/16) words).
+ * `dbg` receives 8 extra counters per tile that are only filled by a -DVEGS_TILE_DEBUG=1 build.
+ */
+int vegs_export_tile_clocks(const void* img, int32_t W, int32_t H, uint32_t* fwd, uint32_t* bwd,
+                            uint32_t* dbg /* [8*T], debug builds only, may be NULL */, void* stream);
+
 /* Number of kernels launched by this library in this process so far (bench bookkeeping). */
 uint64_t vegs_kernel_launch_count(void);
 

@@ -32,7 +32,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC",
-]
+] + (["-DVEGS_TILE_DEBUG=1"] if os.environ.get("VEGS_TILE_DEBUG") == "1" else [])
 
 
 def _nvcc() -> str:

@@ -286,3 +286,15 @@ extern "C" int vegs_export_state(const VegsForwardArgs* a, int32_t num_rendered,
                          ranges, tiles_touched, depths, means2D, conic_opacity, rgb, n_contrib,
                          stream);
 }
+
+extern "C" int vegs_export_tile_clocks(const void* img, int32_t W, int32_t H, uint32_t* fwd, uint32_t* bwd,
+                                       uint32_t* dbg, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    if (!img || W <= 0 || H <= 0) { set_error("vegs_export_tile_clocks: bad argument"); return VEGS_EINVAL; }
+    const ImgView im = img_view(aligned(img), W, H);
+    const size_t T = (size_t)((W + kTile - 1) / kTile) * ((H + kTile - 1) / kTile);
+    if (fwd) VEGS_CUDA_OK(cudaMemcpyAsync(fwd, im.tile_clocks, T * 4, cudaMemcpyDeviceToDevice, stream));
+    if (bwd) VEGS_CUDA_OK(cudaMemcpyAsync(bwd, im.tile_clocks + T, T * 4, cudaMemcpyDeviceToDevice, stream));
+    if (dbg) VEGS_CUDA_OK(cudaMemcpyAsync(dbg, im.tile_dbg, T * 32, cudaMemcpyDeviceToDevice, stream));
+    return VEGS_OK;
+}

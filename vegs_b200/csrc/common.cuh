@@ -17,7 +17,8 @@
 //
 // Record contents (only written for Gaussians with radii > 0):
 //   recA = { mean2D.x, mean2D.y, conic.a, conic.b }
-//   recB = { conic.c, opacity, tau, depth(view z) }        tau = log(255*opacity) + 0.01
+//   recB = { conic.c, opacity, half2(ex, ey), depth(view z) }   ex, ey: half extents of the box
+//                                                           outside which alpha < 1/255 (preprocess.cu)
 //   recC = { rgb.r, rgb.g, rgb.b, sin(theta) }             theta = acos(rot.r)
 //   recD = { scale.x, scale.y, scale.z, rot.r }            raw kernel inputs (no modifier)
 //   recE = { rot.x, rot.y, rot.z, theta }
@@ -72,6 +73,8 @@ struct ImgView {
     uint32_t* n_contrib;
     uint2* ranges;
     uint32_t* tile_order;
+    uint32_t* tile_clocks;   // [2*T] SM cycles/1024 spent on each tile by composite fwd / bwd (diagnostics)
+    uint32_t* tile_dbg;      // [8*T] extra counters, only written when built with -DVEGS_TILE_DEBUG=1
     size_t bytes;
 };
 
@@ -135,6 +138,8 @@ static inline ImgView img_view(void* base, int W, int H) {
     v.n_contrib = carve<uint32_t>(cur, npix ? npix : 1);
     v.ranges = carve<uint2>(cur, T ? T : 1);
     v.tile_order = carve<uint32_t>(cur, T ? T : 1);
+    v.tile_clocks = carve<uint32_t>(cur, 2 * (T ? T : 1));
+    v.tile_dbg = carve<uint32_t>(cur, 8 * (T ? T : 1));
     v.bytes = (size_t)(cur - reinterpret_cast<char*>(base));
     return v;
 }

@@ -1,52 +1,83 @@
 // Helpers shared by the forward and backward compositing kernels.
+//
+// Work decomposition of both kernels: the unit of work is one WARP = one 8x4 pixel block of a
+// 16x16 tile (8 blocks per tile).  A unit walks its tile's depth-sorted instance list in batches of
+// 32 entries and is independent of the other units, so there is no block-level barrier, heavy
+// tiles spread over 8 warps on up to 8 SMs, and units are issued longest-list-first.
+//
+// Per batch the warp alternates between two views of the same 32 x 32 problem:
+//   entry-parallel   lane t owns entry t: it loads the packed records, clips the Gaussian's
+//                    conservative box (half extents from the preprocess stage) to the block and
+//                    evaluates the reference's exact contribution test on the few pixels inside,
+//                    giving a 32-bit hit mask over the block's pixels;
+//   pixel-parallel   after a 32x32 bit transpose through shuffles, lane p owns pixel p and visits
+//                    only its own hits, in list order, with the reference's sequential arithmetic.
+// At LiDAR density a Gaussian touches a handful of the tile's 256 pixels, so this replaces
+// "32 lanes evaluate every entry" by "each entry is evaluated only where it can matter".
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 namespace vegs {
 
-__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
-    const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem_src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+constexpr int kUnitW = 8, kUnitH = 4;          // pixel block of one warp
+constexpr int kUnitsPerTile = 8;
 
-// Which of the tile's eight 8x4 pixel blocks (bit = by*2 + bx, block origin (X0 + 8bx, Y0 + 4by))
-// can contain a pixel where this Gaussian reaches alpha >= 1/255.
-//
-// a = {x, y, conic.a, conic.b}, b = {conic.c, opacity, tau, depth}.  alpha >= 1/255 needs
-// power >= -tau, i.e. A dx^2 + 2 B dx dy + C dy^2 <= 2 tau, an ellipse whose half extents are
-// sqrt(2 tau C / det) in x and sqrt(2 tau A / det) in y (det = AC - B^2).  tau already carries a
-// margin; the extents get another one, so the box is conservative and skipping the other blocks
-// cannot change a result.  Whenever the box cannot be trusted (non-finite inputs, for which the
-// reference's fminf(0.99, NaN) = 0.99 makes EVERY pixel contribute, or a conic that is not
-// positive definite) all eight blocks are kept.
-__device__ __forceinline__ uint32_t block_mask(const float4 a, const float4 b, int X0, int Y0) {
-    const float tau = b.z;
-    const bool finite = isfinite(a.x) && isfinite(a.y) && isfinite(a.z) && isfinite(a.w) &&
-                        isfinite(b.x) && isfinite(tau);
-    if (!finite) return 0xffu;
-    if (tau < 0.0f) return 0u;
-    const float det = a.z * b.x - a.w * a.w;
-    if (!(det > 0.0f)) return 0xffu;
-    const float s2 = 2.0f * tau / det;
-    const float ex = sqrtf(s2 * b.x) * 1.0001f + 0.01f;
-    const float ey = sqrtf(s2 * a.z) * 1.0001f + 0.01f;
-    if (!isfinite(ex) || !isfinite(ey)) return 0xffu;
-    const float x_lo = a.x - ex, x_hi = a.x + ex, y_lo = a.y - ey, y_hi = a.y + ey;
-    uint32_t mx = 0, m = 0;
+// 32x32 bit-matrix transpose across the warp: bit t of the result in lane p = bit p of v in lane t.
+__device__ __forceinline__ uint32_t transpose32(uint32_t v, int lane) {
 #pragma unroll
-    for (int bx = 0; bx < 2; bx++) {
-        const float lo = (float)(X0 + 8 * bx), hi = lo + 7.0f;
-        if (x_hi >= lo && x_lo <= hi) mx |= 1u << bx;
+    for (int s = 16; s >= 1; s >>= 1) {
+        const uint32_t m = (s == 16) ? 0x0000ffffu : (s == 8) ? 0x00ff00ffu : (s == 4) ? 0x0f0f0f0fu
+                         : (s == 2) ? 0x33333333u : 0x55555555u;
+        const uint32_t o = __shfl_xor_sync(0xffffffffu, v, s);
+        v = (lane & s) ? ((v & ~m) | ((o & ~m) >> s)) : ((v & m) | ((o & m) << s));
     }
-#pragma unroll
-    for (int by = 0; by < 4; by++) {
-        const float lo = (float)(Y0 + 4 * by), hi = lo + 3.0f;
-        if (y_hi >= lo && y_lo <= hi) m |= mx << (2 * by);
-    }
-    return m;
+    return v;
 }
+
+// Hit mask of one entry over the block's 32 pixels (bit = (y - by0) * 8 + (x - bx0)).
+// a = {x, y, conic.a, conic.b}, b = {conic.c, opacity, half2(ex, ey), depth}.
+// The test is the reference's (cuda_rasterizer/forward.cu:371-381): power <= 0 and
+// min(0.99, opacity * exp(power)) >= 1/255, in its float operation order (power as
+// fma(fma(A*dx, dx, (C*dy)*dy), -0.5, -((B*dx)*dy)), read from the reference's SASS).
+// Pixels outside the precomputed box cannot pass it, so they are not evaluated.
+__device__ __forceinline__ uint32_t entry_hits(const float4 a, const float4 b, int bx0, int by0,
+                                               int bx1, int by1) {
+    const uint32_t packed = __float_as_uint(b.z);
+    const float2 e = __half22float2(*reinterpret_cast<const __half2*>(&packed));
+    // clip the box to the block (bx0..bx1, by0..by1 inclusive, already clipped to the image);
+    // +inf extents keep the whole block, negative extents give an empty range
+    const int x0 = (int)ceilf(fmaxf(a.x - e.x, (float)bx0));
+    const int x1 = (int)floorf(fminf(a.x + e.x, (float)bx1));
+    const int y0 = (int)ceilf(fmaxf(a.y - e.y, (float)by0));
+    const int y1 = (int)floorf(fminf(a.y + e.y, (float)by1));
+    uint32_t hits = 0;
+    for (int y = y0; y <= y1; y++) {
+        const float dy = __fsub_rn(a.y, (float)y);
+        const float cyy = __fmul_rn(__fmul_rn(b.x, dy), dy);
+        for (int x = x0; x <= x1; x++) {
+            const float dx = __fsub_rn(a.x, (float)x);
+            const float sum = __fmaf_rn(__fmul_rn(a.z, dx), dx, cyy);
+            const float power = __fmaf_rn(sum, -0.5f, -__fmul_rn(__fmul_rn(a.w, dx), dy));
+            if (power > 0.0f) continue;
+            const float alpha = fminf(0.99f, __fmul_rn(b.y, expf(power)));
+            if (alpha < 1.0f / 255.0f) continue;
+            hits |= 1u << ((y - by0) * kUnitW + (x - bx0));
+        }
+    }
+    return hits;
+}
+
+// power and alpha of one (pixel, entry) pair that is known to be a hit (same arithmetic as above)
+__device__ __forceinline__ float pair_power(const float4 a, const float4 b, float pixfx, float pixfy,
+                                            float& dx, float& dy) {
+    dx = __fsub_rn(a.x, pixfx);
+    dy = __fsub_rn(a.y, pixfy);
+    const float sum = __fmaf_rn(__fmul_rn(a.z, dx), dx, __fmul_rn(__fmul_rn(b.x, dy), dy));
+    return __fmaf_rn(sum, -0.5f, -__fmul_rn(__fmul_rn(a.w, dx), dy));
+}
+
+__device__ __forceinline__ float4 ldg_f4(const float4* p) { return __ldg(p); }
 
 }  // namespace vegs

@@ -1,29 +1,30 @@
-// Front-to-back alpha compositing, one 16x16 tile per CTA, one pixel per thread.
+// Front-to-back alpha compositing.  One warp per 8x4 pixel block ("unit"), 8 units per 16x16 tile.
 //
 // Replaces FORWARD::render / renderCUDA (reference cuda_rasterizer/forward.cu:262-441), including
 // the VEGS additions: depth map, alpha map, accumulated covariance quaternion map (sequential
 // slerp product, glm::mix — third_party/glm/glm/ext/quaternion_common.inl:4-26) and scale map.
 //
-// What differs from the reference's kernel:
-//   * the tile's Gaussians are staged in shared memory with asynchronous 16-byte copies
-//     (cp.async, SASS LDGSTS) of packed records, double buffered: batch b+1 is in flight while
-//     batch b is composited, and the index run for batch b+2 is already loaded;
-//   * colour and depth travel in the staged records instead of being re-read from global memory
-//     inside the per-pixel loop (forward.cu:391-392);
+// What differs from the reference's kernel (one 256-thread block per tile, every thread evaluates
+// every list entry, __syncthreads per 256 entries):
+//   * entry-parallel hit detection, pixel-parallel blending (composite_common.cuh): per batch of
+//     32 list entries each lane tests ITS entry against the few block pixels inside the entry's
+//     conservative box, a warp bit-transpose turns the 32 hit masks into per-pixel hit lists, and
+//     each pixel lane then runs the reference's sequential arithmetic over its own hits only;
+//   * no block-level synchronisation: units are independent warps, so the very long lists of a
+//     LiDAR-density scene (several 1e5 entries in the horizon tiles) are shared by 8 warps that can
+//     run on 8 SMs, units are issued longest-list-first, and a unit stops as soon as ITS 32 pixels
+//     are saturated;
+//   * colour, depth, scale and rotation travel in packed 16-byte records (no per-contribution
+//     re-reads of several arrays, forward.cu:391-392); records of the next batch are loaded while
+//     the current one is processed;
 //   * acos(q.r) and sin(acos(q.r)) of the slerp are per-Gaussian constants from the preprocess
-//     stage instead of being recomputed per (pixel, Gaussian);
-//   * per-block culling: each warp owns an 8x4 pixel block.  For every staged entry one thread
-//     computes the bounding box of the region where alpha can reach 1/255
-//     (power >= -tau, tau = log(255*opacity) + margin) and an 8-bit mask of the pixel blocks it
-//     overlaps; a warp then visits only its own entries (ballot + find-first-set keeps their
-//     order).  At LiDAR density a Gaussian covers a few pixels, so a warp skips most of the list;
-//     the decisions of the entries it does visit are the reference's, so results are unchanged;
-//   * exp() is skipped when power < -tau (alpha would be below 1/255 with margin);
-//   * tiles are taken from a longest-list-first table so the few very long lists start first.
-// The per-pixel arithmetic that decides which Gaussians contribute (power, alpha, test_T) uses the
-// reference's exact float operation order so n_contrib matches bit for bit.
-// Roofline: not HBM-bound (gathers 80 B per fetched instance, writes 52 B per pixel); the bound is
-// the issue rate / latency of the per-(pixel, Gaussian) loop and MUFU for exp / sin.
+//     stage instead of being recomputed per (pixel, Gaussian).
+// Every decision (power > 0, alpha >= 1/255, T(1-alpha) < 1e-4) is evaluated with the reference's
+// float operation order on exactly the (pixel, Gaussian) pairs where the reference evaluates it
+// to "contribute", so n_contrib and all outputs match.
+// Roofline: not HBM-bound (32 B per list entry per unit from L2, 48 B more per entry with a hit,
+// 52 B written per pixel); the bound is instruction issue of the per-hit blend (slerp: 2 sin,
+// 4 div, quaternion product) and of the box tests.
 #include <cfloat>
 #include "common.cuh"
 #include "composite_common.cuh"
@@ -41,29 +42,32 @@ struct FwdParams {
     const float* bg;
     float *out_color, *out_depth, *out_quat, *out_scale, *out_alpha;
     uint32_t* n_contrib;
+    uint32_t* tile_clocks;
 };
 
-__global__ void __launch_bounds__(kTilePix) composite_fwd_kernel(const FwdParams p) {
-    __shared__ __align__(16) float4 sA[2][kTilePix];
-    __shared__ __align__(16) float4 sB[2][kTilePix];
-    __shared__ __align__(16) float4 sC[2][kTilePix];
-    __shared__ __align__(16) float4 sD[2][kTilePix];
-    __shared__ __align__(16) float4 sE[2][kTilePix];
-    __shared__ uint32_t sMask[kTilePix];
+__global__ void __launch_bounds__(32) composite_fwd_kernel(const FwdParams p) {
+    __shared__ __align__(16) float4 sA[32];
+    __shared__ __align__(16) float4 sB[32];
+    __shared__ __align__(16) float4 sC[32];
+    __shared__ __align__(16) float4 sD[32];
+    __shared__ __align__(16) float4 sE[32];
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t tile = p.tile_order[blockIdx.x];
+    const long long t_start = clock64();
+    const int lane = threadIdx.x;
+    const uint32_t unit = blockIdx.x;
+    const uint32_t tile = p.tile_order[unit >> 3];
+    const int blk = (int)(unit & 7u);
     const int tile_x = (int)(tile % (uint32_t)p.gx), tile_y = (int)(tile / (uint32_t)p.gx);
-    const int X0 = tile_x * kTile, Y0 = tile_y * kTile;
-    // warp w owns the 8x4 pixel block (w & 1, w >> 1)
-    const int px = X0 + (warp & 1) * 8 + (lane & 7);
-    const int py = Y0 + (warp >> 1) * 4 + (lane >> 3);
+    const int bx0 = tile_x * kTile + (blk & 1) * kUnitW;
+    const int by0 = tile_y * kTile + (blk >> 1) * kUnitH;
+    if (bx0 >= p.W || by0 >= p.H) return;                     // block entirely outside the image
+    const int bx1 = min(bx0 + kUnitW - 1, p.W - 1), by1 = min(by0 + kUnitH - 1, p.H - 1);
+    const int px = bx0 + (lane & 7), py = by0 + (lane >> 3);
     const bool inside = px < p.W && py < p.H;
     const float pixfx = (float)px, pixfy = (float)py;
 
     const uint2 range = p.ranges[tile];
     const int n = (int)(range.y - range.x);
-    const int nbatches = (n + kTilePix - 1) / kTilePix;
     const uint32_t* list = p.point_list + range.x;
 
     float T = 1.0f;
@@ -73,68 +77,47 @@ __global__ void __launch_bounds__(kTilePix) composite_fwd_kernel(const FwdParams
     uint32_t last_contributor = 0;
     bool done = !inside;
 
-    auto issue = [&](int stage, int id) {
-        if (id >= 0) {
-            cp_async16(&sA[stage][tid], p.recA + id);
-            cp_async16(&sB[stage][tid], p.recB + id);
-            cp_async16(&sC[stage][tid], p.recC + id);
-            cp_async16(&sD[stage][tid], p.recD + id);
-            cp_async16(&sE[stage][tid], p.recE + id);
-        }
-        cp_async_commit();
-    };
+    // software pipeline: records of batch k+1 and indices of batch k+2 are in flight during batch k
+    int id_cur = (lane < n) ? (int)list[lane] : -1;
+    float4 a_cur = make_float4(0.f, 0.f, 0.f, 0.f), b_cur = a_cur;
+    if (id_cur >= 0) { a_cur = ldg_f4(p.recA + id_cur); b_cur = ldg_f4(p.recB + id_cur); }
+    int id_nxt = (32 + lane < n) ? (int)list[32 + lane] : -1;
 
-    int id_next = -1;
-    if (nbatches > 0) {
-        const int id0 = (tid < n) ? (int)list[tid] : -1;
-        issue(0, id0);
-        id_next = (kTilePix + tid < n) ? (int)list[kTilePix + tid] : -1;
-    }
+    for (int base = 0; base < n; base += 32) {
+        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f), b_nxt = a_nxt;
+        if (id_nxt >= 0) { a_nxt = ldg_f4(p.recA + id_nxt); b_nxt = ldg_f4(p.recB + id_nxt); }
+        const int nn = base + 64 + lane;
+        const int id_nn = (nn < n) ? (int)list[nn] : -1;
 
-    for (int b = 0; b < nbatches; b++) {
-        cp_async_wait_all();
-        // Barrier: batch b is visible to all threads, and every thread has finished reading the
-        // other stage and the mask array.  The vote ends the tile early when every pixel is
-        // saturated (forward.cu:334-336).
-        const int num_done = __syncthreads_count(done);
-        if (num_done == kTilePix) break;
-        if (b + 1 < nbatches) {
-            issue((b + 1) & 1, id_next);
-            const int nn = (b + 2) * kTilePix + tid;
-            id_next = (nn < n) ? (int)list[nn] : -1;
-        }
-        const int st = b & 1;
-        const int cnt = min(kTilePix, n - b * kTilePix);
-        sMask[tid] = (tid < cnt) ? block_mask(sA[st][tid], sB[st][tid], X0, Y0) : 0u;
-        __syncthreads();
-
-        const uint32_t base_ord = (uint32_t)(b * kTilePix);
-        for (int c0 = 0; c0 < cnt; c0 += 32) {
-            if (__all_sync(0xffffffffu, done)) break;
-            uint32_t bits = __ballot_sync(0xffffffffu, (sMask[c0 + lane] >> warp) & 1u);
-            while (bits) {
-                const int j = c0 + __ffs(bits) - 1;
-                bits &= bits - 1;
-                if (done) continue;
-                const float4 a = sA[st][j];   // x, y, conic.a, conic.b
-                const float4 bb = sB[st][j];  // conic.c, opacity, tau, depth
-                const float dx = __fsub_rn(a.x, pixfx);
-                const float dy = __fsub_rn(a.y, pixfy);
-                // power = -0.5f*(A*dx*dx + C*dy*dy) - B*dx*dy in the reference's operation order
-                const float sum = __fmaf_rn(__fmul_rn(a.z, dx), dx, __fmul_rn(__fmul_rn(bb.x, dy), dy));
-                const float power = __fmaf_rn(sum, -0.5f, -__fmul_rn(__fmul_rn(a.w, dx), dy));
-                if (power > 0.0f) continue;
-                if (power < -bb.z) continue;   // alpha < 1/255 with margin: same outcome, no exp
+        // ---- entry-parallel: lane t tests entry base + t against the block's pixels
+        const uint32_t h = (id_cur >= 0) ? entry_hits(a_cur, b_cur, bx0, by0, bx1, by1) : 0u;
+        if (__any_sync(0xffffffffu, h != 0u)) {
+            if (h != 0u) {
+                sA[lane] = a_cur;
+                sB[lane] = b_cur;
+                sC[lane] = ldg_f4(p.recC + id_cur);
+                sD[lane] = ldg_f4(p.recD + id_cur);
+                sE[lane] = ldg_f4(p.recE + id_cur);
+            }
+            uint32_t mybits = transpose32(h, lane);   // lane p: entries of this batch that hit pixel p
+            __syncwarp();
+            // ---- pixel-parallel: the reference's per-pixel sequence over this pixel's hits
+            while (mybits != 0u && !done) {
+                const int t = __ffs(mybits) - 1;
+                mybits &= mybits - 1;
+                const float4 a = sA[t];    // x, y, conic.a, conic.b
+                const float4 bb = sB[t];   // conic.c, opacity, half2(ex, ey), depth
+                float dx, dy;
+                const float power = pair_power(a, bb, pixfx, pixfy, dx, dy);
                 const float alpha = fminf(0.99f, __fmul_rn(bb.y, expf(power)));
-                if (alpha < 1.0f / 255.0f) continue;
                 const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
-                if (test_T < 0.0001f) {
+                if (test_T < 0.0001f) {      // this Gaussian is not blended (forward.cu:382-386)
                     done = true;
-                    continue;
+                    break;
                 }
-                const float4 c = sC[st][j];   // r, g, b, sin(theta)
-                const float4 d = sD[st][j];   // scale xyz, rot.r
-                const float4 e = sE[st][j];   // rot xyz, theta
+                const float4 c = sC[t];    // r, g, b, sin(theta)
+                const float4 d = sD[t];    // scale xyz, rot.r
+                const float4 e = sE[t];    // rot xyz, theta
                 C0 = __fmaf_rn(__fmul_rn(c.x, alpha), T, C0);
                 C1 = __fmaf_rn(__fmul_rn(c.y, alpha), T, C1);
                 C2 = __fmaf_rn(__fmul_rn(c.z, alpha), T, C2);
@@ -142,8 +125,7 @@ __global__ void __launch_bounds__(kTilePix) composite_fwd_kernel(const FwdParams
                 S0 = __fmaf_rn(__fmul_rn(d.x, alpha), T, S0);
                 S1 = __fmaf_rn(__fmul_rn(d.y, alpha), T, S1);
                 S2 = __fmaf_rn(__fmul_rn(d.z, alpha), T, S2);
-
-                // r = mix(identity, q, w) with q = (w=rot.r, x, y, z), w = alpha*T
+                // r = mix(identity, q, w) with q = (w = rot.r, x, y, z), w = alpha * T
                 const float wgt = __fmul_rn(alpha, T);
                 const float om = __fsub_rn(1.0f, wgt);
                 float rw, rx, ry, rz;
@@ -166,13 +148,14 @@ __global__ void __launch_bounds__(kTilePix) composite_fwd_kernel(const FwdParams
                 const float ny = Qw * ry + Qy * rw + Qz * rx - Qx * rz;
                 const float nz = Qw * rz + Qz * rw + Qx * ry - Qy * rx;
                 Qw = nw; Qx = nx; Qy = ny; Qz = nz;
-
                 T = test_T;
-                last_contributor = base_ord + (uint32_t)j + 1u;   // ordinal in the tile's list
+                last_contributor = (uint32_t)(base + t) + 1u;   // ordinal in the tile's list
             }
+            __syncwarp();
+            if (__all_sync(0xffffffffu, done)) break;   // every pixel of the block is saturated
         }
+        id_cur = id_nxt; a_cur = a_nxt; b_cur = b_nxt; id_nxt = id_nn;
     }
-    cp_async_wait_all();
 
     if (inside) {
         const size_t npix = (size_t)p.W * p.H;
@@ -198,6 +181,7 @@ __global__ void __launch_bounds__(kTilePix) composite_fwd_kernel(const FwdParams
         p.out_scale[npix + pid] = S1;
         p.out_scale[2 * npix + pid] = S2;
     }
+    if (lane == 0) atomicMax(&p.tile_clocks[tile], (uint32_t)((clock64() - t_start) >> 10));
 }
 
 }  // namespace
@@ -215,8 +199,10 @@ int launch_composite_fwd(const VegsForwardArgs& a, const GeomView& g, const Scra
     p.out_color = a.out_color; p.out_depth = a.out_depth; p.out_quat = a.out_cov_quat;
     p.out_scale = a.out_cov_scale; p.out_alpha = a.out_alpha;
     p.n_contrib = im.n_contrib;
+    p.tile_clocks = im.tile_clocks;
     const int T = p.gx * ((a.H + kTile - 1) / kTile);
-    composite_fwd_kernel<<<T, kTilePix, 0, stream>>>(p);
+    VEGS_CUDA_OK(cudaMemsetAsync(im.tile_clocks, 0, (size_t)2 * T * sizeof(uint32_t), stream));
+    composite_fwd_kernel<<<T * kUnitsPerTile, 32, 0, stream>>>(p);
     VEGS_LAUNCH_CHECK("composite_fwd", stream, a.debug);
     return VEGS_OK;
 }

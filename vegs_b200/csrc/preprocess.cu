@@ -14,6 +14,7 @@
 //     duplicateWithKeys pass has to re-derive them.
 // Roofline: HBM.  Algorithmic bytes per Gaussian: 20 (mean + radius + key) for all P plus
 // 12+16+4+12*M inputs and 80+8+1 outputs for the visible ones.
+#include <cuda_fp16.h>
 #include "common.cuh"
 #include "gsmath.cuh"
 
@@ -250,11 +251,33 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_fwd_kernel(const PrePa
         }
         const float theta = acosf(d4.w);
         e4.w = theta;
-        // tau: a pixel can only reach alpha >= 1/255 where power >= -tau (margin 0.01 covers the
-        // rounding of exp and of the product); used to skip exp() and to cull per pixel block
-        const float tau = logf(255.0f * opacity) + 0.01f;
+        // Half extents (ex, ey) of the box that contains every pixel where this Gaussian can reach
+        // alpha >= 1/255: that needs power >= -tau with tau = log(255*opacity), i.e. the ellipse
+        // A dx^2 + 2 B dx dy + C dy^2 <= 2 tau, whose extents are sqrt(2 tau C / det), sqrt(2 tau A / det).
+        // Margins (0.01 on tau, 1e-3 relative + 0.01 px on the extents, upward fp16 rounding) keep the
+        // box conservative, so the compositing kernels may skip the pixels outside it.  Encodings:
+        // (+inf, +inf) = "cannot bound, test the whole tile" (non-finite inputs, for which the
+        // reference's fminf(0.99, NaN) = 0.99 makes every pixel contribute); (-1, -1) = no pixel.
+        float ex = __int_as_float(0x7f800000), ey = ex;
+        {
+            const float tau = logf(255.0f * opacity) + 0.01f;
+            const bool fin = isfinite(pix_x) && isfinite(pix_y) && isfinite(conic.x) &&
+                             isfinite(conic.y) && isfinite(conic.z) && isfinite(tau);
+            if (fin) {
+                const float cdet = conic.x * conic.z - conic.y * conic.y;
+                if (tau < 0.0f) {
+                    ex = ey = -1.0f;
+                } else if (cdet > 0.0f) {
+                    const float s2 = 2.0f * tau / cdet;
+                    const float tx = sqrtf(s2 * conic.z) * 1.002f + 0.01f;
+                    const float ty = sqrtf(s2 * conic.x) * 1.002f + 0.01f;
+                    if (isfinite(tx) && isfinite(ty)) { ex = tx; ey = ty; }
+                }
+            }
+        }
+        const __half2 eh = __floats2half2_rn(ex, ey);   // 1.002 above covers the 2^-11 rounding
         p.recA[idx] = make_float4(pix_x, pix_y, conic.x, conic.y);
-        p.recB[idx] = make_float4(conic.z, opacity, tau, depth);
+        p.recB[idx] = make_float4(conic.z, opacity, __uint_as_float(*reinterpret_cast<const uint32_t*>(&eh)), depth);
         p.recC[idx] = make_float4(rgb.x, rgb.y, rgb.z, sinf(theta));
         p.recD[idx] = d4;
         p.recE[idx] = e4;
