@@ -49,16 +49,9 @@ f = fwd.cpu().numpy().astype(np.int64) * 1024; b = bwd.cpu().numpy().astype(np.i
 np.savez_compressed(out, len=rl, tmax=tmax, tsum=tsum, fwd_cycles=f, bwd_cycles=b, gx=gx, gy=gy)
 order = np.argsort(-f)
 print("tiles", T, "R", rl.sum(), "sum fwd Mcycles", f.sum() / 1e6, "sum bwd Mcycles", b.sum() / 1e6)
-dbg = dbg.cpu().numpy().astype(np.int64).reshape(T, 8)
-print("top fwd tiles: (tile, row, len, maxcontrib, fwd Mcyc, bwd Mcyc, cyc/entry fwd | m1 batches, m2 batches, phaseA Mcyc, phaseB Mcyc, mode1 Mcyc, m2 area/entry, hits/px/m2batch)")
-for t in order[:16]:
-    d = dbg[t]
-    print(t, t // gx, rl[t], tmax[t], round(f[t] / 1e6, 2), round(b[t] / 1e6, 2), round(f[t] / max(rl[t], 1), 1), "|", d[0], d[1],
-          round(d[2] * 1024 / 1e6, 2), round(d[3] * 1024 / 1e6, 2), round(d[4] * 1024 / 1e6, 2), round(d[5] / max(d[1] * 256, 1), 1),
-          round(d[6] / 256 / max(d[1], 1), 1), "| cpwait Mcyc", round(d[7] * 1024 / 1e6, 2), "sync0 Mcyc", round(d[0] * 1024 / 1e6, 2),
-          "PROLOGUE", round(d[1] * 1024 / 1e6, 2), "LOOP", round(d[4] * 1024 / 1e6, 2), "B1", round(d[5] * 1024 / 1e6, 2))
-print("all tiles: m1 batches", dbg[:, 0].sum(), "m2 batches", dbg[:, 1].sum(), "phaseA Mcyc", dbg[:, 2].sum() * 1024 / 1e6,
-      "phaseB Mcyc", dbg[:, 3].sum() * 1024 / 1e6, "mode1 Mcyc", dbg[:, 4].sum() * 1024 / 1e6)
+print("top fwd tiles: (tile, row, len, maxcontrib, fwd max-unit Mcyc, bwd max-unit Mcyc, fwd cyc/entry)")
+for t in order[:12]:
+    print(t, t // gx, rl[t], tmax[t], round(f[t] / 1e6, 2), round(b[t] / 1e6, 2), round(f[t] / max(rl[t], 1), 1))
 print("len percentiles", np.percentile(rl, [50, 90, 99, 100]))
 print("fwd cycles percentiles (M)", np.percentile(f, [50, 90, 99, 100]) / 1e6)
 print("bwd cycles percentiles (M)", np.percentile(b, [50, 90, 99, 100]) / 1e6)

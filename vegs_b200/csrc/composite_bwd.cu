@@ -1,25 +1,26 @@
-// Blend-stage backward.  One warp per 8x4 pixel block ("unit"), 8 units per 16x16 tile; each unit
-// walks its tile's list back to front from the block's deepest contributor.
+// Blend-stage backward.  One CTA of 8 warps per 8x4 pixel block ("unit"), 8 units per 16x16 tile;
+// a unit walks its tile's list back to front from the block's deepest contributor in super-batches
+// of 256 entries.
 //
 // Replaces BACKWARD::render / renderCUDA (reference cuda_rasterizer/backward.cu:417-694).
 //
 // The reference lets all 256 pixel threads of a tile evaluate every list entry and issues >= 10
-// global float atomics per (pixel, Gaussian) pair (backward.cu:612,654,682-691).  Here, per batch
-// of 32 entries (composite_common.cuh):
-//   A  entry-parallel   lane t finds the block pixels entry t contributes to (exact test inside
-//                       the entry's conservative box) -> 32-bit hit mask; warp bit-transpose
-//   B  pixel-parallel   lane p walks ITS hits in list order (back to front) and runs the
-//                       reference's sequential recurrences (T, accumulated colour / depth /
-//                       alpha); for every hit it leaves the two per-pair scalars that depend on
-//                       that sequential state, w = alpha*T and dL/dalpha, in a 32x32 shared
-//                       matrix
-//   C  entry-parallel   lane t sums the ten gradient components of ITS entry over the pixels of
-//                       its hit mask (recomputing dx, dy, G from the records, reading w and
-//                       dL/dalpha from the matrix) in registers, and issues three 16-byte vector
-//                       reductions (red.global.add.v4.f32, SASS REDG.E.ADD.F32x4) into the packed
-//                       48-byte per-Gaussian accumulator
-// so there are no per-pair atomics, no warp-shuffle reductions and no block-level barriers, and
-// list entries that touch none of the block's pixels cost one box test.
+// global float atomics per (pixel, Gaussian) pair (backward.cu:612,654,682-691).  Here, per
+// super-batch (composite_common.cuh):
+//   S0  entry-parallel (256 threads, one entry each): the block pixels the entry contributes to
+//       (exact test inside the entry's conservative box) as a 32-bit hit mask, and each hit's alpha
+//   S1  each warp bit-transposes its 32 hit masks into per-pixel hit lists
+//   S2  warp 0, lane = pixel: the reference's sequential recurrences over that pixel's hits, back
+//       to front (T /= 1-alpha, accumulated colour / depth / alpha behind the hit); for every
+//       hit it leaves the two per-pair scalars that depend on that sequential state,
+//       w = alpha*T and dL/dalpha, in a 32 x 256 shared matrix
+//   S3  entry-parallel: thread t sums the ten gradient components of ITS entry over the pixels of
+//       its hit mask in registers (recomputing dx, dy, G from the records) and issues three 16-byte
+//       vector reductions (red.global.add.v4.f32, SASS REDG.E.ADD.F32x4) into the packed 48-byte
+//       per-Gaussian accumulator
+// so there are no per-pair atomics, no warp-shuffle reductions, the expensive parts are spread
+// over 8 warps per pixel block, and entries that touch none of the block's pixels cost one box
+// test.  Units are issued longest-list-first.
 // The quaternion / scale-map cotangents are not propagated: the reference accumulates them into
 // buffers that its next kernel overwrites (backward.cu:624-647 vs :322-325,:340-341), so its
 // returned gradients do not contain them.
@@ -39,6 +40,9 @@ __device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float
                  : "memory");
 }
 
+constexpr int kSuper = 256;                 // entries per super-batch = threads per CTA
+constexpr int kWarps = kSuper / 32;
+
 struct BwdParams {
     const uint2* ranges;
     const uint32_t* point_list;
@@ -53,15 +57,19 @@ struct BwdParams {
     uint32_t* tile_clocks;
 };
 
-__global__ void __launch_bounds__(32) composite_bwd_kernel(const BwdParams p) {
-    __shared__ __align__(16) float4 sA[32];
-    __shared__ __align__(16) float4 sB[32];
-    __shared__ __align__(16) float4 sC[32];
-    __shared__ __align__(16) float4 sPix[32];        // per pixel: dL/dcolor rgb, dL/ddepth
-    __shared__ __align__(8) float2 sM[32 * 32];      // [pixel][entry]: (alpha*T, dL/dalpha)
+struct BwdSmem {
+    float2 M[32 * kSuper];          // [pixel][slot]: (alpha, -) after S0, (alpha*T, dL/dalpha) after S2
+    float4 A[kSuper], B[kSuper], C[kSuper];
+    float4 pix[32];                 // per pixel: dL/dcolor rgb, dL/ddepth
+    uint32_t bits[kWarps][32];      // [segment][pixel]: hits of the pixel inside the segment
+};
+
+__global__ void __launch_bounds__(kSuper) composite_bwd_kernel(const BwdParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
 
     const long long t_start = clock64();
-    const int lane = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t unit = blockIdx.x;
     const uint32_t tile = p.tile_order[unit >> 3];
     const int blk = (int)(unit & 7u);
@@ -70,6 +78,7 @@ __global__ void __launch_bounds__(32) composite_bwd_kernel(const BwdParams p) {
     const int by0 = tile_y * kTile + (blk >> 1) * kUnitH;
     if (bx0 >= p.W || by0 >= p.H) return;
     const int bx1 = min(bx0 + kUnitW - 1, p.W - 1), by1 = min(by0 + kUnitH - 1, p.H - 1);
+    // lane = pixel (every warp computes it; the pixel state below is used by warp 0 only)
     const int px = bx0 + (lane & 7), py = by0 + (lane >> 3);
     const bool inside = px < p.W && py < p.H;
     const float pixfx = (float)px, pixfy = (float)py;
@@ -77,8 +86,8 @@ __global__ void __launch_bounds__(32) composite_bwd_kernel(const BwdParams p) {
     const size_t pid = (size_t)py * p.W + px;
 
     const uint32_t last_contributor = inside ? p.n_contrib[pid] : 0u;
-    const int n = (int)__reduce_max_sync(0xffffffffu, last_contributor);   // deepest contributor
-    if (n == 0) return;
+    const int n = (int)__reduce_max_sync(0xffffffffu, last_contributor);   // deepest contributor of the block
+    if (n == 0) return;                                                      // same value in every warp
     const uint2 range = p.ranges[tile];
     const uint32_t* list = p.point_list + range.x;
 
@@ -94,7 +103,7 @@ __global__ void __launch_bounds__(32) composite_bwd_kernel(const BwdParams p) {
         if (p.dL_ddepth) dpix_depth = p.dL_ddepth[pid];
         if (p.dL_dalpha) dpix_alpha = p.dL_dalpha[pid];
     }
-    sPix[lane] = make_float4(dpix0, dpix1, dpix2, dpix_depth);
+    if (warp == 0) sm.pix[lane] = make_float4(dpix0, dpix1, dpix2, dpix_depth);
     const float bg_dot = p.bg[0] * dpix0 + p.bg[1] * dpix1 + p.bg[2] * dpix2;
     const float ddelx_dx = 0.5f * p.W;
     const float ddely_dy = 0.5f * p.H;
@@ -102,69 +111,73 @@ __global__ void __launch_bounds__(32) composite_bwd_kernel(const BwdParams p) {
     float accum_rec0 = 0.f, accum_rec1 = 0.f, accum_rec2 = 0.f, accum_red = 0.f, accum_rea = 0.f;
     float last_alpha = 0.f, last_c0 = 0.f, last_c1 = 0.f, last_c2 = 0.f, last_depth = 0.f;
 
-    // slot t of the batch starting at `base` holds list entry n - 1 - (base + t): back to front
-    const int e_first = n - 1 - lane;
+    // slot t of the super-batch starting at `base` holds list entry n - 1 - (base + t): back to front
+    const int e_first = n - 1 - tid;
     int id_cur = (e_first >= 0) ? (int)list[e_first] : -1;
     float4 a_cur = make_float4(0.f, 0.f, 0.f, 0.f), b_cur = a_cur;
     if (id_cur >= 0) { a_cur = ldg_f4(p.recA + id_cur); b_cur = ldg_f4(p.recB + id_cur); }
-    int id_nxt = (e_first - 32 >= 0) ? (int)list[e_first - 32] : -1;
-    __syncwarp();
+    int id_nxt = (e_first - kSuper >= 0) ? (int)list[e_first - kSuper] : -1;
 
-    for (int base = 0; base < n; base += 32) {
+    for (int base = 0; base < n; base += kSuper) {
         float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f), b_nxt = a_nxt;
         if (id_nxt >= 0) { a_nxt = ldg_f4(p.recA + id_nxt); b_nxt = ldg_f4(p.recB + id_nxt); }
-        const int e_nn = n - 1 - (base + 64 + lane);
+        const int e_nn = n - 1 - (base + 2 * kSuper + tid);
         const int id_nn = (e_nn >= 0) ? (int)list[e_nn] : -1;
 
-        // ---- A: lane t tests entry e_base - t against the block's pixels
-        const uint32_t h = (id_cur >= 0) ? entry_hits(a_cur, b_cur, bx0, by0, bx1, by1) : 0u;
-        if (__any_sync(0xffffffffu, h != 0u)) {
-            if (h != 0u) {
-                sA[lane] = a_cur;
-                sB[lane] = b_cur;
-                sC[lane] = ldg_f4(p.recC + id_cur);
-            }
-            uint32_t mybits = transpose32(h, lane);
-            const int e_base = n - 1 - base;
-            __syncwarp();
-            // ---- B: lane p walks its hits back to front (ascending slot = descending entry)
-            while (mybits != 0u) {
-                const int t = __ffs(mybits) - 1;
-                mybits &= mybits - 1;
-                const uint32_t e = (uint32_t)(e_base - t);
-                float2 m = make_float2(0.f, 0.f);
-                if (e < last_contributor) {     // else behind this pixel's last contributor (backward.cu:561-563)
-                    const float4 a = sA[t];     // x, y, conic.a, conic.b
-                    const float4 bb = sB[t];    // conic.c, opacity, half2(ex, ey), depth
-                    const float4 c = sC[t];     // r, g, b, -
-                    float dx, dy;
-                    const float power = pair_power(a, bb, pixfx, pixfy, dx, dy);
-                    const float G = expf(power);
-                    const float alpha = fminf(0.99f, __fmul_rn(bb.y, G));
-                    T = T / (1.0f - alpha);
-                    const float w = alpha * T;
-                    float dL_dalpha = 0.0f;
-                    accum_rec0 = last_alpha * last_c0 + (1.f - last_alpha) * accum_rec0;
-                    accum_rec1 = last_alpha * last_c1 + (1.f - last_alpha) * accum_rec1;
-                    accum_rec2 = last_alpha * last_c2 + (1.f - last_alpha) * accum_rec2;
-                    last_c0 = c.x; last_c1 = c.y; last_c2 = c.z;
-                    dL_dalpha += (c.x - accum_rec0) * dpix0;
-                    dL_dalpha += (c.y - accum_rec1) * dpix1;
-                    dL_dalpha += (c.z - accum_rec2) * dpix2;
-                    accum_red = last_alpha * last_depth + (1.f - last_alpha) * accum_red;
-                    last_depth = bb.w;
-                    dL_dalpha += (bb.w - accum_red) * dpix_depth;
-                    accum_rea = last_alpha + (1.f - last_alpha) * accum_rea;
-                    dL_dalpha += (1.f - accum_rea) * dpix_alpha;
-                    dL_dalpha *= T;
-                    last_alpha = alpha;
-                    dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot;
-                    m = make_float2(w, dL_dalpha);
+        // ---- S0: thread = entry.  Hit mask over the unit's pixels, alpha of every hit.
+        uint32_t h = 0;
+        if (id_cur >= 0)
+            h = entry_hits_alpha(a_cur, b_cur, bx0, by0, bx1, by1, reinterpret_cast<float*>(sm.M + tid), 2 * kSuper);
+        if (h != 0u) {
+            sm.A[tid] = a_cur;
+            sm.B[tid] = b_cur;
+            sm.C[tid] = ldg_f4(p.recC + id_cur);
+        }
+        // ---- S1: per-pixel hit lists of this warp's 32-entry segment
+        sm.bits[warp][lane] = transpose32(h, lane);
+        const int any_hit = __syncthreads_or(h != 0u);
+        if (any_hit) {
+            // ---- S2: warp 0, lane = pixel: the sequential recurrences, back to front
+            if (warp == 0) {
+                const int e_base = n - 1 - base;
+                for (int w = 0; w < kWarps; w++) {
+                    uint32_t bits = sm.bits[w][lane];
+                    while (bits != 0u) {
+                        const int t = w * 32 + __ffs(bits) - 1;
+                        bits &= bits - 1;
+                        float2* slot = &sm.M[lane * kSuper + t];
+                        const uint32_t e = (uint32_t)(e_base - t);
+                        float2 m = make_float2(0.f, 0.f);
+                        if (e < last_contributor) {   // else behind this pixel's last contributor (backward.cu:561-563)
+                            const float alpha = slot->x;
+                            const float4 c = sm.C[t];     // r, g, b, -
+                            const float depth = sm.B[t].w;
+                            T = T / (1.0f - alpha);
+                            const float wgt = alpha * T;
+                            float dL_dalpha = 0.0f;
+                            accum_rec0 = last_alpha * last_c0 + (1.f - last_alpha) * accum_rec0;
+                            accum_rec1 = last_alpha * last_c1 + (1.f - last_alpha) * accum_rec1;
+                            accum_rec2 = last_alpha * last_c2 + (1.f - last_alpha) * accum_rec2;
+                            last_c0 = c.x; last_c1 = c.y; last_c2 = c.z;
+                            dL_dalpha += (c.x - accum_rec0) * dpix0;
+                            dL_dalpha += (c.y - accum_rec1) * dpix1;
+                            dL_dalpha += (c.z - accum_rec2) * dpix2;
+                            accum_red = last_alpha * last_depth + (1.f - last_alpha) * accum_red;
+                            last_depth = depth;
+                            dL_dalpha += (depth - accum_red) * dpix_depth;
+                            accum_rea = last_alpha + (1.f - last_alpha) * accum_rea;
+                            dL_dalpha += (1.f - accum_rea) * dpix_alpha;
+                            dL_dalpha *= T;
+                            last_alpha = alpha;
+                            dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot;
+                            m = make_float2(wgt, dL_dalpha);
+                        }
+                        *slot = m;
+                    }
                 }
-                sM[lane * 32 + t] = m;
             }
-            __syncwarp();
-            // ---- C: lane t sums its entry's gradient over the pixels it hit
+            __syncthreads();
+            // ---- S3: thread = entry: sum the entry's gradient over the pixels it hit
             if (h != 0u) {
                 const float4 a = a_cur, bb = b_cur;
                 float g_mx = 0.f, g_my = 0.f, g_cxx = 0.f, g_cxy = 0.f, g_cyy = 0.f, g_op = 0.f;
@@ -174,16 +187,16 @@ __global__ void __launch_bounds__(32) composite_bwd_kernel(const BwdParams p) {
                 while (bits != 0u) {
                     const int q = __ffs(bits) - 1;
                     bits &= bits - 1;
-                    const float2 m = sM[q * 32 + lane];
+                    const float2 m = sm.M[q * kSuper + tid];
                     if (m.x == 0.0f && m.y == 0.0f) continue;
                     any = true;
-                    const float4 dp = sPix[q];
+                    const float4 dp = sm.pix[q];
                     float dx, dy;
                     const float power = pair_power(a, bb, (float)(bx0 + (q & 7)), (float)(by0 + (q >> 3)), dx, dy);
                     const float G = expf(power);
-                    const float w = m.x, dL_dalpha = m.y;
-                    g_c0 += w * dp.x; g_c1 += w * dp.y; g_c2 += w * dp.z;
-                    g_dep += w * dp.w;
+                    const float wgt = m.x, dL_dalpha = m.y;
+                    g_c0 += wgt * dp.x; g_c1 += wgt * dp.y; g_c2 += wgt * dp.z;
+                    g_dep += wgt * dp.w;
                     const float dL_dG = bb.y * dL_dalpha;
                     const float gdx = G * dx;
                     const float gdy = G * dy;
@@ -203,11 +216,11 @@ __global__ void __launch_bounds__(32) composite_bwd_kernel(const BwdParams p) {
                     red_add_v4(dst + 2, g_c2, g_dep, 0.0f, 0.0f);
                 }
             }
-            __syncwarp();
         }
+        __syncthreads();   // shared arrays are reused by the next super-batch
         id_cur = id_nxt; a_cur = a_nxt; b_cur = b_nxt; id_nxt = id_nn;
     }
-    if (lane == 0) atomicMax(&p.tile_clocks[tile], (uint32_t)((clock64() - t_start) >> 10));
+    if (tid == 0) atomicMax(&p.tile_clocks[tile], (uint32_t)((clock64() - t_start) >> 10));
 }
 
 }  // namespace
@@ -228,7 +241,13 @@ int launch_composite_bwd(const VegsBackwardArgs& a, const GeomView& g, const Img
     p.acc = acc;
     const int T = p.gx * ((a.H + kTile - 1) / kTile);
     p.tile_clocks = const_cast<uint32_t*>(im.tile_clocks) + T;
-    composite_bwd_kernel<<<T * kUnitsPerTile, 32, 0, stream>>>(p);
+    static bool configured = false;
+    if (!configured) {
+        VEGS_CUDA_OK(cudaFuncSetAttribute(composite_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)sizeof(BwdSmem)));
+        configured = true;
+    }
+    composite_bwd_kernel<<<T * kUnitsPerTile, kSuper, sizeof(BwdSmem), stream>>>(p);
     VEGS_LAUNCH_CHECK("composite_bwd", stream, a.debug);
     return VEGS_OK;
 }

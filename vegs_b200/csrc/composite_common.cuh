@@ -69,6 +69,34 @@ __device__ __forceinline__ uint32_t entry_hits(const float4 a, const float4 b, i
     return hits;
 }
 
+// Same, and stores each hit's alpha at alpha_out[pixel * stride].
+__device__ __forceinline__ uint32_t entry_hits_alpha(const float4 a, const float4 b, int bx0, int by0,
+                                                     int bx1, int by1, float* alpha_out, int stride) {
+    const uint32_t packed = __float_as_uint(b.z);
+    const float2 e = __half22float2(*reinterpret_cast<const __half2*>(&packed));
+    const int x0 = (int)ceilf(fmaxf(a.x - e.x, (float)bx0));
+    const int x1 = (int)floorf(fminf(a.x + e.x, (float)bx1));
+    const int y0 = (int)ceilf(fmaxf(a.y - e.y, (float)by0));
+    const int y1 = (int)floorf(fminf(a.y + e.y, (float)by1));
+    uint32_t hits = 0;
+    for (int y = y0; y <= y1; y++) {
+        const float dy = __fsub_rn(a.y, (float)y);
+        const float cyy = __fmul_rn(__fmul_rn(b.x, dy), dy);
+        for (int x = x0; x <= x1; x++) {
+            const float dx = __fsub_rn(a.x, (float)x);
+            const float sum = __fmaf_rn(__fmul_rn(a.z, dx), dx, cyy);
+            const float power = __fmaf_rn(sum, -0.5f, -__fmul_rn(__fmul_rn(a.w, dx), dy));
+            if (power > 0.0f) continue;
+            const float alpha = fminf(0.99f, __fmul_rn(b.y, expf(power)));
+            if (alpha < 1.0f / 255.0f) continue;
+            const int pix = (y - by0) * kUnitW + (x - bx0);
+            hits |= 1u << pix;
+            alpha_out[pix * stride] = alpha;
+        }
+    }
+    return hits;
+}
+
 // power and alpha of one (pixel, entry) pair that is known to be a hit (same arithmetic as above)
 __device__ __forceinline__ float pair_power(const float4 a, const float4 b, float pixfx, float pixfy,
                                             float& dx, float& dy) {

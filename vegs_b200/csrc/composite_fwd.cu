@@ -1,30 +1,36 @@
-// Front-to-back alpha compositing.  One warp per 8x4 pixel block ("unit"), 8 units per 16x16 tile.
+// Front-to-back alpha compositing.  One CTA of 8 warps per 8x4 pixel block ("unit"), 8 units per
+// 16x16 tile; a unit walks its tile's depth-sorted list in super-batches of 256 entries.
 //
 // Replaces FORWARD::render / renderCUDA (reference cuda_rasterizer/forward.cu:262-441), including
 // the VEGS additions: depth map, alpha map, accumulated covariance quaternion map (sequential
 // slerp product, glm::mix — third_party/glm/glm/ext/quaternion_common.inl:4-26) and scale map.
 //
-// What differs from the reference's kernel (one 256-thread block per tile, every thread evaluates
-// every list entry, __syncthreads per 256 entries):
-//   * entry-parallel hit detection, pixel-parallel blending (composite_common.cuh): per batch of
-//     32 list entries each lane tests ITS entry against the few block pixels inside the entry's
-//     conservative box, a warp bit-transpose turns the 32 hit masks into per-pixel hit lists, and
-//     each pixel lane then runs the reference's sequential arithmetic over its own hits only;
-//   * no block-level synchronisation: units are independent warps, so the very long lists of a
-//     LiDAR-density scene (several 1e5 entries in the horizon tiles) are shared by 8 warps that can
-//     run on 8 SMs, units are issued longest-list-first, and a unit stops as soon as ITS 32 pixels
-//     are saturated;
-//   * colour, depth, scale and rotation travel in packed 16-byte records (no per-contribution
-//     re-reads of several arrays, forward.cu:391-392); records of the next batch are loaded while
-//     the current one is processed;
-//   * acos(q.r) and sin(acos(q.r)) of the slerp are per-Gaussian constants from the preprocess
-//     stage instead of being recomputed per (pixel, Gaussian).
-// Every decision (power > 0, alpha >= 1/255, T(1-alpha) < 1e-4) is evaluated with the reference's
-// float operation order on exactly the (pixel, Gaussian) pairs where the reference evaluates it
-// to "contribute", so n_contrib and all outputs match.
+// The reference runs one 256-thread block per tile in which every pixel thread evaluates every
+// list entry.  At LiDAR density that is the wrong shape: the horizon tiles hold several 1e5 tiny
+// Gaussians, each touching a handful of pixels, and one block walks them while the other SMs
+// idle.  The only truly sequential part of compositing is the transmittance chain
+// T <- T * (1 - alpha) with its saturation test; everything else is parallel.  Per super-batch:
+//   S0  entry-parallel (256 threads, one entry each): clip the entry's conservative box
+//       (preprocess stage) to the unit's 32 pixels, run the reference's exact contribution test on
+//       the pixels inside, keep a 32-bit hit mask and each hit's alpha (alpha matrix in shared
+//       memory); entries with a hit stage their packed records
+//   S1  each warp bit-transposes its 32 hit masks into per-pixel hit lists
+//   S2  warp 0, lane = pixel: the sequential chain over that pixel's hits of the whole super-batch,
+//       in list order and in the reference's float operation order: T before each hit, the
+//       saturation point (T(1-alpha) < 1e-4 stops the pixel, that Gaussian is not blended),
+//       n_contrib, plus the colour and depth sums — a handful of FMAs per hit
+//   S3  pixel-parallel per 32-entry segment (8 warps, lane = pixel): scale sums and the slerp
+//       quaternion product of the segment's hits with the T values from S2
+//   S4  warp 0 folds the eight segment partials into the pixel state, in list order
+// so the expensive work (exp, 2 sin + 4 div + quaternion product per contribution, box tests) is
+// spread over 8 warps per pixel block and 64 warps per tile, units are issued
+// longest-list-first, and a unit stops as soon as its 32 pixels are saturated.
+// Exactness: which Gaussians contribute to a pixel, alpha, T, n_contrib, colour, depth and alpha
+// map are bit-identical to the reference (same float operations in the same order).  The scale
+// sums and the quaternion product are associated per 32-entry segment instead of in one running
+// chain, a last-bit difference far inside the 1e-5 tolerance (values of magnitude <= 1).
 // Roofline: not HBM-bound (32 B per list entry per unit from L2, 48 B more per entry with a hit,
-// 52 B written per pixel); the bound is instruction issue of the per-hit blend (slerp: 2 sin,
-// 4 div, quaternion product) and of the box tests.
+// 52 B written per pixel); the bound is instruction issue of the per-hit blend and the box tests.
 #include <cfloat>
 #include "common.cuh"
 #include "composite_common.cuh"
@@ -32,6 +38,9 @@
 namespace vegs {
 
 namespace {
+
+constexpr int kSuper = 256;                 // entries per super-batch = threads per CTA
+constexpr int kWarps = kSuper / 32;
 
 struct FwdParams {
     const uint2* ranges;
@@ -45,15 +54,22 @@ struct FwdParams {
     uint32_t* tile_clocks;
 };
 
-__global__ void __launch_bounds__(32) composite_fwd_kernel(const FwdParams p) {
-    __shared__ __align__(16) float4 sA[32];
-    __shared__ __align__(16) float4 sB[32];
-    __shared__ __align__(16) float4 sC[32];
-    __shared__ __align__(16) float4 sD[32];
-    __shared__ __align__(16) float4 sE[32];
+struct FwdSmem {
+    float alphaT[32 * kSuper];      // [pixel][slot]: alpha after S0, T-before-the-hit after S2
+    float4 A[kSuper], B[kSuper], C[kSuper], D[kSuper], E[kSuper];
+    uint32_t bits[kWarps][32];      // [segment][pixel]: hits of the pixel inside the segment
+    uint32_t stop_at[32];           // first slot the pixel does not blend any more (kSuper = none)
+    float part[kWarps][11][32];     // segment partials: rows 4-6 scale, rows 7-10 quaternion
+    uint32_t seg_any[kWarps];       // segment has at least one hit
+    int all_done;
+};
+
+__global__ void __launch_bounds__(kSuper) composite_fwd_kernel(const FwdParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    FwdSmem& sm = *reinterpret_cast<FwdSmem*>(smem_raw);
 
     const long long t_start = clock64();
-    const int lane = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t unit = blockIdx.x;
     const uint32_t tile = p.tile_order[unit >> 3];
     const int blk = (int)(unit & 7u);
@@ -62,6 +78,7 @@ __global__ void __launch_bounds__(32) composite_fwd_kernel(const FwdParams p) {
     const int by0 = tile_y * kTile + (blk >> 1) * kUnitH;
     if (bx0 >= p.W || by0 >= p.H) return;                     // block entirely outside the image
     const int bx1 = min(bx0 + kUnitW - 1, p.W - 1), by1 = min(by0 + kUnitH - 1, p.H - 1);
+    // lane = pixel (used by S2..S4)
     const int px = bx0 + (lane & 7), py = by0 + (lane >> 3);
     const bool inside = px < p.W && py < p.H;
     const float pixfx = (float)px, pixfy = (float)py;
@@ -70,6 +87,7 @@ __global__ void __launch_bounds__(32) composite_fwd_kernel(const FwdParams p) {
     const int n = (int)(range.y - range.x);
     const uint32_t* list = p.point_list + range.x;
 
+    // pixel state, meaningful in warp 0 only
     float T = 1.0f;
     float C0 = 0.f, C1 = 0.f, C2 = 0.f, Dacc = 0.f;
     float S0 = 0.f, S1 = 0.f, S2 = 0.f;
@@ -77,56 +95,98 @@ __global__ void __launch_bounds__(32) composite_fwd_kernel(const FwdParams p) {
     uint32_t last_contributor = 0;
     bool done = !inside;
 
-    // software pipeline: records of batch k+1 and indices of batch k+2 are in flight during batch k
-    int id_cur = (lane < n) ? (int)list[lane] : -1;
+    // software pipeline over super-batches: records of the next one are loaded during this one
+    int id_cur = (tid < n) ? (int)list[tid] : -1;
     float4 a_cur = make_float4(0.f, 0.f, 0.f, 0.f), b_cur = a_cur;
     if (id_cur >= 0) { a_cur = ldg_f4(p.recA + id_cur); b_cur = ldg_f4(p.recB + id_cur); }
-    int id_nxt = (32 + lane < n) ? (int)list[32 + lane] : -1;
+    int id_nxt = (kSuper + tid < n) ? (int)list[kSuper + tid] : -1;
 
-    for (int base = 0; base < n; base += 32) {
+    for (int base = 0; base < n; base += kSuper) {
         float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f), b_nxt = a_nxt;
         if (id_nxt >= 0) { a_nxt = ldg_f4(p.recA + id_nxt); b_nxt = ldg_f4(p.recB + id_nxt); }
-        const int nn = base + 64 + lane;
+        const int nn = base + 2 * kSuper + tid;
         const int id_nn = (nn < n) ? (int)list[nn] : -1;
 
-        // ---- entry-parallel: lane t tests entry base + t against the block's pixels
-        const uint32_t h = (id_cur >= 0) ? entry_hits(a_cur, b_cur, bx0, by0, bx1, by1) : 0u;
-        if (__any_sync(0xffffffffu, h != 0u)) {
-            if (h != 0u) {
-                sA[lane] = a_cur;
-                sB[lane] = b_cur;
-                sC[lane] = ldg_f4(p.recC + id_cur);
-                sD[lane] = ldg_f4(p.recD + id_cur);
-                sE[lane] = ldg_f4(p.recE + id_cur);
+        // ---- S0: thread = entry.  Hit mask over the unit's pixels, alpha of every hit.
+        uint32_t h = 0;
+        if (id_cur >= 0) h = entry_hits_alpha(a_cur, b_cur, bx0, by0, bx1, by1, sm.alphaT + tid, kSuper);
+        if (h != 0u) {
+            sm.A[tid] = a_cur;
+            sm.B[tid] = b_cur;
+            sm.C[tid] = ldg_f4(p.recC + id_cur);
+            sm.D[tid] = ldg_f4(p.recD + id_cur);
+            sm.E[tid] = ldg_f4(p.recE + id_cur);
+        }
+        // ---- S1: per-pixel hit lists of this warp's 32-entry segment
+        const uint32_t mybits = transpose32(h, lane);   // lane = pixel, bit = slot inside the segment
+        sm.bits[warp][lane] = mybits;
+        const bool seg_any = __any_sync(0xffffffffu, h != 0u);
+        if (lane == 0) sm.seg_any[warp] = seg_any ? 1u : 0u;
+        __syncthreads();
+
+        // ---- S2: warp 0, lane = pixel: sequential transmittance chain over the super-batch
+        if (warp == 0) {
+            uint32_t stop = kSuper;
+            if (!done) {
+                for (int w = 0; w < kWarps && stop == (uint32_t)kSuper; w++) {
+                    uint32_t bits = sm.bits[w][lane];
+                    while (bits != 0u) {
+                        const int t = w * 32 + __ffs(bits) - 1;
+                        bits &= bits - 1;
+                        float* slot = &sm.alphaT[lane * kSuper + t];
+                        const float alpha = *slot;
+                        const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
+                        if (test_T < 0.0001f) {      // not blended; the pixel is finished (forward.cu:382-386)
+                            done = true;
+                            stop = (uint32_t)t;
+                            break;
+                        }
+                        *slot = T;                   // transmittance in front of this hit
+                        // colour and depth are accumulated here, in the reference's running order, so
+                        // they stay bit-identical (depth values are large: re-associating the sum
+                        // would already cost a few 1e-6)
+                        const float4 c = sm.C[t];
+                        C0 = __fmaf_rn(__fmul_rn(c.x, alpha), T, C0);
+                        C1 = __fmaf_rn(__fmul_rn(c.y, alpha), T, C1);
+                        C2 = __fmaf_rn(__fmul_rn(c.z, alpha), T, C2);
+                        Dacc = __fmaf_rn(__fmul_rn(sm.B[t].w, alpha), T, Dacc);
+                        T = test_T;
+                        last_contributor = (uint32_t)(base + t) + 1u;   // ordinal in the tile's list
+                    }
+                }
+            } else {
+                stop = 0u;
             }
-            uint32_t mybits = transpose32(h, lane);   // lane p: entries of this batch that hit pixel p
-            __syncwarp();
-            // ---- pixel-parallel: the reference's per-pixel sequence over this pixel's hits
-            while (mybits != 0u && !done) {
-                const int t = __ffs(mybits) - 1;
-                mybits &= mybits - 1;
-                const float4 a = sA[t];    // x, y, conic.a, conic.b
-                const float4 bb = sB[t];   // conic.c, opacity, half2(ex, ey), depth
+            sm.stop_at[lane] = stop;
+            const bool all = __all_sync(0xffffffffu, done);
+            if (lane == 0) sm.all_done = all ? 1 : 0;
+        }
+        __syncthreads();
+
+        // ---- S3: warp = segment, lane = pixel: blend terms of the segment's hits
+        if (sm.seg_any[warp] != 0u) {
+            const uint32_t stop = sm.stop_at[lane];
+            uint32_t bits = mybits;
+            float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+            float qw = 1.f, qx = 0.f, qy = 0.f, qz = 0.f;
+            while (bits != 0u) {
+                const int t = warp * 32 + __ffs(bits) - 1;
+                bits &= bits - 1;
+                if ((uint32_t)t >= stop) break;
+                const float4 a = sm.A[t];    // x, y, conic.a, conic.b
+                const float4 bb = sm.B[t];   // conic.c, opacity, half2(ex, ey), depth
                 float dx, dy;
                 const float power = pair_power(a, bb, pixfx, pixfy, dx, dy);
                 const float alpha = fminf(0.99f, __fmul_rn(bb.y, expf(power)));
-                const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
-                if (test_T < 0.0001f) {      // this Gaussian is not blended (forward.cu:382-386)
-                    done = true;
-                    break;
-                }
-                const float4 c = sC[t];    // r, g, b, sin(theta)
-                const float4 d = sD[t];    // scale xyz, rot.r
-                const float4 e = sE[t];    // rot xyz, theta
-                C0 = __fmaf_rn(__fmul_rn(c.x, alpha), T, C0);
-                C1 = __fmaf_rn(__fmul_rn(c.y, alpha), T, C1);
-                C2 = __fmaf_rn(__fmul_rn(c.z, alpha), T, C2);
-                Dacc = __fmaf_rn(__fmul_rn(bb.w, alpha), T, Dacc);
-                S0 = __fmaf_rn(__fmul_rn(d.x, alpha), T, S0);
-                S1 = __fmaf_rn(__fmul_rn(d.y, alpha), T, S1);
-                S2 = __fmaf_rn(__fmul_rn(d.z, alpha), T, S2);
+                const float Tb = sm.alphaT[lane * kSuper + t];
+                const float4 c = sm.C[t];    // r, g, b, sin(theta)
+                const float4 d = sm.D[t];    // scale xyz, rot.r
+                const float4 e = sm.E[t];    // rot xyz, theta
+                s0 = __fmaf_rn(__fmul_rn(d.x, alpha), Tb, s0);
+                s1 = __fmaf_rn(__fmul_rn(d.y, alpha), Tb, s1);
+                s2 = __fmaf_rn(__fmul_rn(d.z, alpha), Tb, s2);
                 // r = mix(identity, q, w) with q = (w = rot.r, x, y, z), w = alpha * T
-                const float wgt = __fmul_rn(alpha, T);
+                const float wgt = __fmul_rn(alpha, Tb);
                 const float om = __fsub_rn(1.0f, wgt);
                 float rw, rx, ry, rz;
                 if (d.w > 1.0f - FLT_EPSILON) {
@@ -135,29 +195,47 @@ __global__ void __launch_bounds__(32) composite_fwd_kernel(const FwdParams p) {
                     ry = __fmul_rn(e.y, wgt);
                     rz = __fmul_rn(e.z, wgt);
                 } else {
-                    const float s0 = sinf(__fmul_rn(om, e.w));
-                    const float s1 = sinf(__fmul_rn(wgt, e.w));
-                    rw = __fdiv_rn(__fmaf_rn(d.w, s1, s0), c.w);
-                    rx = __fdiv_rn(__fmul_rn(e.x, s1), c.w);
-                    ry = __fdiv_rn(__fmul_rn(e.y, s1), c.w);
-                    rz = __fdiv_rn(__fmul_rn(e.z, s1), c.w);
+                    const float sn0 = sinf(__fmul_rn(om, e.w));
+                    const float sn1 = sinf(__fmul_rn(wgt, e.w));
+                    rw = __fdiv_rn(__fmaf_rn(d.w, sn1, sn0), c.w);
+                    rx = __fdiv_rn(__fmul_rn(e.x, sn1), c.w);
+                    ry = __fdiv_rn(__fmul_rn(e.y, sn1), c.w);
+                    rz = __fdiv_rn(__fmul_rn(e.z, sn1), c.w);
                 }
-                // Q = Q * r (Hamilton product, glm/detail/type_quat.inl:286-296)
+                // q = q * r (Hamilton product, glm/detail/type_quat.inl:286-296)
+                const float nw = qw * rw - qx * rx - qy * ry - qz * rz;
+                const float nx = qw * rx + qx * rw + qy * rz - qz * ry;
+                const float ny = qw * ry + qy * rw + qz * rx - qx * rz;
+                const float nz = qw * rz + qz * rw + qx * ry - qy * rx;
+                qw = nw; qx = nx; qy = ny; qz = nz;
+            }
+            float (*pp)[32] = sm.part[warp];
+            pp[4][lane] = s0; pp[5][lane] = s1; pp[6][lane] = s2;
+            pp[7][lane] = qw; pp[8][lane] = qx; pp[9][lane] = qy; pp[10][lane] = qz;
+        }
+        __syncthreads();
+
+        // ---- S4: warp 0 folds the segment partials into the pixel state, in list order
+        if (warp == 0) {
+            for (int w = 0; w < kWarps; w++) {
+                if (sm.seg_any[w] == 0u) continue;
+                float (*pp)[32] = sm.part[w];
+                S0 += pp[4][lane]; S1 += pp[5][lane]; S2 += pp[6][lane];
+                const float rw = pp[7][lane], rx = pp[8][lane], ry = pp[9][lane], rz = pp[10][lane];
                 const float nw = Qw * rw - Qx * rx - Qy * ry - Qz * rz;
                 const float nx = Qw * rx + Qx * rw + Qy * rz - Qz * ry;
                 const float ny = Qw * ry + Qy * rw + Qz * rx - Qx * rz;
                 const float nz = Qw * rz + Qz * rw + Qx * ry - Qy * rx;
                 Qw = nw; Qx = nx; Qy = ny; Qz = nz;
-                T = test_T;
-                last_contributor = (uint32_t)(base + t) + 1u;   // ordinal in the tile's list
             }
-            __syncwarp();
-            if (__all_sync(0xffffffffu, done)) break;   // every pixel of the block is saturated
         }
+        const bool finished = sm.all_done != 0;
+        __syncthreads();   // shared arrays are reused by the next super-batch
+        if (finished) break;
         id_cur = id_nxt; a_cur = a_nxt; b_cur = b_nxt; id_nxt = id_nn;
     }
 
-    if (inside) {
+    if (warp == 0 && inside) {
         const size_t npix = (size_t)p.W * p.H;
         const size_t pid = (size_t)py * p.W + px;
         p.out_alpha[pid] = 1.0f - T;
@@ -181,7 +259,7 @@ __global__ void __launch_bounds__(32) composite_fwd_kernel(const FwdParams p) {
         p.out_scale[npix + pid] = S1;
         p.out_scale[2 * npix + pid] = S2;
     }
-    if (lane == 0) atomicMax(&p.tile_clocks[tile], (uint32_t)((clock64() - t_start) >> 10));
+    if (tid == 0) atomicMax(&p.tile_clocks[tile], (uint32_t)((clock64() - t_start) >> 10));
 }
 
 }  // namespace
@@ -201,8 +279,14 @@ int launch_composite_fwd(const VegsForwardArgs& a, const GeomView& g, const Scra
     p.n_contrib = im.n_contrib;
     p.tile_clocks = im.tile_clocks;
     const int T = p.gx * ((a.H + kTile - 1) / kTile);
+    static bool configured = false;
+    if (!configured) {
+        VEGS_CUDA_OK(cudaFuncSetAttribute(composite_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)sizeof(FwdSmem)));
+        configured = true;
+    }
     VEGS_CUDA_OK(cudaMemsetAsync(im.tile_clocks, 0, (size_t)2 * T * sizeof(uint32_t), stream));
-    composite_fwd_kernel<<<T * kUnitsPerTile, 32, 0, stream>>>(p);
+    composite_fwd_kernel<<<T * kUnitsPerTile, kSuper, sizeof(FwdSmem), stream>>>(p);
     VEGS_LAUNCH_CHECK("composite_fwd", stream, a.debug);
     return VEGS_OK;
 }
