@@ -125,7 +125,7 @@ class Workload:
             scale_modifier=1.0, viewmatrix=cam.viewmatrix, projmatrix=cam.projmatrix, sh_degree=3,
             campos=cam.campos, prefiltered=False, debug=False)
 
-    def step(self, mod, resident: bool):
+    def step(self, mod, resident: bool, reduce: bool = True):
         """One optimisation step's rasterizer work: local views fwd+bwd, stats, all-reduce."""
         p = self.params
         for t in p.values():
@@ -144,7 +144,7 @@ class Workload:
             loss.backward()
             stats.add_view(means2D.grad, radii)
             total = total + loss.detach()
-        if self.world > 1:
+        if self.world > 1 and reduce:
             self.flat = self.vdist.allreduce_step(p, stats, flat=self.flat)
         if not resident:
             return float(total.item())   # device -> host read of the step's result
@@ -234,6 +234,16 @@ def cpu_baseline_oracle(args, n_views_sample=1):
                        f"{int(1408 * args.scale)}x{int(376 * args.scale)}, oracle/vegs_oracle.c with OpenMP")
 
 
+def emit(line: dict) -> None:
+    """The ONE JSON line on the real stdout (everything else, e.g. NCCL's version banner, was
+    redirected to stderr at start-up)."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)   # anything a library prints to stdout goes to stderr
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -262,14 +272,15 @@ def main():
                     config=dict(workload=f"{args.P} Gaussians, {args.views}-view batch, CPU oracle port"),
                     cpu_baseline=cb, e2e=dict(value=cb["value"], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                     gpu_launches=0)
-        print(json.dumps(line)); return
+        emit(line); return
 
     assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU path)"
     device = torch.device("cuda", local_rank)
     torch.cuda.set_device(device)
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=device)
+        import datetime
+        dist.init_process_group("nccl", device_id=device, timeout=datetime.timedelta(seconds=180))
     from vegs_b200 import _lib
     wl = Workload(args, device, rank, world)
 
@@ -305,7 +316,7 @@ def main():
         # ---- roofline leg: per-kernel CUDA-event times from the library, byte model of SURVEY §8d
         peak, peak_src = peaks()
         _lib.profile_enable(True)
-        wl.step(mod, True)
+        wl.step(mod, True, reduce=False)      # rank 0 only: no collective in this extra step
         torch.cuda.synchronize(device)
         prof = _lib.profile_collect()
         _lib.profile_enable(False)
@@ -331,9 +342,10 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_oracle(args, 1)
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         import torch.distributed as dist
+        dist.barrier()
         dist.destroy_process_group()
 
 
