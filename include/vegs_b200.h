@@ -78,7 +78,9 @@ typedef struct VegsForwardArgs {
     /* scratch, free to release when the forward returns */
     void* scratch;        /* vegs_scratch_bytes(P) */
     void* bin_scratch;    /* vegs_bin_scratch_bytes(R,W,H); only needed by vegs_forward_render */
-    /* host word that receives num_rendered (asynchronously on `stream`; pinned memory) */
+    /* TWO host words (pinned memory), written asynchronously on `stream` by vegs_forward_prepare:
+     * [0] = num_rendered, [1] = number of emission work items.  Keep both untouched until
+     * vegs_forward_render has been called: it reads [1] on the host. */
     int32_t* num_rendered_host;
 } VegsForwardArgs;
 

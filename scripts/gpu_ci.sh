@@ -28,6 +28,11 @@ for s in $stages; do
       timeout 900 python bench.py --impl reference > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "bench_ref rc=$?" | tee -a gpurun_out/summary.txt ;;
     configs)
       timeout 1200 python scripts/bench_configs.py > gpurun_out/configs.json 2> gpurun_out/configs.err; echo "configs rc=$?" | tee -a gpurun_out/summary.txt ;;
+    ncu_pre)
+      CMD="python bench.py --P 6000000 --views 1 --steps 1 --warmup 1 --no-cpu-baseline"
+      timeout 600 $CMD > gpurun_out/ncu_plain.log 2>&1 &&
+      timeout 900 ncu --set full --clock-control none --import-source on -k regex:'preprocess_(fwd|bwd)_kernel|emit_kernel|radix_scatter' -s 6 -c 8 -o gpurun_out/prof_pre $CMD > gpurun_out/ncu_pre.log 2>&1
+      echo "ncu pre rc=$?" | tee -a gpurun_out/summary.txt ;;
     ncu)
       # launch list (cold-cache, serialised: compare shares) and one full capture of the top kernels;
       # the same command must have exited 0 without ncu first

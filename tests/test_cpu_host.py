@@ -71,14 +71,14 @@ def test_invalid_arguments_return_einval_not_abort():
     lib = _lib.load()
     a = _lib.VegsForwardArgs()
     a.P, a.W, a.H, a.D = 10, 0, 10, 3
-    word = ctypes.c_int32(-1)
+    word = (ctypes.c_int32 * 2)(-1, -1)
     a.num_rendered_host = ctypes.addressof(word)
     assert lib.vegs_forward_prepare(ctypes.byref(a), None) == 1
     assert b"bad sizes" in lib.vegs_last_error()
     a.W = 16
     assert lib.vegs_forward_prepare(ctypes.byref(a), None) == 1   # null required pointers
     a.P = 0
-    assert lib.vegs_forward_prepare(ctypes.byref(a), None) == 0 and word.value == 0
+    assert lib.vegs_forward_prepare(ctypes.byref(a), None) == 0 and word[0] == 0
     assert lib.vegs_dist2(5, None, None, None, 0, None) == 1
     assert lib.vegs_mark_visible(5, None, None, None, None, None) == 1
     with pytest.raises(ValueError):

@@ -130,7 +130,7 @@ extern "C" int vegs_forward_prepare(const VegsForwardArgs* a, void* stream_) {
     int rc = validate_common(a->P, a->D, a->M, a->W, a->H);
     if (rc) return rc;
     if (!a->num_rendered_host) { set_error("num_rendered_host is null"); return VEGS_EINVAL; }
-    if (a->P == 0) { *a->num_rendered_host = 0; return VEGS_OK; }
+    if (a->P == 0) { a->num_rendered_host[0] = 0; a->num_rendered_host[1] = 0; return VEGS_OK; }
     if (!a->means3D || !a->opacities || !a->viewmatrix || !a->projmatrix || !a->campos ||
         !a->radii || !a->geom || !a->scratch) {
         set_error("vegs_forward_prepare: a required pointer is null");
@@ -160,9 +160,10 @@ extern "C" int vegs_forward_prepare(const VegsForwardArgs* a, void* stream_) {
                           stream, a->debug != 0);
     if (rc) return rc;
     const uint32_t* order = second ? s.vals1 : s.vals0;
-    rc = launch_tile_count(a->P, order, s.rect, s.chunksum, g.counters, stream, a->debug != 0);
+    rc = launch_tile_count(a->P, order, s.rect, s.chunksum, s.partbase, g.counters, stream,
+                           a->debug != 0);
     if (rc) return rc;
-    VEGS_CUDA_OK(cudaMemcpyAsync(a->num_rendered_host, g.counters, sizeof(int32_t),
+    VEGS_CUDA_OK(cudaMemcpyAsync(a->num_rendered_host, g.counters, 2 * sizeof(int32_t),
                                  cudaMemcpyDeviceToHost, stream));
     prof_mark("num_rendered_d2h", stream);
     return VEGS_OK;
@@ -203,7 +204,12 @@ extern "C" int vegs_forward_render(const VegsForwardArgs* a, int32_t num_rendere
         if ((passes & 1) == 0) { v0 = b.point_list; v1 = bs.tvals1; }
         else { v0 = bs.tvals1; v1 = b.point_list; }
         const uint32_t* order = s.vals0;  // 4 depth passes: result is back in the first pair
-        rc = launch_emit(a->P, order, s.rect, s.chunksum, gx, k0, v0, R, stream, debug);
+        if (!a->num_rendered_host || a->num_rendered_host[0] != num_rendered) {
+            set_error("vegs_forward_render: num_rendered_host must still hold what vegs_forward_prepare wrote");
+            return VEGS_EINVAL;
+        }
+        const uint32_t nparts = (uint32_t)a->num_rendered_host[1];
+        rc = launch_emit(a->P, order, s.rect, s.chunksum, s.partbase, nparts, gx, k0, v0, R, stream, debug);
         if (rc) return rc;
         bool second = false;
         rc = radix_sort_pairs(k0, v0, k1, v1, false, R, nbits, bs.hist, bs.rowtot,

@@ -22,6 +22,7 @@ namespace vegs {
 namespace {
 
 constexpr int kEmitThreads = 256;
+constexpr uint32_t kEmitPart = 8192;   // instances emitted by one CTA
 constexpr int kEmitPerThread = kEmitChunk / kEmitThreads;  // 8
 
 __device__ __forceinline__ uint32_t rect_tiles(uint2 r) {
@@ -58,14 +59,51 @@ tile_count_kernel(int P, const uint32_t* __restrict__ order, const uint2* __rest
 }
 
 // Single block: in-place exclusive scan of chunksum[0..n), chunksum[n] = total = num_rendered.
+// Also the emission work list: chunk c is cut into ceil(instances / kEmitPart) parts so that a
+// chunk of near, screen-filling Gaussians (millions of instances) is emitted by many CTAs;
+// partbase[0..n] = exclusive scan of the part counts, counters[1] = total parts.
 __global__ void __launch_bounds__(1024)
-tile_spine_kernel(uint32_t* __restrict__ chunksum, uint32_t n,
+tile_spine_kernel(uint32_t* __restrict__ chunksum, uint32_t* __restrict__ partbase, uint32_t n,
                   uint32_t* __restrict__ num_rendered) {
     __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_carry;
+    __shared__ uint32_t s_pcarry;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) s_carry = 0;
+    if (threadIdx.x == 0) { s_carry = 0; s_pcarry = 0; }
     __syncthreads();
+    // pass 1: parts (needs the raw per-chunk counts, so it runs before they are overwritten)
+    for (uint32_t base = 0; base < n; base += 1024) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t v = (i < n) ? (chunksum[i] + kEmitPart - 1) / kEmitPart : 0u;
+        uint32_t inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t w = s_warp[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += t;
+            }
+            s_warp[lane] = w;
+        }
+        __syncthreads();
+        const uint32_t carry = s_pcarry;
+        const uint32_t woff = warp ? s_warp[warp - 1] : 0u;
+        if (i < n) partbase[i] = carry + woff + inc - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_pcarry = carry + woff + inc;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        partbase[n] = s_pcarry;
+        num_rendered[1] = s_pcarry;
+    }
     for (uint32_t base = 0; base < n; base += 1024) {
         const uint32_t i = base + threadIdx.x;
         const uint32_t v = (i < n) ? chunksum[i] : 0u;
@@ -96,23 +134,34 @@ tile_spine_kernel(uint32_t* __restrict__ chunksum, uint32_t n,
     }
     if (threadIdx.x == 0) {
         chunksum[n] = s_carry;
-        *num_rendered = s_carry;
+        num_rendered[0] = s_carry;
     }
 }
 
 __global__ void __launch_bounds__(kEmitThreads)
 emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__ rect,
-            const uint32_t* __restrict__ chunksum, int grid_x, uint32_t* __restrict__ tkeys,
+            const uint32_t* __restrict__ chunksum, const uint32_t* __restrict__ partbase,
+            uint32_t nchunks, int grid_x, uint32_t* __restrict__ tkeys,
             uint32_t* __restrict__ tvals, uint32_t R) {
     __shared__ uint32_t s_g[kEmitChunk];
     __shared__ uint2 s_rect[kEmitChunk];
     __shared__ uint32_t s_off[kEmitChunk + 1];
     __shared__ uint32_t s_warp[kEmitThreads / 32];
 
-    const uint32_t base = blockIdx.x * (uint32_t)kEmitChunk;
-    const uint32_t gbase = chunksum[blockIdx.x];
-    const uint32_t n_inst = chunksum[blockIdx.x + 1] - gbase;
-    if (n_inst == 0) return;
+    // which chunk does this part belong to: last c with partbase[c] <= blockIdx.x
+    uint32_t clo = 0, chi = nchunks;
+    while (chi - clo > 1) {
+        const uint32_t mid = (clo + chi) >> 1;
+        if (partbase[mid] <= blockIdx.x) clo = mid; else chi = mid;
+    }
+    const uint32_t chunk = clo;
+    const uint32_t part = blockIdx.x - partbase[chunk];
+    const uint32_t base = chunk * (uint32_t)kEmitChunk;
+    const uint32_t gbase = chunksum[chunk];
+    const uint32_t n_inst = chunksum[chunk + 1] - gbase;
+    const uint32_t i_begin = part * kEmitPart;
+    const uint32_t i_end = min(n_inst, i_begin + kEmitPart);
+    if (i_begin >= n_inst) return;
 
     // Thread t owns sorted positions base + 8t .. base + 8t + 7 (position order = depth order).
     uint32_t cnt[kEmitPerThread];
@@ -156,7 +205,7 @@ emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__
     __syncthreads();
 
     // One thread per instance.
-    for (uint32_t i = threadIdx.x; i < n_inst; i += kEmitThreads) {
+    for (uint32_t i = i_begin + threadIdx.x; i < i_end; i += kEmitThreads) {
         uint32_t lo = 0, hi = kEmitChunk;
         while (hi - lo > 1) {
             const uint32_t mid = (lo + hi) >> 1;
@@ -225,21 +274,22 @@ tile_order_kernel(const uint2* __restrict__ ranges, uint32_t T, uint32_t* __rest
 }  // namespace
 
 int launch_tile_count(int P, const uint32_t* order, const uint2* rect, uint32_t* chunksum,
-                      uint32_t* num_rendered_dev, cudaStream_t stream, bool debug) {
+                      uint32_t* partbase, uint32_t* num_rendered_dev, cudaStream_t stream, bool debug) {
     const uint32_t nchunks = div_up(P, kEmitChunk);
     tile_count_kernel<<<nchunks, kEmitThreads, 0, stream>>>(P, order, rect, chunksum);
     VEGS_LAUNCH_CHECK("tile_count", stream, debug);
-    tile_spine_kernel<<<1, 1024, 0, stream>>>(chunksum, nchunks, num_rendered_dev);
+    tile_spine_kernel<<<1, 1024, 0, stream>>>(chunksum, partbase, nchunks, num_rendered_dev);
     VEGS_LAUNCH_CHECK("tile_spine", stream, debug);
     return VEGS_OK;
 }
 
 int launch_emit(int P, const uint32_t* order, const uint2* rect, const uint32_t* chunksum,
-                int grid_x, uint32_t* tkeys, uint32_t* tvals, uint32_t R, cudaStream_t stream,
-                bool debug) {
+                const uint32_t* partbase, uint32_t nparts, int grid_x, uint32_t* tkeys,
+                uint32_t* tvals, uint32_t R, cudaStream_t stream, bool debug) {
     const uint32_t nchunks = div_up(P, kEmitChunk);
-    emit_kernel<<<nchunks, kEmitThreads, 0, stream>>>(P, order, rect, chunksum, grid_x, tkeys,
-                                                      tvals, R);
+    if (nparts == 0) return VEGS_OK;
+    emit_kernel<<<nparts, kEmitThreads, 0, stream>>>(P, order, rect, chunksum, partbase, nchunks,
+                                                     grid_x, tkeys, tvals, R);
     VEGS_LAUNCH_CHECK("emit", stream, debug);
     return VEGS_OK;
 }

@@ -31,7 +31,7 @@ def _pinned_word(device: torch.device, stream) -> torch.Tensor:
     key = (device.index, stream.cuda_stream)
     t = _pinned.get(key)
     if t is None:
-        t = torch.zeros(1, dtype=torch.int32).pin_memory()
+        t = torch.zeros(2, dtype=torch.int32).pin_memory()
         _pinned[key] = t
     return t
 
@@ -143,7 +143,7 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
         sp = C.c_void_p(stream.cuda_stream)
         _lib.check(lib.vegs_forward_prepare(C.byref(a), sp), "vegs_forward_prepare")
         stream.synchronize()  # the one host sync of the forward (reference: rasterizer_impl.cu:286)
-        R = int(word.item())
+        R = int(word[0].item())
         st.R = R
         if R > 0:
             st.binning = torch.empty(lib.vegs_binning_bytes(R), **u8)
