@@ -32,7 +32,8 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC",
-] + (["-DVEGS_TILE_DEBUG=1"] if os.environ.get("VEGS_TILE_DEBUG") == "1" else [])
+] + (["-DVEGS_TILE_DEBUG=1"] if os.environ.get("VEGS_TILE_DEBUG") == "1" else []) \
+  + os.environ.get("VEGS_NVCC_EXTRA", "").split()     # tuning sweeps, e.g. -DVEGS_FWD_SUPER=128
 
 
 def _nvcc() -> str:

@@ -19,7 +19,7 @@
 //   recA = { mean2D.x, mean2D.y, conic.a, conic.b }
 //   recB = { conic.c, opacity, half2(ex, ey), depth(view z) }   ex, ey: half extents of the box
 //                                                           outside which alpha < 1/255 (preprocess.cu)
-//   recC = { rgb.r, rgb.g, rgb.b, sin(theta) }             theta = acos(rot.r)
+//   recC = { rgb.r, rgb.g, rgb.b, 1/sin(theta) }            theta = acos(rot.r)
 //   recD = { scale.x, scale.y, scale.z, rot.r }            raw kernel inputs (no modifier)
 //   recE = { rot.x, rot.y, rot.z, theta }
 #pragma once
@@ -66,6 +66,7 @@ struct ScratchView {
     uint32_t* hist;      // kRadix * nblocks(P)
     uint32_t* rowtot;    // kRadix
     uint32_t* chunksum;  // nchunks(P) + 1
+    uint32_t* partbase;  // nchunks(P) + 1
     size_t bytes;
 };
 
@@ -126,6 +127,7 @@ static inline ScratchView scratch_view(void* base, int P) {
     v.hist = carve<uint32_t>(cur, (size_t)kRadix * div_up(n, kSortTile));
     v.rowtot = carve<uint32_t>(cur, kRadix);
     v.chunksum = carve<uint32_t>(cur, (size_t)div_up(n, kEmitChunk) + 1);
+    v.partbase = carve<uint32_t>(cur, (size_t)div_up(n, kEmitChunk) + 1);
     v.bytes = (size_t)(cur - reinterpret_cast<char*>(base));
     return v;
 }
@@ -218,10 +220,10 @@ int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t*
 
 // binning.cu
 int launch_tile_count(int P, const uint32_t* order, const uint2* rect, uint32_t* chunksum,
-                      uint32_t* num_rendered_dev, cudaStream_t stream, bool debug);
+                      uint32_t* partbase, uint32_t* num_rendered_dev, cudaStream_t stream, bool debug);
 int launch_emit(int P, const uint32_t* order, const uint2* rect, const uint32_t* chunksum,
-                int grid_x, uint32_t* tkeys, uint32_t* tvals, uint32_t R, cudaStream_t stream,
-                bool debug);
+                const uint32_t* partbase, uint32_t nparts, int grid_x, uint32_t* tkeys,
+                uint32_t* tvals, uint32_t R, cudaStream_t stream, bool debug);
 int launch_tile_ranges(uint32_t R, const uint32_t* tkeys_sorted, uint2* ranges,
                        uint32_t* tile_order, int T, cudaStream_t stream, bool debug);
 
