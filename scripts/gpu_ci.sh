@@ -28,6 +28,34 @@ for s in $stages; do
       timeout 900 python bench.py --impl reference > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "bench_ref rc=$?" | tee -a gpurun_out/summary.txt ;;
     configs)
       timeout 1200 python scripts/bench_configs.py > gpurun_out/configs.json 2> gpurun_out/configs.err; echo "configs rc=$?" | tee -a gpurun_out/summary.txt ;;
+    sweep)
+      # super-batch size of the compositing kernels (threads per CTA): rebuild and time each
+      for sz in ${VEGS_SWEEP:-128 64}; do
+        touch vegs_b200/csrc/composite_fwd.cu vegs_b200/csrc/composite_bwd.cu
+        VEGS_NVCC_EXTRA="-DVEGS_FWD_SUPER=$sz -DVEGS_BWD_SUPER=$sz" python vegs_b200/build.py > gpurun_out/sweep_build_$sz.log 2>&1
+        timeout 600 python bench.py --steps 6 --warmup 3 --no-cpu-baseline > gpurun_out/sweep_$sz.json 2> gpurun_out/sweep_$sz.err
+        echo "sweep $sz rc=$?" | tee -a gpurun_out/summary.txt
+        timeout 600 python -m pytest tests -m gpu -q -k "against_oracle or golden" -p no:cacheprovider > gpurun_out/sweep_pytest_$sz.log 2>&1
+        echo "sweep pytest $sz rc=$? $(tail -1 gpurun_out/sweep_pytest_$sz.log)" | tee -a gpurun_out/summary.txt
+      done
+      touch vegs_b200/csrc/composite_fwd.cu vegs_b200/csrc/composite_bwd.cu
+      python vegs_b200/build.py > gpurun_out/sweep_build_default.log 2>&1 ;;
+    exp)
+      # A/B of experimental compile-time switches in the compositing kernels
+      for flag in ${VEGS_EXP:-NOPIPE SIN2 ENDBAR}; do
+        touch vegs_b200/csrc/composite_fwd.cu vegs_b200/csrc/composite_bwd.cu
+        VEGS_NVCC_EXTRA="-DVEGS_EXP_$flag" python vegs_b200/build.py > gpurun_out/exp_build_$flag.log 2>&1
+        timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/exp_$flag.json 2> gpurun_out/exp_$flag.err
+        echo "exp $flag rc=$?" | tee -a gpurun_out/summary.txt
+      done
+      touch vegs_b200/csrc/composite_fwd.cu vegs_b200/csrc/composite_bwd.cu
+      python vegs_b200/build.py > gpurun_out/exp_build_default.log 2>&1 ;;
+    tilestats)
+      touch vegs_b200/csrc/composite_fwd.cu vegs_b200/csrc/composite_bwd.cu
+      VEGS_TILE_DEBUG=1 python vegs_b200/build.py > gpurun_out/dbg_build.log 2>&1
+      timeout 600 python scripts/tile_stats.py > gpurun_out/tile_stats.log 2>&1; echo "tilestats rc=$?" | tee -a gpurun_out/summary.txt
+      touch vegs_b200/csrc/composite_fwd.cu vegs_b200/csrc/composite_bwd.cu
+      python vegs_b200/build.py >> gpurun_out/dbg_build.log 2>&1 ;;
     ncu_pre)
       CMD="python bench.py --P 6000000 --views 1 --steps 1 --warmup 1 --no-cpu-baseline"
       timeout 600 $CMD > gpurun_out/ncu_plain.log 2>&1 &&

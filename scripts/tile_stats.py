@@ -52,6 +52,12 @@ print("tiles", T, "R", rl.sum(), "sum fwd Mcycles", f.sum() / 1e6, "sum bwd Mcyc
 print("top fwd tiles: (tile, row, len, maxcontrib, fwd max-unit Mcyc, bwd max-unit Mcyc, fwd cyc/entry)")
 for t in order[:12]:
     print(t, t // gx, rl[t], tmax[t], round(f[t] / 1e6, 2), round(b[t] / 1e6, 2), round(f[t] / max(rl[t], 1), 1))
+d = dbg.cpu().numpy().astype(np.int64).reshape(T, 8) * 1024
+if d.any():
+    print("phase Mcycles of unit 0 of the top tiles: fwd S0 S2 S3 S4 | bwd S0 pass1 pass2 S3")
+    for t in order[:12]:
+        print(t, rl[t], " ".join("%.2f" % (x / 1e6) for x in d[t, :4]), "|", " ".join("%.2f" % (x / 1e6) for x in d[t, 4:]))
+    print("all tiles:", " ".join("%.1f" % (x / 1e6) for x in d.sum(axis=0)))
 print("len percentiles", np.percentile(rl, [50, 90, 99, 100]))
 print("fwd cycles percentiles (M)", np.percentile(f, [50, 90, 99, 100]) / 1e6)
 print("bwd cycles percentiles (M)", np.percentile(b, [50, 90, 99, 100]) / 1e6)

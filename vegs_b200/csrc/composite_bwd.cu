@@ -8,16 +8,19 @@
 // global float atomics per (pixel, Gaussian) pair (backward.cu:612,654,682-691).  Here, per
 // super-batch (composite_common.cuh):
 //   S0  entry-parallel (256 threads, one entry each): the block pixels the entry contributes to
-//       (exact test inside the entry's conservative box) as a 32-bit hit mask, and each hit's alpha
+//       (exact test inside the entry's conservative box) as a 32-bit hit mask, each hit's alpha
+//       and v = <colour, depth, 1> . <dL/dpixel colour, depth, alpha>, the hit's value under the
+//       pixel's cotangent
 //   S1  each warp bit-transposes its 32 hit masks into per-pixel hit lists
-//   S2  warp 0, lane = pixel: the reference's sequential recurrences over that pixel's hits, back
-//       to front (T /= 1-alpha, accumulated colour / depth / alpha behind the hit); for every
-//       hit it leaves the two per-pair scalars that depend on that sequential state,
-//       w = alpha*T and dL/dalpha, in a 32 x 256 shared matrix
-//   S3  entry-parallel: thread t sums the ten gradient components of ITS entry over the pixels of
-//       its hit mask in registers (recomputing dx, dy, G from the records) and issues three 16-byte
-//       vector reductions (red.global.add.v4.f32, SASS REDG.E.ADD.F32x4) into the packed 48-byte
-//       per-Gaussian accumulator
+//   S2  the reference's sequential recurrences over a pixel's hits, back to front
+//       (T /= 1-alpha, and the colour / depth / alpha accumulated behind the hit, backward.cu:
+//       586-623).  The five accumulators share their coefficients, so under the cotangent they
+//       collapse into one scalar recurrence  A' = alpha*v + (1-alpha)*A  with
+//       dL/dalpha = T*(v - A) - T_final*<bg, dL/dcolour>/(1-alpha).  Both T and A are affine in
+//       their incoming value, so the 8 warps scan the 8 segments of the super-batch in parallel:
+//       pass 1 reduces every segment to (prod 1/(1-alpha), a, b) per pixel, pass 2 re-walks the
+//       segment from the composed incoming state and leaves w = alpha*T and dL/dalpha of every
+//       hit in a 32 x 256 shared matrix
 // so there are no per-pair atomics, no warp-shuffle reductions, the expensive parts are spread
 // over 8 warps per pixel block, and entries that touch none of the block's pixels cost one box
 // test.  Units are issued longest-list-first.
@@ -40,7 +43,10 @@ __device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float
                  : "memory");
 }
 
-constexpr int kSuper = 256;                 // entries per super-batch = threads per CTA
+#ifndef VEGS_BWD_SUPER
+#define VEGS_BWD_SUPER 256
+#endif
+constexpr int kSuper = VEGS_BWD_SUPER;      // entries per super-batch = threads per CTA
 constexpr int kWarps = kSuper / 32;
 
 struct BwdParams {
@@ -55,14 +61,23 @@ struct BwdParams {
     const float *dL_dcolor, *dL_ddepth, *dL_dalpha;
     float4* acc;
     uint32_t* tile_clocks;
+    uint32_t* tile_dbg;
 };
 
 struct BwdSmem {
-    float2 M[32 * kSuper];          // [pixel][slot]: (alpha, -) after S0, (alpha*T, dL/dalpha) after S2
-    float4 A[kSuper], B[kSuper], C[kSuper];
+    float2 M[32 * kSuper];          // [pixel][slot]: (alpha, v) after S0, (alpha*T, dL/dalpha) after S2
     float4 pix[32];                 // per pixel: dL/dcolor rgb, dL/ddepth
-    uint32_t bits[kWarps][32];      // [segment][pixel]: hits of the pixel inside the segment
+    float pixa[32];                 // per pixel: dL/dalpha map
+    float agg[kWarps][3][32];       // [segment][prod 1/(1-alpha), a, b][pixel]: A_out = a + b * A_in
 };
+
+#if VEGS_TILE_DEBUG
+#define PHASE_INIT long long ph_t = clock64(), ph_acc[4] = {0, 0, 0, 0}
+#define PHASE_MARK(k) { long long now_; asm volatile("mov.u64 %0, %%clock64;" : "=l"(now_) :: "memory"); ph_acc[k] += now_ - ph_t; ph_t = now_; }
+#else
+#define PHASE_INIT
+#define PHASE_MARK(k)
+#endif
 
 __global__ void __launch_bounds__(kSuper) composite_bwd_kernel(const BwdParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -78,7 +93,7 @@ __global__ void __launch_bounds__(kSuper) composite_bwd_kernel(const BwdParams p
     const int by0 = tile_y * kTile + (blk >> 1) * kUnitH;
     if (bx0 >= p.W || by0 >= p.H) return;
     const int bx1 = min(bx0 + kUnitW - 1, p.W - 1), by1 = min(by0 + kUnitH - 1, p.H - 1);
-    // lane = pixel (every warp computes it; the pixel state below is used by warp 0 only)
+    // lane = pixel (every warp computes it)
     const int px = bx0 + (lane & 7), py = by0 + (lane >> 3);
     const bool inside = px < p.W && py < p.H;
     const float pixfx = (float)px, pixfy = (float)py;
@@ -92,7 +107,6 @@ __global__ void __launch_bounds__(kSuper) composite_bwd_kernel(const BwdParams p
     const uint32_t* list = p.point_list + range.x;
 
     const float T_final = inside ? 1.0f - p.out_alpha[pid] : 0.0f;
-    float T = T_final;
     float dpix0 = 0.f, dpix1 = 0.f, dpix2 = 0.f, dpix_depth = 0.f, dpix_alpha = 0.f;
     if (inside) {
         if (p.dL_dcolor) {
@@ -103,13 +117,18 @@ __global__ void __launch_bounds__(kSuper) composite_bwd_kernel(const BwdParams p
         if (p.dL_ddepth) dpix_depth = p.dL_ddepth[pid];
         if (p.dL_dalpha) dpix_alpha = p.dL_dalpha[pid];
     }
-    if (warp == 0) sm.pix[lane] = make_float4(dpix0, dpix1, dpix2, dpix_depth);
-    const float bg_dot = p.bg[0] * dpix0 + p.bg[1] * dpix1 + p.bg[2] * dpix2;
+    if (warp == 0) {
+        sm.pix[lane] = make_float4(dpix0, dpix1, dpix2, dpix_depth);
+        sm.pixa[lane] = dpix_alpha;
+    }
+    __syncthreads();
+    const float bg_term = -T_final * (p.bg[0] * dpix0 + p.bg[1] * dpix1 + p.bg[2] * dpix2);
     const float ddelx_dx = 0.5f * p.W;
     const float ddely_dy = 0.5f * p.H;
 
-    float accum_rec0 = 0.f, accum_rec1 = 0.f, accum_rec2 = 0.f, accum_red = 0.f, accum_rea = 0.f;
-    float last_alpha = 0.f, last_c0 = 0.f, last_c1 = 0.f, last_c2 = 0.f, last_depth = 0.f;
+    // sequential state of the pixel, replicated in every warp: transmittance in front of the last
+    // processed hit and the cotangent-weighted accumulation behind it
+    float T_carry = T_final, A_carry = 0.0f;
 
     // slot t of the super-batch starting at `base` holds list entry n - 1 - (base + t): back to front
     const int e_first = n - 1 - tid;
@@ -118,65 +137,85 @@ __global__ void __launch_bounds__(kSuper) composite_bwd_kernel(const BwdParams p
     if (id_cur >= 0) { a_cur = ldg_f4(p.recA + id_cur); b_cur = ldg_f4(p.recB + id_cur); }
     int id_nxt = (e_first - kSuper >= 0) ? (int)list[e_first - kSuper] : -1;
 
+    PHASE_INIT;
     for (int base = 0; base < n; base += kSuper) {
         float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f), b_nxt = a_nxt;
         if (id_nxt >= 0) { a_nxt = ldg_f4(p.recA + id_nxt); b_nxt = ldg_f4(p.recB + id_nxt); }
         const int e_nn = n - 1 - (base + 2 * kSuper + tid);
         const int id_nn = (e_nn >= 0) ? (int)list[e_nn] : -1;
 
-        // ---- S0: thread = entry.  Hit mask over the unit's pixels, alpha of every hit.
+        // ---- S0: thread = entry.  Hit mask over the unit's pixels, (alpha, v) of every hit.
         uint32_t h = 0;
         if (id_cur >= 0)
-            h = entry_hits_alpha(a_cur, b_cur, bx0, by0, bx1, by1, reinterpret_cast<float*>(sm.M + tid), 2 * kSuper);
+            h = entry_hits_alpha(a_cur, b_cur, bx0, by0, bx1, by1, reinterpret_cast<float*>(sm.M), tid, kSuper, 2);
         if (h != 0u) {
-            sm.A[tid] = a_cur;
-            sm.B[tid] = b_cur;
-            sm.C[tid] = ldg_f4(p.recC + id_cur);
+            const float4 c = ldg_f4(p.recC + id_cur);
+            uint32_t bits = h;
+            while (bits != 0u) {
+                const int q = __ffs(bits) - 1;
+                bits &= bits - 1;
+                const float4 dp = sm.pix[q];
+                sm.M[q * kSuper + swz(tid, q)].y = c.x * dp.x + c.y * dp.y + c.z * dp.z + b_cur.w * dp.w + sm.pixa[q];
+            }
         }
         // ---- S1: per-pixel hit lists of this warp's 32-entry segment
-        sm.bits[warp][lane] = transpose32(h, lane);
+        const uint32_t mybits = transpose32(h, lane);
         const int any_hit = __syncthreads_or(h != 0u);
+        PHASE_MARK(0);
         if (any_hit) {
-            // ---- S2: warp 0, lane = pixel: the sequential recurrences, back to front
-            if (warp == 0) {
-                const int e_base = n - 1 - base;
+            // slot t holds list entry e_base - t; entries at or behind the pixel's last contributor
+            // do not take part (backward.cu:561-563): slots below t_min
+            const int s_min = (n - 1 - base) - (int)last_contributor + 1 - warp * 32;
+            const uint32_t valid = s_min <= 0 ? 0xffffffffu : (s_min >= 32 ? 0u : 0xffffffffu << s_min);
+            const float2* Mrow = sm.M + lane * kSuper + warp * 32;
+            // ---- S2 pass 1: warp = segment, lane = pixel: the segment as an affine map
+            {
+                float P = 1.0f, a = 0.0f, b = 1.0f;
+                uint32_t bits = mybits & valid;
+                while (bits != 0u) {
+                    const int sl = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    const float2 m = Mrow[swz(sl, lane)];
+                    const float om = 1.0f - m.x;
+                    P *= __frcp_rn(om);
+                    a = m.x * m.y + om * a;
+                    b *= om;
+                }
+                sm.agg[warp][0][lane] = P;
+                sm.agg[warp][1][lane] = a;
+                sm.agg[warp][2][lane] = b;
+            }
+            __syncthreads();
+            PHASE_MARK(1);
+            // ---- S2 pass 2: compose the segments in front of this one, then walk it for real
+            {
+                float T = T_carry, A = A_carry;
+#pragma unroll
                 for (int w = 0; w < kWarps; w++) {
-                    uint32_t bits = sm.bits[w][lane];
-                    while (bits != 0u) {
-                        const int t = w * 32 + __ffs(bits) - 1;
-                        bits &= bits - 1;
-                        float2* slot = &sm.M[lane * kSuper + t];
-                        const uint32_t e = (uint32_t)(e_base - t);
-                        float2 m = make_float2(0.f, 0.f);
-                        if (e < last_contributor) {   // else behind this pixel's last contributor (backward.cu:561-563)
-                            const float alpha = slot->x;
-                            const float4 c = sm.C[t];     // r, g, b, -
-                            const float depth = sm.B[t].w;
-                            T = T / (1.0f - alpha);
-                            const float wgt = alpha * T;
-                            float dL_dalpha = 0.0f;
-                            accum_rec0 = last_alpha * last_c0 + (1.f - last_alpha) * accum_rec0;
-                            accum_rec1 = last_alpha * last_c1 + (1.f - last_alpha) * accum_rec1;
-                            accum_rec2 = last_alpha * last_c2 + (1.f - last_alpha) * accum_rec2;
-                            last_c0 = c.x; last_c1 = c.y; last_c2 = c.z;
-                            dL_dalpha += (c.x - accum_rec0) * dpix0;
-                            dL_dalpha += (c.y - accum_rec1) * dpix1;
-                            dL_dalpha += (c.z - accum_rec2) * dpix2;
-                            accum_red = last_alpha * last_depth + (1.f - last_alpha) * accum_red;
-                            last_depth = depth;
-                            dL_dalpha += (depth - accum_red) * dpix_depth;
-                            accum_rea = last_alpha + (1.f - last_alpha) * accum_rea;
-                            dL_dalpha += (1.f - accum_rea) * dpix_alpha;
-                            dL_dalpha *= T;
-                            last_alpha = alpha;
-                            dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot;
-                            m = make_float2(wgt, dL_dalpha);
-                        }
-                        *slot = m;
+                    if (w == warp) { T = T_carry; A = A_carry; }
+                    T_carry *= sm.agg[w][0][lane];
+                    A_carry = sm.agg[w][1][lane] + sm.agg[w][2][lane] * A_carry;
+                }
+                float2* Mw = sm.M + lane * kSuper + warp * 32;
+                uint32_t bits = mybits;
+                while (bits != 0u) {
+                    const int sl = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    float2 out = make_float2(0.f, 0.f);
+                    if ((valid >> sl) & 1u) {
+                        const float2 m = Mw[swz(sl, lane)];   // alpha, v
+                        const float om = 1.0f - m.x;
+                        const float r = __frcp_rn(om);
+                        T *= r;                            // transmittance in front of this hit
+                        out.x = m.x * T;
+                        out.y = T * (m.y - A) + bg_term * r;
+                        A = m.x * m.y + om * A;
                     }
+                    Mw[swz(sl, lane)] = out;
                 }
             }
             __syncthreads();
+            PHASE_MARK(2);
             // ---- S3: thread = entry: sum the entry's gradient over the pixels it hit
             if (h != 0u) {
                 const float4 a = a_cur, bb = b_cur;
@@ -187,7 +226,7 @@ __global__ void __launch_bounds__(kSuper) composite_bwd_kernel(const BwdParams p
                 while (bits != 0u) {
                     const int q = __ffs(bits) - 1;
                     bits &= bits - 1;
-                    const float2 m = sm.M[q * kSuper + tid];
+                    const float2 m = sm.M[q * kSuper + swz(tid, q)];
                     if (m.x == 0.0f && m.y == 0.0f) continue;
                     any = true;
                     const float4 dp = sm.pix[q];
@@ -218,9 +257,14 @@ __global__ void __launch_bounds__(kSuper) composite_bwd_kernel(const BwdParams p
             }
         }
         __syncthreads();   // shared arrays are reused by the next super-batch
+        PHASE_MARK(3);
         id_cur = id_nxt; a_cur = a_nxt; b_cur = b_nxt; id_nxt = id_nn;
     }
     if (tid == 0) atomicMax(&p.tile_clocks[tile], (uint32_t)((clock64() - t_start) >> 10));
+#if VEGS_TILE_DEBUG
+    if (tid == 0 && blk == 0)
+        for (int k = 0; k < 4; k++) p.tile_dbg[tile * 8 + 4 + k] = (uint32_t)(ph_acc[k] >> 10);
+#endif
 }
 
 }  // namespace
@@ -241,6 +285,7 @@ int launch_composite_bwd(const VegsBackwardArgs& a, const GeomView& g, const Img
     p.acc = acc;
     const int T = p.gx * ((a.H + kTile - 1) / kTile);
     p.tile_clocks = const_cast<uint32_t*>(im.tile_clocks) + T;
+    p.tile_dbg = const_cast<uint32_t*>(im.tile_dbg);
     static bool configured = false;
     if (!configured) {
         VEGS_CUDA_OK(cudaFuncSetAttribute(composite_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

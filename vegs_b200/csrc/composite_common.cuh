@@ -1,19 +1,17 @@
 // Helpers shared by the forward and backward compositing kernels.
 //
-// Work decomposition of both kernels: the unit of work is one WARP = one 8x4 pixel block of a
-// 16x16 tile (8 blocks per tile).  A unit walks its tile's depth-sorted instance list in batches of
-// 32 entries and is independent of the other units, so there is no block-level barrier, heavy
-// tiles spread over 8 warps on up to 8 SMs, and units are issued longest-list-first.
-//
-// Per batch the warp alternates between two views of the same 32 x 32 problem:
-//   entry-parallel   lane t owns entry t: it loads the packed records, clips the Gaussian's
+// Work decomposition of both kernels: the unit of work is one 8x4 pixel block of a 16x16 tile
+// (8 blocks per tile), processed by one 8-warp CTA that walks the tile's depth-sorted instance list
+// in super-batches of 256 entries; units are independent and issued longest-list-first.
+// Per super-batch the CTA alternates between two views of the same problem:
+//   entry-parallel   thread t owns entry t: it loads the packed records, clips the Gaussian's
 //                    conservative box (half extents from the preprocess stage) to the block and
 //                    evaluates the reference's exact contribution test on the few pixels inside,
-//                    giving a 32-bit hit mask over the block's pixels;
+//                    giving a 32-bit hit mask over the block's pixels and each hit's alpha;
 //   pixel-parallel   after a 32x32 bit transpose through shuffles, lane p owns pixel p and visits
-//                    only its own hits, in list order, with the reference's sequential arithmetic.
+//                    only its own hits, in list order.
 // At LiDAR density a Gaussian touches a handful of the tile's 256 pixels, so this replaces
-// "32 lanes evaluate every entry" by "each entry is evaluated only where it can matter".
+// "every pixel thread evaluates every entry" by "each entry is evaluated only where it can matter".
 #pragma once
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
@@ -36,42 +34,23 @@ __device__ __forceinline__ uint32_t transpose32(uint32_t v, int lane) {
     return v;
 }
 
-// Hit mask of one entry over the block's 32 pixels (bit = (y - by0) * 8 + (x - bx0)).
+// Column of slot t in row `pix` of a [pixel][slot] shared matrix.  The pixel-parallel phases read
+// the matrix with lane = pixel, and neighbouring pixels mostly walk the same entries: without the
+// XOR all 32 lanes would hit one bank (row stride is a multiple of 32 words).  Entry-parallel
+// accesses (fixed pixel, consecutive slots) stay a permutation of the banks.
+__device__ __forceinline__ int swz(int t, int pix) { return t ^ pix; }
+
+// Hit mask of one entry (slot `slot` of the super-batch) over the block's 32 pixels; each hit's
+// alpha is stored at mat[(pixel * stride + swz(slot, pixel)) * words].
+// Mask layout: (bit = (y - by0) * 8 + (x - bx0)).
 // a = {x, y, conic.a, conic.b}, b = {conic.c, opacity, half2(ex, ey), depth}.
 // The test is the reference's (cuda_rasterizer/forward.cu:371-381): power <= 0 and
 // min(0.99, opacity * exp(power)) >= 1/255, in its float operation order (power as
 // fma(fma(A*dx, dx, (C*dy)*dy), -0.5, -((B*dx)*dy)), read from the reference's SASS).
 // Pixels outside the precomputed box cannot pass it, so they are not evaluated.
-__device__ __forceinline__ uint32_t entry_hits(const float4 a, const float4 b, int bx0, int by0,
-                                               int bx1, int by1) {
-    const uint32_t packed = __float_as_uint(b.z);
-    const float2 e = __half22float2(*reinterpret_cast<const __half2*>(&packed));
-    // clip the box to the block (bx0..bx1, by0..by1 inclusive, already clipped to the image);
-    // +inf extents keep the whole block, negative extents give an empty range
-    const int x0 = (int)ceilf(fmaxf(a.x - e.x, (float)bx0));
-    const int x1 = (int)floorf(fminf(a.x + e.x, (float)bx1));
-    const int y0 = (int)ceilf(fmaxf(a.y - e.y, (float)by0));
-    const int y1 = (int)floorf(fminf(a.y + e.y, (float)by1));
-    uint32_t hits = 0;
-    for (int y = y0; y <= y1; y++) {
-        const float dy = __fsub_rn(a.y, (float)y);
-        const float cyy = __fmul_rn(__fmul_rn(b.x, dy), dy);
-        for (int x = x0; x <= x1; x++) {
-            const float dx = __fsub_rn(a.x, (float)x);
-            const float sum = __fmaf_rn(__fmul_rn(a.z, dx), dx, cyy);
-            const float power = __fmaf_rn(sum, -0.5f, -__fmul_rn(__fmul_rn(a.w, dx), dy));
-            if (power > 0.0f) continue;
-            const float alpha = fminf(0.99f, __fmul_rn(b.y, expf(power)));
-            if (alpha < 1.0f / 255.0f) continue;
-            hits |= 1u << ((y - by0) * kUnitW + (x - bx0));
-        }
-    }
-    return hits;
-}
-
-// Same, and stores each hit's alpha at alpha_out[pixel * stride].
 __device__ __forceinline__ uint32_t entry_hits_alpha(const float4 a, const float4 b, int bx0, int by0,
-                                                     int bx1, int by1, float* alpha_out, int stride) {
+                                                     int bx1, int by1, float* mat, int slot, int stride,
+                                                     int words) {
     const uint32_t packed = __float_as_uint(b.z);
     const float2 e = __half22float2(*reinterpret_cast<const __half2*>(&packed));
     const int x0 = (int)ceilf(fmaxf(a.x - e.x, (float)bx0));
@@ -91,7 +70,7 @@ __device__ __forceinline__ uint32_t entry_hits_alpha(const float4 a, const float
             if (alpha < 1.0f / 255.0f) continue;
             const int pix = (y - by0) * kUnitW + (x - bx0);
             hits |= 1u << pix;
-            alpha_out[pix * stride] = alpha;
+            mat[(pix * stride + swz(slot, pix)) * words] = alpha;
         }
     }
     return hits;
