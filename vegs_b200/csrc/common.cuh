@@ -16,9 +16,10 @@
 //   bin_scratch (forward only)   tile keys ping-pong, value ping, hist
 //
 // Record contents (only written for Gaussians with radii > 0):
-//   recA = { mean2D.x, mean2D.y, conic.a, conic.b }
-//   recB = { conic.c, opacity, half2(ex, ey), depth(view z) }   ex, ey: half extents of the box
-//                                                           outside which alpha < 1/255 (preprocess.cu)
+//   recA = { mean2D.x, mean2D.y, half2(ex, ey), depth(view z) }   ex, ey: half extents of the box
+//                                                           outside which alpha < 1/255 (preprocess.cu);
+//                                                           all a compositing unit needs to reject an entry
+//   recB = { conic.a, conic.b, conic.c, opacity }
 //   recC = { rgb.r, rgb.g, rgb.b, 1/sin(theta) }            theta = acos(rot.r)
 //   recD = { scale.x, scale.y, scale.z, rot.r }            raw kernel inputs (no modifier)
 //   recE = { rot.x, rot.y, rot.z, theta }

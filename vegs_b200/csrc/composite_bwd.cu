@@ -1,13 +1,14 @@
 // Blend-stage backward.  One CTA of 8 warps per 8x4 pixel block ("unit"), 8 units per 16x16 tile;
-// a unit walks its tile's list back to front from the block's deepest contributor in super-batches
-// of 256 entries.
+// a unit walks its tile's list back to front from the block's deepest contributor.
 //
 // Replaces BACKWARD::render / renderCUDA (reference cuda_rasterizer/backward.cu:417-694).
 //
 // The reference lets all 256 pixel threads of a tile evaluate every list entry and issues >= 10
-// global float atomics per (pixel, Gaussian) pair (backward.cu:612,654,682-691).  Here, per
-// super-batch (composite_common.cuh):
-//   S0  entry-parallel (256 threads, one entry each): the block pixels the entry contributes to
+// global float atomics per (pixel, Gaussian) pair (backward.cu:612,654,682-691).  Here
+// (composite_common.cuh) the unit first SCANS the raw list, 256 entries per step, keeping the
+// entries whose conservative box reaches the block as candidates in a ring, and then, per working
+// set of 256 candidates:
+//   S0  entry-parallel (256 threads, one candidate each): the block pixels the entry contributes to
 //       (exact test inside the entry's conservative box) as a 32-bit hit mask, each hit's alpha
 //       and v = <colour, depth, 1> . <dL/dpixel colour, depth, alpha>, the hit's value under the
 //       pixel's cotangent
@@ -43,11 +44,9 @@ __device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float
                  : "memory");
 }
 
-#ifndef VEGS_BWD_SUPER
-#define VEGS_BWD_SUPER 256
-#endif
-constexpr int kSuper = VEGS_BWD_SUPER;      // entries per super-batch = threads per CTA
+constexpr int kSuper = 256;                 // candidates per working set = threads per CTA
 constexpr int kWarps = kSuper / 32;
+constexpr int kRing = 768;                  // candidate ring, 3 working sets
 
 struct BwdParams {
     const uint2* ranges;
@@ -69,6 +68,8 @@ struct BwdSmem {
     float4 pix[32];                 // per pixel: dL/dcolor rgb, dL/ddepth
     float pixa[32];                 // per pixel: dL/dalpha map
     float agg[kWarps][3][32];       // [segment][prod 1/(1-alpha), a, b][pixel]: A_out = a + b * A_in
+    uint2 ring[kRing];              // candidates, back to front: (Gaussian id, ordinal in the tile's list)
+    uint32_t scan_cnt[2][kWarps];   // survivors per warp of a scan step (double-buffered)
 };
 
 #if VEGS_TILE_DEBUG
@@ -79,7 +80,7 @@ struct BwdSmem {
 #define PHASE_MARK(k)
 #endif
 
-__global__ void __launch_bounds__(kSuper) composite_bwd_kernel(const BwdParams p) {
+__global__ void __launch_bounds__(kSuper, 3) composite_bwd_kernel(const BwdParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
 
@@ -96,7 +97,6 @@ __global__ void __launch_bounds__(kSuper) composite_bwd_kernel(const BwdParams p
     // lane = pixel (every warp computes it)
     const int px = bx0 + (lane & 7), py = by0 + (lane >> 3);
     const bool inside = px < p.W && py < p.H;
-    const float pixfx = (float)px, pixfy = (float)py;
     const size_t npix = (size_t)p.W * p.H;
     const size_t pid = (size_t)py * p.W + px;
 
@@ -130,43 +130,106 @@ __global__ void __launch_bounds__(kSuper) composite_bwd_kernel(const BwdParams p
     // processed hit and the cotangent-weighted accumulation behind it
     float T_carry = T_final, A_carry = 0.0f;
 
-    // slot t of the super-batch starting at `base` holds list entry n - 1 - (base + t): back to front
-    const int e_first = n - 1 - tid;
-    int id_cur = (e_first >= 0) ? (int)list[e_first] : -1;
-    float4 a_cur = make_float4(0.f, 0.f, 0.f, 0.f), b_cur = a_cur;
-    if (id_cur >= 0) { a_cur = ldg_f4(p.recA + id_cur); b_cur = ldg_f4(p.recB + id_cur); }
-    int id_nxt = (e_first - kSuper >= 0) ? (int)list[e_first - kSuper] : -1;
+    // raw-list pipeline of the scan (raw position r = list entry n - 1 - r: back to front):
+    // ids two steps ahead, box records one step ahead
+    int raw_base = 0;
+    int rid_cur = (n - 1 - tid >= 0) ? (int)list[n - 1 - tid] : -1;
+    float4 ra_cur = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (rid_cur >= 0) ra_cur = ldg_f4(p.recA + rid_cur);
+    int rid_nxt = (n - 1 - kSuper - tid >= 0) ? (int)list[n - 1 - kSuper - tid] : -1;
+    uint32_t head = 0, tail = 0;            // ring positions, same in every thread
+    int scan_par = 0;
+    // working-set pipeline: this thread's candidate of the next working set, when already queued
+    uint32_t pre_pos = 0xffffffffu;
+    uint2 pre_ent = make_uint2(0u, 0u);
+    float4 pre_a = make_float4(0.f, 0.f, 0.f, 0.f), pre_b = pre_a;
 
     PHASE_INIT;
-    for (int base = 0; base < n; base += kSuper) {
-        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f), b_nxt = a_nxt;
-        if (id_nxt >= 0) { a_nxt = ldg_f4(p.recA + id_nxt); b_nxt = ldg_f4(p.recB + id_nxt); }
-        const int e_nn = n - 1 - (base + 2 * kSuper + tid);
-        const int id_nn = (e_nn >= 0) ? (int)list[e_nn] : -1;
+    for (;;) {
+        // ---- SCAN: queue candidates until two working sets are ready or the list ends
+        bool scanned = false;
+        while (tail - head < 2u * kSuper && raw_base < n) {
+            float4 ra_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (rid_nxt >= 0) ra_nxt = ldg_f4(p.recA + rid_nxt);
+            const int e_nn = n - 1 - (raw_base + 2 * kSuper + tid);
+            const int rid_nn = (e_nn >= 0) ? (int)list[e_nn] : -1;
+            int x0, x1, y0, y1;
+            const bool keep = rid_cur >= 0 && unit_box(ra_cur, bx0, by0, bx1, by1, x0, x1, y0, y1);
+            const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+            if (lane == 0) sm.scan_cnt[scan_par][warp] = __popc(bal);
+            __syncthreads();
+            uint32_t before = 0, total = 0;
+#pragma unroll
+            for (int w = 0; w < kWarps; w++) {
+                const uint32_t c = sm.scan_cnt[scan_par][w];
+                before += (w < warp) ? c : 0u;
+                total += c;
+            }
+            if (keep)
+                sm.ring[(tail + before + __popc(bal & ((1u << lane) - 1u))) % kRing] =
+                    make_uint2((uint32_t)rid_cur, (uint32_t)(n - 1 - (raw_base + tid)));
+            tail += total;
+            raw_base += kSuper;
+            scan_par ^= 1;
+            scanned = true;
+            rid_cur = rid_nxt; ra_cur = ra_nxt; rid_nxt = rid_nn;
+        }
+        const int m = min((int)(tail - head), kSuper);
+        if (m == 0) break;                   // list exhausted, nothing queued
+        if (scanned) __syncthreads();        // ring entries of the last scan step
+        PHASE_MARK(0);
 
-        // ---- S0: thread = entry.  Hit mask over the unit's pixels, (alpha, v) of every hit.
+        // this thread's candidate: prefetched during the previous working set when it was queued by then
+        uint2 ent = make_uint2(0u, 0xffffffffu);
+        float4 a_cur = make_float4(0.f, 0.f, 0.f, 0.f), b_cur = a_cur;
+        if (tid < m) {
+            if (pre_pos == head + tid) {
+                ent = pre_ent; a_cur = pre_a; b_cur = pre_b;
+            } else {
+                ent = sm.ring[(head + tid) % kRing];
+                a_cur = ldg_f4(p.recA + ent.x);
+                b_cur = ldg_f4(p.recB + ent.x);
+            }
+        }
+        pre_pos = 0xffffffffu;
+        if (head + kSuper + tid < tail) {
+            pre_pos = head + kSuper + tid;
+            pre_ent = sm.ring[pre_pos % kRing];
+            pre_a = ldg_f4(p.recA + pre_ent.x);
+            pre_b = ldg_f4(p.recB + pre_ent.x);
+        }
+
+        // ---- S0: thread = candidate.  Hit mask over the unit's pixels, (alpha, v) of every hit.
         uint32_t h = 0;
-        if (id_cur >= 0)
+        if (tid < m)
             h = entry_hits_alpha(a_cur, b_cur, bx0, by0, bx1, by1, reinterpret_cast<float*>(sm.M), tid, kSuper, 2);
         if (h != 0u) {
-            const float4 c = ldg_f4(p.recC + id_cur);
+            const float4 c = ldg_f4(p.recC + ent.x);
             uint32_t bits = h;
             while (bits != 0u) {
                 const int q = __ffs(bits) - 1;
                 bits &= bits - 1;
                 const float4 dp = sm.pix[q];
-                sm.M[q * kSuper + swz(tid, q)].y = c.x * dp.x + c.y * dp.y + c.z * dp.z + b_cur.w * dp.w + sm.pixa[q];
+                sm.M[q * kSuper + swz(tid, q)].y = c.x * dp.x + c.y * dp.y + c.z * dp.z + a_cur.w * dp.w + sm.pixa[q];
             }
         }
         // ---- S1: per-pixel hit lists of this warp's 32-entry segment
         const uint32_t mybits = transpose32(h, lane);
         const int any_hit = __syncthreads_or(h != 0u);
-        PHASE_MARK(0);
+        PHASE_MARK(1);
         if (any_hit) {
-            // slot t holds list entry e_base - t; entries at or behind the pixel's last contributor
-            // do not take part (backward.cu:561-563): slots below t_min
-            const int s_min = (n - 1 - base) - (int)last_contributor + 1 - warp * 32;
-            const uint32_t valid = s_min <= 0 ? 0xffffffffu : (s_min >= 32 ? 0u : 0xffffffffu << s_min);
+            // entries at or behind the pixel's last contributor do not take part (backward.cu:
+            // 561-563).  Ordinals fall along the working set, so per pixel these are the first
+            // slots of the segment: binary search over the segment's ordinals (lane = slot)
+            const int my_ord = (int)ent.y;                    // -1 for an empty slot
+            int lo = 0, hi = 32;
+#pragma unroll
+            for (int it = 0; it < 6; it++) {           // 33 possible answers
+                const int mid = (lo + hi) >> 1;
+                const int v = __shfl_sync(0xffffffffu, my_ord, mid & 31);
+                if (lo < hi) { if (v >= (int)last_contributor) lo = mid + 1; else hi = mid; }
+            }
+            const uint32_t valid = lo >= 32 ? 0u : 0xffffffffu << lo;
             const float2* Mrow = sm.M + lane * kSuper + warp * 32;
             // ---- S2 pass 1: warp = segment, lane = pixel: the segment as an affine map
             {
@@ -186,7 +249,7 @@ __global__ void __launch_bounds__(kSuper) composite_bwd_kernel(const BwdParams p
                 sm.agg[warp][2][lane] = b;
             }
             __syncthreads();
-            PHASE_MARK(1);
+            PHASE_MARK(2);
             // ---- S2 pass 2: compose the segments in front of this one, then walk it for real
             {
                 float T = T_carry, A = A_carry;
@@ -236,11 +299,11 @@ __global__ void __launch_bounds__(kSuper) composite_bwd_kernel(const BwdParams p
                     const float wgt = m.x, dL_dalpha = m.y;
                     g_c0 += wgt * dp.x; g_c1 += wgt * dp.y; g_c2 += wgt * dp.z;
                     g_dep += wgt * dp.w;
-                    const float dL_dG = bb.y * dL_dalpha;
+                    const float dL_dG = bb.w * dL_dalpha;
                     const float gdx = G * dx;
                     const float gdy = G * dy;
-                    const float dG_ddelx = -gdx * a.z - gdy * a.w;
-                    const float dG_ddely = -gdy * bb.x - gdx * a.w;
+                    const float dG_ddelx = -gdx * bb.x - gdy * bb.y;
+                    const float dG_ddely = -gdy * bb.z - gdx * bb.y;
                     g_mx += dL_dG * dG_ddelx * ddelx_dx;
                     g_my += dL_dG * dG_ddely * ddely_dy;
                     g_cxx += -0.5f * gdx * dx * dL_dG;
@@ -249,16 +312,16 @@ __global__ void __launch_bounds__(kSuper) composite_bwd_kernel(const BwdParams p
                     g_op += G * dL_dalpha;
                 }
                 if (any) {
-                    float4* dst = p.acc + 3 * (size_t)id_cur;
+                    float4* dst = p.acc + 3 * (size_t)ent.x;
                     red_add_v4(dst + 0, g_mx, g_my, g_cxx, g_cxy);
                     red_add_v4(dst + 1, g_cyy, g_op, g_c0, g_c1);
                     red_add_v4(dst + 2, g_c2, g_dep, 0.0f, 0.0f);
                 }
             }
         }
-        __syncthreads();   // shared arrays are reused by the next super-batch
+        __syncthreads();   // shared arrays are reused by the next working set
         PHASE_MARK(3);
-        id_cur = id_nxt; a_cur = a_nxt; b_cur = b_nxt; id_nxt = id_nn;
+        head += (uint32_t)m;
     }
     if (tid == 0) atomicMax(&p.tile_clocks[tile], (uint32_t)((clock64() - t_start) >> 10));
 #if VEGS_TILE_DEBUG

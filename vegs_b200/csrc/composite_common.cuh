@@ -1,17 +1,21 @@
 // Helpers shared by the forward and backward compositing kernels.
 //
 // Work decomposition of both kernels: the unit of work is one 8x4 pixel block of a 16x16 tile
-// (8 blocks per tile), processed by one 8-warp CTA that walks the tile's depth-sorted instance list
-// in super-batches of 256 entries; units are independent and issued longest-list-first.
-// Per super-batch the CTA alternates between two views of the same problem:
-//   entry-parallel   thread t owns entry t: it loads the packed records, clips the Gaussian's
-//                    conservative box (half extents from the preprocess stage) to the block and
-//                    evaluates the reference's exact contribution test on the few pixels inside,
-//                    giving a 32-bit hit mask over the block's pixels and each hit's alpha;
+// (8 blocks per tile), processed by one 8-warp CTA that walks the tile's depth-sorted instance list;
+// units are independent and issued longest-list-first.  The CTA first SCANS the raw list 256
+// entries at a time (one 16-byte record per entry: clip the Gaussian's conservative box, half
+// extents from the preprocess stage, to the block) and appends the survivors, in list order, to a
+// ring of candidates; whenever 256 candidates are queued (or the list ends) it PROCESSES them as
+// one working set, alternating between two views of the same problem:
+//   entry-parallel   thread t owns candidate t: it evaluates the reference's exact contribution
+//                    test on the few pixels inside the clipped box, giving a 32-bit hit mask over
+//                    the block's pixels and each hit's alpha;
 //   pixel-parallel   after a 32x32 bit transpose through shuffles, lane p owns pixel p and visits
 //                    only its own hits, in list order.
 // At LiDAR density a Gaussian touches a handful of the tile's 256 pixels, so this replaces
-// "every pixel thread evaluates every entry" by "each entry is evaluated only where it can matter".
+// "every pixel thread evaluates every entry" by "each entry is evaluated only where it can matter",
+// and the per-working-set costs (barriers, the sequential pass) are paid per 256 candidates, not
+// per 256 list entries.
 #pragma once
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
@@ -40,10 +44,23 @@ __device__ __forceinline__ uint32_t transpose32(uint32_t v, int lane) {
 // accesses (fixed pixel, consecutive slots) stay a permutation of the banks.
 __device__ __forceinline__ int swz(int t, int pix) { return t ^ pix; }
 
-// Hit mask of one entry (slot `slot` of the super-batch) over the block's 32 pixels; each hit's
+// Clip an entry's conservative box to the unit's pixel block; false when nothing is left.
+// a = recA = {x, y, half2(ex, ey), depth}.
+__device__ __forceinline__ bool unit_box(const float4 a, int bx0, int by0, int bx1, int by1, int& x0,
+                                         int& x1, int& y0, int& y1) {
+    const uint32_t packed = __float_as_uint(a.z);
+    const float2 e = __half22float2(*reinterpret_cast<const __half2*>(&packed));
+    x0 = (int)ceilf(fmaxf(a.x - e.x, (float)bx0));
+    x1 = (int)floorf(fminf(a.x + e.x, (float)bx1));
+    y0 = (int)ceilf(fmaxf(a.y - e.y, (float)by0));
+    y1 = (int)floorf(fminf(a.y + e.y, (float)by1));
+    return x0 <= x1 && y0 <= y1;
+}
+
+// Hit mask of one entry (slot `slot` of the working set) over the block's 32 pixels; each hit's
 // alpha is stored at mat[(pixel * stride + swz(slot, pixel)) * words].
 // Mask layout: (bit = (y - by0) * 8 + (x - bx0)).
-// a = {x, y, conic.a, conic.b}, b = {conic.c, opacity, half2(ex, ey), depth}.
+// a = recA = {x, y, half2(ex, ey), depth}, b = recB = {conic.a, conic.b, conic.c, opacity}.
 // The test is the reference's (cuda_rasterizer/forward.cu:371-381): power <= 0 and
 // min(0.99, opacity * exp(power)) >= 1/255, in its float operation order (power as
 // fma(fma(A*dx, dx, (C*dy)*dy), -0.5, -((B*dx)*dy)), read from the reference's SASS).
@@ -51,22 +68,18 @@ __device__ __forceinline__ int swz(int t, int pix) { return t ^ pix; }
 __device__ __forceinline__ uint32_t entry_hits_alpha(const float4 a, const float4 b, int bx0, int by0,
                                                      int bx1, int by1, float* mat, int slot, int stride,
                                                      int words) {
-    const uint32_t packed = __float_as_uint(b.z);
-    const float2 e = __half22float2(*reinterpret_cast<const __half2*>(&packed));
-    const int x0 = (int)ceilf(fmaxf(a.x - e.x, (float)bx0));
-    const int x1 = (int)floorf(fminf(a.x + e.x, (float)bx1));
-    const int y0 = (int)ceilf(fmaxf(a.y - e.y, (float)by0));
-    const int y1 = (int)floorf(fminf(a.y + e.y, (float)by1));
+    int x0, x1, y0, y1;
+    if (!unit_box(a, bx0, by0, bx1, by1, x0, x1, y0, y1)) return 0u;
     uint32_t hits = 0;
     for (int y = y0; y <= y1; y++) {
         const float dy = __fsub_rn(a.y, (float)y);
-        const float cyy = __fmul_rn(__fmul_rn(b.x, dy), dy);
+        const float cyy = __fmul_rn(__fmul_rn(b.z, dy), dy);
         for (int x = x0; x <= x1; x++) {
             const float dx = __fsub_rn(a.x, (float)x);
-            const float sum = __fmaf_rn(__fmul_rn(a.z, dx), dx, cyy);
-            const float power = __fmaf_rn(sum, -0.5f, -__fmul_rn(__fmul_rn(a.w, dx), dy));
+            const float sum = __fmaf_rn(__fmul_rn(b.x, dx), dx, cyy);
+            const float power = __fmaf_rn(sum, -0.5f, -__fmul_rn(__fmul_rn(b.y, dx), dy));
             if (power > 0.0f) continue;
-            const float alpha = fminf(0.99f, __fmul_rn(b.y, expf(power)));
+            const float alpha = fminf(0.99f, __fmul_rn(b.w, expf(power)));
             if (alpha < 1.0f / 255.0f) continue;
             const int pix = (y - by0) * kUnitW + (x - bx0);
             hits |= 1u << pix;
@@ -76,13 +89,13 @@ __device__ __forceinline__ uint32_t entry_hits_alpha(const float4 a, const float
     return hits;
 }
 
-// power and alpha of one (pixel, entry) pair that is known to be a hit (same arithmetic as above)
+// power of one (pixel, entry) pair (same arithmetic as above)
 __device__ __forceinline__ float pair_power(const float4 a, const float4 b, float pixfx, float pixfy,
                                             float& dx, float& dy) {
     dx = __fsub_rn(a.x, pixfx);
     dy = __fsub_rn(a.y, pixfy);
-    const float sum = __fmaf_rn(__fmul_rn(a.z, dx), dx, __fmul_rn(__fmul_rn(b.x, dy), dy));
-    return __fmaf_rn(sum, -0.5f, -__fmul_rn(__fmul_rn(a.w, dx), dy));
+    const float sum = __fmaf_rn(__fmul_rn(b.x, dx), dx, __fmul_rn(__fmul_rn(b.z, dy), dy));
+    return __fmaf_rn(sum, -0.5f, -__fmul_rn(__fmul_rn(b.y, dx), dy));
 }
 
 __device__ __forceinline__ float4 ldg_f4(const float4* p) { return __ldg(p); }

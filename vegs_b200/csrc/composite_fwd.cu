@@ -1,5 +1,5 @@
 // Front-to-back alpha compositing.  One CTA of 8 warps per 8x4 pixel block ("unit"), 8 units per
-// 16x16 tile; a unit walks its tile's depth-sorted list in super-batches of 256 entries.
+// 16x16 tile; a unit walks its tile's depth-sorted list.
 //
 // Replaces FORWARD::render / renderCUDA (reference cuda_rasterizer/forward.cu:262-441), including
 // the VEGS additions: depth map, alpha map, accumulated covariance quaternion map (sequential
@@ -9,28 +9,34 @@
 // list entry.  At LiDAR density that is the wrong shape: the horizon tiles hold several 1e5 tiny
 // Gaussians, each touching a handful of pixels, and one block walks them while the other SMs
 // idle.  The only truly sequential part of compositing is the transmittance chain
-// T <- T * (1 - alpha) with its saturation test; everything else is parallel.  Per super-batch:
-//   S0  entry-parallel (256 threads, one entry each): clip the entry's conservative box
-//       (preprocess stage) to the unit's 32 pixels, run the reference's exact contribution test on
-//       the pixels inside, keep a 32-bit hit mask and each hit's alpha (alpha matrix in shared
-//       memory); entries with a hit stage their packed records
+// T <- T * (1 - alpha) with its saturation test; everything else is parallel.
+//   SCAN  256 raw list entries per step, one per thread: clip the entry's conservative box
+//         (preprocess stage, one 16-byte record) to the unit's 32 pixels; survivors are appended in
+//         list order to a ring of candidates (ballot + prefix over the 8 warps).  Repeated until
+//         two working sets are queued or the list ends.
+//   then, per working set of 256 candidates:
+//   S0  entry-parallel: run the reference's exact contribution test on the pixels inside the box,
+//       keep a 32-bit hit mask and each hit's alpha (alpha matrix in shared memory); entries with
+//       a hit stage their packed records
 //   S1  each warp bit-transposes its 32 hit masks into per-pixel hit lists
-//   S2  warp 0, lane = pixel: the sequential chain over that pixel's hits of the whole super-batch,
-//       in list order and in the reference's float operation order: T before each hit, the
+//   S2  warp 0, lane = pixel: the sequential chain over that pixel's hits of the working set, in
+//       list order and in the reference's float operation order: T before each hit, the
 //       saturation point (T(1-alpha) < 1e-4 stops the pixel, that Gaussian is not blended),
 //       n_contrib, plus the depth sum — a handful of instructions per hit
-//   S3  pixel-parallel per 32-entry segment (8 warps, lane = pixel): colour and scale sums and the
-//       slerp quaternion product of the segment's hits with the T values from S2
+//   S3  pixel-parallel per 32-candidate segment (8 warps, lane = pixel): colour and scale sums and
+//       the slerp quaternion product of the segment's hits with the T values from S2
 //   S4  warp 0 folds the eight segment partials into the pixel state, in list order
-// so the expensive work (exp, 2 sin + 4 div + quaternion product per contribution, box tests) is
-// spread over 8 warps per pixel block and 64 warps per tile, units are issued
-// longest-list-first, and a unit stops as soon as its 32 pixels are saturated.
+// so the expensive work (exp, sin, cos, quaternion product per contribution) is spread over 8
+// warps per pixel block and 64 warps per tile, the fixed costs of a working set are paid per 256
+// candidates rather than per 256 list entries, units are issued longest-list-first, and a unit
+// stops as soon as its 32 pixels are saturated.
 // Exactness: which Gaussians contribute to a pixel, alpha, T, n_contrib, depth and alpha map are
 // bit-identical to the reference (same float operations in the same order).  The colour / scale
-// sums and the quaternion product are associated per 32-entry segment instead of in one running
-// chain, a last-bit difference far inside the 1e-5 tolerance (values of magnitude <= 1).
-// Roofline: not HBM-bound (32 B per list entry per unit from L2, 48 B more per entry with a hit,
-// 52 B written per pixel); the bound is instruction issue of the per-hit blend and the box tests.
+// sums and the quaternion product are associated per 32-candidate segment instead of in one
+// running chain, a last-bit difference far inside the 1e-5 tolerance (values of magnitude <= 1).
+// Roofline: not HBM-bound (16 B per list entry per unit from L2, 16 B more per candidate, 48 B
+// more per entry with a hit, 52 B written per pixel); the bound is instruction issue of the
+// per-hit blend and the box tests.
 #include <cfloat>
 #include "common.cuh"
 #include "composite_common.cuh"
@@ -39,11 +45,9 @@ namespace vegs {
 
 namespace {
 
-#ifndef VEGS_FWD_SUPER
-#define VEGS_FWD_SUPER 256
-#endif
-constexpr int kSuper = VEGS_FWD_SUPER;      // entries per super-batch = threads per CTA
+constexpr int kSuper = 256;                 // candidates per working set = threads per CTA
 constexpr int kWarps = kSuper / 32;
+constexpr int kRing = 1024;                 // candidate ring (>= 3 * kSuper, power of two)
 
 struct FwdParams {
     const uint2* ranges;
@@ -59,12 +63,14 @@ struct FwdParams {
 };
 
 struct FwdSmem {
-    float alphaT[32 * kSuper];      // [pixel][slot]: alpha after S0, T-before-the-hit after S2
-    float4 A[kSuper], B[kSuper], C[kSuper], D[kSuper], E[kSuper];
+    float alphaT[32 * kSuper];      // [pixel][slot] (columns XOR-swizzled): alpha after S0, T after S2
+    float4 A[kSuper], B[kSuper], C[kSuper], D[kSuper], E[kSuper];   // records of candidates with a hit
+    uint2 ring[kRing];              // candidates in list order: (Gaussian id, ordinal in the tile's list)
     uint32_t bits[kWarps][32];      // [segment][pixel]: hits of the pixel inside the segment
     uint32_t stop_at[32];           // first slot the pixel does not blend any more (kSuper = none)
-    float part[kWarps][11][32];     // segment partials: rows 0-2 colour, 4-6 scale, 7-10 quaternion
+    float part[kWarps][10][32];     // segment partials: rows 0-2 colour, 3-5 scale, 6-9 quaternion
     uint32_t seg_any[kWarps];       // segment has at least one hit
+    uint32_t scan_cnt[2][kWarps];   // survivors per warp of a scan step (double-buffered)
     int all_done;
 };
 
@@ -107,28 +113,83 @@ __global__ void __launch_bounds__(kSuper) composite_fwd_kernel(const FwdParams p
     uint32_t last_contributor = 0;
     bool done = !inside;
 
-    // software pipeline over super-batches: records of the next one are loaded during this one
-    int id_cur = (tid < n) ? (int)list[tid] : -1;
-    float4 a_cur = make_float4(0.f, 0.f, 0.f, 0.f), b_cur = a_cur;
-    if (id_cur >= 0) { a_cur = ldg_f4(p.recA + id_cur); b_cur = ldg_f4(p.recB + id_cur); }
-    int id_nxt = (kSuper + tid < n) ? (int)list[kSuper + tid] : -1;
+    // raw-list pipeline of the scan: ids two steps ahead, box records one step ahead
+    int raw_base = 0;
+    int rid_cur = (tid < n) ? (int)list[tid] : -1;
+    float4 ra_cur = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (rid_cur >= 0) ra_cur = ldg_f4(p.recA + rid_cur);
+    int rid_nxt = (kSuper + tid < n) ? (int)list[kSuper + tid] : -1;
+    uint32_t head = 0, tail = 0;            // ring positions, same in every thread
+    int scan_par = 0;
+    // working-set pipeline: this thread's candidate of the next working set, when already queued
+    uint32_t pre_pos = 0xffffffffu;
+    uint2 pre_ent = make_uint2(0u, 0u);
+    float4 pre_a = make_float4(0.f, 0.f, 0.f, 0.f), pre_b = pre_a;
 
     PHASE_INIT;
-    for (int base = 0; base < n; base += kSuper) {
-        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f), b_nxt = a_nxt;
-        if (id_nxt >= 0) { a_nxt = ldg_f4(p.recA + id_nxt); b_nxt = ldg_f4(p.recB + id_nxt); }
-        const int nn = base + 2 * kSuper + tid;
-        const int id_nn = (nn < n) ? (int)list[nn] : -1;
+    for (;;) {
+        // ---- SCAN: queue candidates until two working sets are ready or the list ends
+        bool scanned = false;
+        while (tail - head < 2u * kSuper && raw_base < n) {
+            float4 ra_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (rid_nxt >= 0) ra_nxt = ldg_f4(p.recA + rid_nxt);
+            const int nn = raw_base + 2 * kSuper + tid;
+            const int rid_nn = (nn < n) ? (int)list[nn] : -1;
+            int x0, x1, y0, y1;
+            const bool keep = rid_cur >= 0 && unit_box(ra_cur, bx0, by0, bx1, by1, x0, x1, y0, y1);
+            const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+            if (lane == 0) sm.scan_cnt[scan_par][warp] = __popc(bal);
+            __syncthreads();
+            uint32_t before = 0, total = 0;
+#pragma unroll
+            for (int w = 0; w < kWarps; w++) {
+                const uint32_t c = sm.scan_cnt[scan_par][w];
+                before += (w < warp) ? c : 0u;
+                total += c;
+            }
+            if (keep)
+                sm.ring[(tail + before + __popc(bal & ((1u << lane) - 1u))) & (kRing - 1)] =
+                    make_uint2((uint32_t)rid_cur, (uint32_t)(raw_base + tid));
+            tail += total;
+            raw_base += kSuper;
+            scan_par ^= 1;
+            scanned = true;
+            rid_cur = rid_nxt; ra_cur = ra_nxt; rid_nxt = rid_nn;
+        }
+        const int m = min((int)(tail - head), kSuper);
+        if (m == 0) break;                   // list exhausted, nothing queued
+        if (scanned) __syncthreads();        // ring entries of the last scan step
+        PHASE_MARK(0);
 
-        // ---- S0: thread = entry.  Hit mask over the unit's pixels, alpha of every hit.
+        // this thread's candidate: prefetched during the previous working set when it was queued by then
+        uint2 ent = make_uint2(0u, 0u);
+        float4 a_cur = make_float4(0.f, 0.f, 0.f, 0.f), b_cur = a_cur;
+        if (tid < m) {
+            if (pre_pos == head + tid) {
+                ent = pre_ent; a_cur = pre_a; b_cur = pre_b;
+            } else {
+                ent = sm.ring[(head + tid) & (kRing - 1)];
+                a_cur = ldg_f4(p.recA + ent.x);
+                b_cur = ldg_f4(p.recB + ent.x);
+            }
+        }
+        pre_pos = 0xffffffffu;
+        if (head + kSuper + tid < tail) {
+            pre_pos = head + kSuper + tid;
+            pre_ent = sm.ring[pre_pos & (kRing - 1)];
+            pre_a = ldg_f4(p.recA + pre_ent.x);
+            pre_b = ldg_f4(p.recB + pre_ent.x);
+        }
+
+        // ---- S0: thread = candidate.  Hit mask over the unit's pixels, alpha of every hit.
         uint32_t h = 0;
-        if (id_cur >= 0) h = entry_hits_alpha(a_cur, b_cur, bx0, by0, bx1, by1, sm.alphaT, tid, kSuper, 1);
+        if (tid < m) h = entry_hits_alpha(a_cur, b_cur, bx0, by0, bx1, by1, sm.alphaT, tid, kSuper, 1);
         if (h != 0u) {
             sm.A[tid] = a_cur;
             sm.B[tid] = b_cur;
-            sm.C[tid] = ldg_f4(p.recC + id_cur);
-            sm.D[tid] = ldg_f4(p.recD + id_cur);
-            sm.E[tid] = ldg_f4(p.recE + id_cur);
+            sm.C[tid] = ldg_f4(p.recC + ent.x);
+            sm.D[tid] = ldg_f4(p.recD + ent.x);
+            sm.E[tid] = ldg_f4(p.recE + ent.x);
         }
         // ---- S1: per-pixel hit lists of this warp's 32-entry segment
         const uint32_t mybits = transpose32(h, lane);   // lane = pixel, bit = slot inside the segment
@@ -136,14 +197,13 @@ __global__ void __launch_bounds__(kSuper) composite_fwd_kernel(const FwdParams p
         const bool seg_any = __any_sync(0xffffffffu, h != 0u);
         if (lane == 0) sm.seg_any[warp] = seg_any ? 1u : 0u;
         __syncthreads();
-        PHASE_MARK(0);
+        PHASE_MARK(1);
 
-        // ---- S2: warp 0, lane = pixel: sequential transmittance chain over the super-batch
+        // ---- S2: warp 0, lane = pixel: sequential transmittance chain over the working set
         if (warp == 0) {
             uint32_t stop = kSuper;
             if (!done) {
-                // the pixel's hits of all segments as one stream; the next hit's operands are
-                // loaded before the current one is processed (the loop is latency-bound)
+                // the pixel's hits of all segments as one stream (the loop is latency-bound)
                 int w = 0;
                 uint32_t bits = sm.bits[0][lane];
                 auto next_hit = [&]() -> int {
@@ -153,28 +213,41 @@ __global__ void __launch_bounds__(kSuper) composite_fwd_kernel(const FwdParams p
                     bits &= bits - 1;
                     return t;
                 };
-                int t = next_hit();
-                float alpha = 0.f, depth = 0.f;
-                if (t >= 0) { alpha = sm.alphaT[lane * kSuper + swz(t, lane)]; depth = sm.B[t].w; }
-                while (t >= 0) {
-                    const int t2 = next_hit();
-                    float alpha2 = 0.f, depth2 = 0.f;
-                    if (t2 >= 0) { alpha2 = sm.alphaT[lane * kSuper + swz(t2, lane)]; depth2 = sm.B[t2].w; }
-                    const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
-                    if (test_T < 0.0001f) {      // not blended; the pixel is finished (forward.cu:382-386)
-                        done = true;
-                        stop = (uint32_t)t;
-                        break;
+                // four hits per round: their operands are fetched together, then the chain runs
+                int last_t = -1;
+                bool stopped = false;
+                for (;;) {
+                    int tt[4];
+                    float al[4], dp[4];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) tt[k] = next_hit();
+                    if (tt[0] < 0) break;
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        al[k] = 0.f; dp[k] = 0.f;
+                        if (tt[k] >= 0) { al[k] = sm.alphaT[lane * kSuper + swz(tt[k], lane)]; dp[k] = sm.A[tt[k]].w; }
                     }
-                    sm.alphaT[lane * kSuper + swz(t, lane)] = T;   // transmittance in front of this hit
-                    // depth is accumulated here, in the reference's running order, so it stays
-                    // bit-identical: depth values are ~1e2, re-associating that sum per segment
-                    // already costs more than the 1e-5 tolerance
-                    Dacc = __fmaf_rn(__fmul_rn(depth, alpha), T, Dacc);
-                    T = test_T;
-                    last_contributor = (uint32_t)(base + t) + 1u;   // ordinal in the tile's list
-                    t = t2; alpha = alpha2; depth = depth2;
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        if (tt[k] < 0 || stopped) continue;
+                        const float test_T = __fmul_rn(T, __fsub_rn(1.0f, al[k]));
+                        if (test_T < 0.0001f) {  // not blended; the pixel is finished (forward.cu:382-386)
+                            done = true;
+                            stopped = true;
+                            stop = (uint32_t)tt[k];
+                            continue;
+                        }
+                        sm.alphaT[lane * kSuper + swz(tt[k], lane)] = T;   // transmittance in front of this hit
+                        // depth is accumulated here, in the reference's running order, so it stays
+                        // bit-identical: depth values are ~1e2, re-associating that sum per segment
+                        // already costs more than the 1e-5 tolerance
+                        Dacc = __fmaf_rn(__fmul_rn(dp[k], al[k]), T, Dacc);
+                        T = test_T;
+                        last_t = tt[k];
+                    }
+                    if (stopped || tt[3] < 0) break;
                 }
+                if (last_t >= 0) last_contributor = sm.ring[(head + last_t) & (kRing - 1)].y + 1u;   // ordinal in the tile's list
             } else {
                 stop = 0u;
             }
@@ -183,7 +256,7 @@ __global__ void __launch_bounds__(kSuper) composite_fwd_kernel(const FwdParams p
             if (lane == 0) sm.all_done = all ? 1 : 0;
         }
         __syncthreads();
-        PHASE_MARK(1);
+        PHASE_MARK(2);
 
         // ---- S3: warp = segment, lane = pixel: blend terms of the segment's hits
         uint32_t seg_mask = 0;
@@ -199,11 +272,11 @@ __global__ void __launch_bounds__(kSuper) composite_fwd_kernel(const FwdParams p
                 const int t = warp * 32 + __ffs(bits) - 1;
                 bits &= bits - 1;
                 if ((uint32_t)t >= stop) break;
-                const float4 a = sm.A[t];    // x, y, conic.a, conic.b
-                const float4 bb = sm.B[t];   // conic.c, opacity, half2(ex, ey), depth
+                const float4 a = sm.A[t];    // x, y, half2(ex, ey), depth
+                const float4 bb = sm.B[t];   // conic.a, conic.b, conic.c, opacity
                 float dx, dy;
                 const float power = pair_power(a, bb, pixfx, pixfy, dx, dy);
-                const float alpha = fminf(0.99f, __fmul_rn(bb.y, expf(power)));
+                const float alpha = fminf(0.99f, __fmul_rn(bb.w, expf(power)));
                 const float Tb = sm.alphaT[lane * kSuper + swz(t, lane)];
                 const float4 c = sm.C[t];    // r, g, b, 1 / sin(theta)
                 const float4 d = sm.D[t];    // scale xyz, rot.r
@@ -245,21 +318,21 @@ __global__ void __launch_bounds__(kSuper) composite_fwd_kernel(const FwdParams p
             }
             float (*pp)[32] = sm.part[warp];
             pp[0][lane] = c0; pp[1][lane] = c1; pp[2][lane] = c2;
-            pp[4][lane] = s0; pp[5][lane] = s1; pp[6][lane] = s2;
-            pp[7][lane] = qw; pp[8][lane] = qx; pp[9][lane] = qy; pp[10][lane] = qz;
+            pp[3][lane] = s0; pp[4][lane] = s1; pp[5][lane] = s2;
+            pp[6][lane] = qw; pp[7][lane] = qx; pp[8][lane] = qy; pp[9][lane] = qz;
         }
         __syncthreads();
-        PHASE_MARK(2);
+        PHASE_MARK(3);
 
         // ---- S4: warp 0 folds the segment partials into the pixel state, in list order.  The other
-        // warps already start the next super-batch (they only write arrays S4 does not read).
+        // warps already start the next scan / working set (they only write arrays S4 does not read).
         if (warp == 0) {
             for (int w = 0; w < kWarps; w++) {
                 if (((seg_mask >> w) & 1u) == 0u) continue;
                 float (*pp)[32] = sm.part[w];
                 C0 += pp[0][lane]; C1 += pp[1][lane]; C2 += pp[2][lane];
-                S0 += pp[4][lane]; S1 += pp[5][lane]; S2 += pp[6][lane];
-                const float rw = pp[7][lane], rx = pp[8][lane], ry = pp[9][lane], rz = pp[10][lane];
+                S0 += pp[3][lane]; S1 += pp[4][lane]; S2 += pp[5][lane];
+                const float rw = pp[6][lane], rx = pp[7][lane], ry = pp[8][lane], rz = pp[9][lane];
                 const float nw = Qw * rw - Qx * rx - Qy * ry - Qz * rz;
                 const float nx = Qw * rx + Qx * rw + Qy * rz - Qz * ry;
                 const float ny = Qw * ry + Qy * rw + Qz * rx - Qx * rz;
@@ -267,9 +340,8 @@ __global__ void __launch_bounds__(kSuper) composite_fwd_kernel(const FwdParams p
                 Qw = nw; Qx = nx; Qy = ny; Qz = nz;
             }
         }
-        PHASE_MARK(3);
         if (finished) break;
-        id_cur = id_nxt; a_cur = a_nxt; b_cur = b_nxt; id_nxt = id_nn;
+        head += (uint32_t)m;
     }
 
     if (warp == 0 && inside) {

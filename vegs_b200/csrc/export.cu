@@ -25,24 +25,24 @@ __global__ void export_gaussians_kernel(int P, const int* __restrict__ radii,
     if (vis) { a = recA[i]; b = recB[i]; c = recC[i]; r = rect[i]; }
     if (tiles_touched)
         tiles_touched[i] = ((r.x >> 16) - (r.x & 0xffffu)) * ((r.y >> 16) - (r.y & 0xffffu));
-    if (depths) depths[i] = b.w;
+    if (depths) depths[i] = a.w;
     if (means2D) { means2D[2 * (size_t)i] = a.x; means2D[2 * (size_t)i + 1] = a.y; }
     if (conic_opacity) {
         float* o = conic_opacity + 4 * (size_t)i;
-        o[0] = a.z; o[1] = a.w; o[2] = b.x; o[3] = b.y;
+        o[0] = b.x; o[1] = b.y; o[2] = b.z; o[3] = b.w;
     }
     if (rgb) { float* o = rgb + 3 * (size_t)i; o[0] = c.x; o[1] = c.y; o[2] = c.z; }
 }
 
 __global__ void export_keys_kernel(const uint2* __restrict__ ranges,
                                    const uint32_t* __restrict__ point_list,
-                                   const float4* __restrict__ recB, uint64_t* __restrict__ keys,
+                                   const float4* __restrict__ recA, uint64_t* __restrict__ keys,
                                    uint32_t* __restrict__ list_out) {
     const uint32_t tile = blockIdx.x;
     const uint2 rg = ranges[tile];
     for (uint32_t i = rg.x + threadIdx.x; i < rg.y; i += blockDim.x) {
         const uint32_t g = point_list[i];
-        if (keys) keys[i] = ((uint64_t)tile << 32) | (uint64_t)__float_as_uint(recB[g].w);
+        if (keys) keys[i] = ((uint64_t)tile << 32) | (uint64_t)__float_as_uint(recA[g].w);
         if (list_out) list_out[i] = g;
     }
 }
@@ -62,7 +62,7 @@ int launch_export(const VegsForwardArgs& a, const GeomView& g, const ScratchView
         VEGS_LAUNCH_CHECK("export_gaussians", stream, true);
     }
     if (R > 0 && (keys || point_list)) {
-        export_keys_kernel<<<T, 256, 0, stream>>>(im.ranges, b.point_list, g.recB, keys,
+        export_keys_kernel<<<T, 256, 0, stream>>>(im.ranges, b.point_list, g.recA, keys,
                                                   point_list);
         VEGS_LAUNCH_CHECK("export_keys", stream, true);
     }

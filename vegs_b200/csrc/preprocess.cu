@@ -276,8 +276,8 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_fwd_kernel(const PrePa
             }
         }
         const __half2 eh = __floats2half2_rn(ex, ey);   // 1.002 above covers the 2^-11 rounding
-        p.recA[idx] = make_float4(pix_x, pix_y, conic.x, conic.y);
-        p.recB[idx] = make_float4(conic.z, opacity, __uint_as_float(*reinterpret_cast<const uint32_t*>(&eh)), depth);
+        p.recA[idx] = make_float4(pix_x, pix_y, __uint_as_float(*reinterpret_cast<const uint32_t*>(&eh)), depth);
+        p.recB[idx] = make_float4(conic.x, conic.y, conic.z, opacity);
         p.recC[idx] = make_float4(rgb.x, rgb.y, rgb.z, __fdiv_rn(1.0f, sinf(theta)));
         p.recD[idx] = d4;
         p.recE[idx] = e4;
