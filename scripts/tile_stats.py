@@ -54,7 +54,7 @@ for t in order[:12]:
     print(t, t // gx, rl[t], tmax[t], round(f[t] / 1e6, 2), round(b[t] / 1e6, 2), round(f[t] / max(rl[t], 1), 1))
 d = dbg.cpu().numpy().astype(np.int64).reshape(T, 8) * 1024
 if d.any():
-    print("phase Mcycles of unit 0 of the top tiles: fwd scan(+S4) S0 S2 S3 | bwd scan S0 S2(pass1+2) S3")
+    print("phase Mcycles of unit 0 of the top tiles: fwd scan(+S4) S0 S2 S3 | bwd S0 pass1 pass2 S3")
     for t in order[:12]:
         print(t, rl[t], " ".join("%.2f" % (x / 1e6) for x in d[t, :4]), "|", " ".join("%.2f" % (x / 1e6) for x in d[t, 4:]))
     print("all tiles:", " ".join("%.1f" % (x / 1e6) for x in d.sum(axis=0)))

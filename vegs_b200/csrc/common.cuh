@@ -42,6 +42,7 @@ constexpr int kRadixBits = 8;
 constexpr int kRadix = 1 << kRadixBits;
 
 // ---------------------------------------------------------------- emission configuration
+constexpr int kUnitsPerTile = 8;  // compositing units (8x4 pixel blocks) per 16x16 tile
 constexpr int kEmitChunk = 2048;  // depth-sorted Gaussians per emission block
 
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
@@ -73,6 +74,7 @@ struct ScratchView {
 
 struct ImgView {
     uint32_t* n_contrib;
+    uint32_t* last_hit;      // [W*H] 1 + index, in the pixel's unit hit list, of its last contributor
     uint2* ranges;
     uint32_t* tile_order;
     uint32_t* tile_clocks;   // [2*T] SM cycles/1024 spent on each tile by composite fwd / bwd (diagnostics)
@@ -82,6 +84,9 @@ struct ImgView {
 
 struct BinView {
     uint32_t* point_list;
+    uint2* hitlist;          // [8*R] per compositing unit: (Gaussian id, pixel hit mask) of the entries
+                             // that reached one of its pixels, in list order; unit (tile, blk) owns
+                             // [8*first + blk*len, +len) with (first, len) the tile's range
     size_t bytes;
 };
 
@@ -139,6 +144,7 @@ static inline ImgView img_view(void* base, int W, int H) {
     size_t npix = (size_t)W * H;
     size_t T = (size_t)((W + kTile - 1) / kTile) * ((H + kTile - 1) / kTile);
     v.n_contrib = carve<uint32_t>(cur, npix ? npix : 1);
+    v.last_hit = carve<uint32_t>(cur, npix ? npix : 1);
     v.ranges = carve<uint2>(cur, T ? T : 1);
     v.tile_order = carve<uint32_t>(cur, T ? T : 1);
     v.tile_clocks = carve<uint32_t>(cur, 2 * (T ? T : 1));
@@ -152,6 +158,7 @@ static inline BinView bin_view(void* base, int64_t R) {
     char* cur = reinterpret_cast<char*>(base);
     size_t n = (size_t)(R > 0 ? R : 1);
     v.point_list = carve<uint32_t>(cur, n);
+    v.hitlist = carve<uint2>(cur, (size_t)kUnitsPerTile * n);
     v.bytes = (size_t)(cur - reinterpret_cast<char*>(base));
     return v;
 }

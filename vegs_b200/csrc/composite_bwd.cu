@@ -1,30 +1,33 @@
-// Blend-stage backward.  One CTA of 8 warps per 8x4 pixel block ("unit"), 8 units per 16x16 tile;
-// a unit walks its tile's list back to front from the block's deepest contributor.
+// Blend-stage backward.  One CTA of 8 warps per 8x4 pixel block ("unit"), 8 units per 16x16 tile.
 //
 // Replaces BACKWARD::render / renderCUDA (reference cuda_rasterizer/backward.cu:417-694).
 //
 // The reference lets all 256 pixel threads of a tile evaluate every list entry and issues >= 10
-// global float atomics per (pixel, Gaussian) pair (backward.cu:612,654,682-691).  Here
-// (composite_common.cuh) the unit first SCANS the raw list, 256 entries per step, keeping the
-// entries whose conservative box reaches the block as candidates in a ring, and then, per working
-// set of 256 candidates:
-//   S0  entry-parallel (256 threads, one candidate each): the block pixels the entry contributes to
-//       (exact test inside the entry's conservative box) as a 32-bit hit mask, each hit's alpha
-//       and v = <colour, depth, 1> . <dL/dpixel colour, depth, alpha>, the hit's value under the
-//       pixel's cotangent
+// global float atomics per (pixel, Gaussian) pair (backward.cu:612,654,682-691).  Here the unit
+// walks ITS HIT LIST, written by the forward pass (composite_fwd.cu): the entries of the tile's
+// list that reached at least one of the unit's 32 pixels, with their pixel hit masks, in list
+// order.  It goes back to front from the deepest contributor of its pixels in working sets of 256
+// entries (composite_common.cuh):
+//   S0  entry-parallel (256 threads, one entry each): alpha of every hit of the entry (same float
+//       operations as the forward pass) and v = <colour, depth, 1> . <dL/dpixel colour, depth,
+//       alpha>, the hit's value under the pixel's cotangent
 //   S1  each warp bit-transposes its 32 hit masks into per-pixel hit lists
 //   S2  the reference's sequential recurrences over a pixel's hits, back to front
 //       (T /= 1-alpha, and the colour / depth / alpha accumulated behind the hit, backward.cu:
 //       586-623).  The five accumulators share their coefficients, so under the cotangent they
 //       collapse into one scalar recurrence  A' = alpha*v + (1-alpha)*A  with
 //       dL/dalpha = T*(v - A) - T_final*<bg, dL/dcolour>/(1-alpha).  Both T and A are affine in
-//       their incoming value, so the 8 warps scan the 8 segments of the super-batch in parallel:
+//       their incoming value, so the 8 warps scan the 8 segments of the working set in parallel:
 //       pass 1 reduces every segment to (prod 1/(1-alpha), a, b) per pixel, pass 2 re-walks the
 //       segment from the composed incoming state and leaves w = alpha*T and dL/dalpha of every
 //       hit in a 32 x 256 shared matrix
-// so there are no per-pair atomics, no warp-shuffle reductions, the expensive parts are spread
-// over 8 warps per pixel block, and entries that touch none of the block's pixels cost one box
-// test.  Units are issued longest-list-first.
+//   S3  entry-parallel: thread t sums the ten gradient components of ITS entry over the pixels of
+//       its hit mask in registers (recomputing dx, dy, G from the records) and issues three 16-byte
+//       vector reductions (red.global.add.v4.f32, SASS REDG.E.ADD.F32x4) into the packed 48-byte
+//       per-Gaussian accumulator
+// so there are no per-pair atomics, no warp-shuffle reductions, every phase is spread over the 8
+// warps of the pixel block, and entries that touch none of the block's pixels are never seen.
+// Units are issued longest-list-first.
 // The quaternion / scale-map cotangents are not propagated: the reference accumulates them into
 // buffers that its next kernel overwrites (backward.cu:624-647 vs :322-325,:340-341), so its
 // returned gradients do not contain them.
@@ -44,19 +47,18 @@ __device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float
                  : "memory");
 }
 
-constexpr int kSuper = 256;                 // candidates per working set = threads per CTA
+constexpr int kSuper = 256;                 // entries per working set = threads per CTA
 constexpr int kWarps = kSuper / 32;
-constexpr int kRing = 768;                  // candidate ring, 3 working sets
 
 struct BwdParams {
     const uint2* ranges;
-    const uint32_t* point_list;
+    const uint2* hitlist;
+    const uint32_t* last_hit;
     const uint32_t* tile_order;
     int W, H, gx;
     const float4 *recA, *recB, *recC;
     const float* bg;
     const float* out_alpha;
-    const uint32_t* n_contrib;
     const float *dL_dcolor, *dL_ddepth, *dL_dalpha;
     float4* acc;
     uint32_t* tile_clocks;
@@ -68,8 +70,6 @@ struct BwdSmem {
     float4 pix[32];                 // per pixel: dL/dcolor rgb, dL/ddepth
     float pixa[32];                 // per pixel: dL/dalpha map
     float agg[kWarps][3][32];       // [segment][prod 1/(1-alpha), a, b][pixel]: A_out = a + b * A_in
-    uint2 ring[kRing];              // candidates, back to front: (Gaussian id, ordinal in the tile's list)
-    uint32_t scan_cnt[2][kWarps];   // survivors per warp of a scan step (double-buffered)
 };
 
 #if VEGS_TILE_DEBUG
@@ -100,11 +100,12 @@ __global__ void __launch_bounds__(kSuper, 3) composite_bwd_kernel(const BwdParam
     const size_t npix = (size_t)p.W * p.H;
     const size_t pid = (size_t)py * p.W + px;
 
-    const uint32_t last_contributor = inside ? p.n_contrib[pid] : 0u;
-    const int n = (int)__reduce_max_sync(0xffffffffu, last_contributor);   // deepest contributor of the block
-    if (n == 0) return;                                                      // same value in every warp
+    // position (+1) of the pixel's last contributor in the unit's hit list
+    const uint32_t last_hit = inside ? p.last_hit[pid] : 0u;
+    const int n = (int)__reduce_max_sync(0xffffffffu, last_hit);   // deepest contributor of the block
+    if (n == 0) return;                                              // same value in every warp
     const uint2 range = p.ranges[tile];
-    const uint32_t* list = p.point_list + range.x;
+    const uint2* list = p.hitlist + ((size_t)kUnitsPerTile * range.x + (size_t)blk * (size_t)(range.y - range.x));
 
     const float T_final = inside ? 1.0f - p.out_alpha[pid] : 0.0f;
     float dpix0 = 0.f, dpix1 = 0.f, dpix2 = 0.f, dpix_depth = 0.f, dpix_alpha = 0.f;
@@ -130,106 +131,50 @@ __global__ void __launch_bounds__(kSuper, 3) composite_bwd_kernel(const BwdParam
     // processed hit and the cotangent-weighted accumulation behind it
     float T_carry = T_final, A_carry = 0.0f;
 
-    // raw-list pipeline of the scan (raw position r = list entry n - 1 - r: back to front):
-    // ids two steps ahead, box records one step ahead
-    int raw_base = 0;
-    int rid_cur = (n - 1 - tid >= 0) ? (int)list[n - 1 - tid] : -1;
-    float4 ra_cur = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (rid_cur >= 0) ra_cur = ldg_f4(p.recA + rid_cur);
-    int rid_nxt = (n - 1 - kSuper - tid >= 0) ? (int)list[n - 1 - kSuper - tid] : -1;
-    uint32_t head = 0, tail = 0;            // ring positions, same in every thread
-    int scan_par = 0;
-    // working-set pipeline: this thread's candidate of the next working set, when already queued
-    uint32_t pre_pos = 0xffffffffu;
-    uint2 pre_ent = make_uint2(0u, 0u);
-    float4 pre_a = make_float4(0.f, 0.f, 0.f, 0.f), pre_b = pre_a;
+    // slot t of the working set starting at `base` holds hit-list entry n - 1 - (base + t): back to
+    // front.  Software pipeline: the records of the next working set are loaded during this one.
+    uint2 ent = make_uint2(0u, 0u);          // (Gaussian id, hit mask); mask 0 = empty slot
+    float4 a_cur = make_float4(0.f, 0.f, 0.f, 0.f), b_cur = a_cur, c_cur = a_cur;
+    if (n - 1 - tid >= 0) {
+        ent = list[n - 1 - tid];
+        a_cur = ldg_f4(p.recA + ent.x); b_cur = ldg_f4(p.recB + ent.x); c_cur = ldg_f4(p.recC + ent.x);
+    }
 
     PHASE_INIT;
-    for (;;) {
-        // ---- SCAN: queue candidates until two working sets are ready or the list ends
-        bool scanned = false;
-        while (tail - head < 2u * kSuper && raw_base < n) {
-            float4 ra_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (rid_nxt >= 0) ra_nxt = ldg_f4(p.recA + rid_nxt);
-            const int e_nn = n - 1 - (raw_base + 2 * kSuper + tid);
-            const int rid_nn = (e_nn >= 0) ? (int)list[e_nn] : -1;
-            int x0, x1, y0, y1;
-            const bool keep = rid_cur >= 0 && unit_box(ra_cur, bx0, by0, bx1, by1, x0, x1, y0, y1);
-            const uint32_t bal = __ballot_sync(0xffffffffu, keep);
-            if (lane == 0) sm.scan_cnt[scan_par][warp] = __popc(bal);
-            __syncthreads();
-            uint32_t before = 0, total = 0;
-#pragma unroll
-            for (int w = 0; w < kWarps; w++) {
-                const uint32_t c = sm.scan_cnt[scan_par][w];
-                before += (w < warp) ? c : 0u;
-                total += c;
-            }
-            if (keep)
-                sm.ring[(tail + before + __popc(bal & ((1u << lane) - 1u))) % kRing] =
-                    make_uint2((uint32_t)rid_cur, (uint32_t)(n - 1 - (raw_base + tid)));
-            tail += total;
-            raw_base += kSuper;
-            scan_par ^= 1;
-            scanned = true;
-            rid_cur = rid_nxt; ra_cur = ra_nxt; rid_nxt = rid_nn;
-        }
-        const int m = min((int)(tail - head), kSuper);
-        if (m == 0) break;                   // list exhausted, nothing queued
-        if (scanned) __syncthreads();        // ring entries of the last scan step
-        PHASE_MARK(0);
-
-        // this thread's candidate: prefetched during the previous working set when it was queued by then
-        uint2 ent = make_uint2(0u, 0xffffffffu);
-        float4 a_cur = make_float4(0.f, 0.f, 0.f, 0.f), b_cur = a_cur;
-        if (tid < m) {
-            if (pre_pos == head + tid) {
-                ent = pre_ent; a_cur = pre_a; b_cur = pre_b;
-            } else {
-                ent = sm.ring[(head + tid) % kRing];
-                a_cur = ldg_f4(p.recA + ent.x);
-                b_cur = ldg_f4(p.recB + ent.x);
-            }
-        }
-        pre_pos = 0xffffffffu;
-        if (head + kSuper + tid < tail) {
-            pre_pos = head + kSuper + tid;
-            pre_ent = sm.ring[pre_pos % kRing];
-            pre_a = ldg_f4(p.recA + pre_ent.x);
-            pre_b = ldg_f4(p.recB + pre_ent.x);
+    for (int base = 0; base < n; base += kSuper) {
+        uint2 ent_nxt = make_uint2(0u, 0u);
+        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f), b_nxt = a_nxt, c_nxt = a_nxt;
+        const int i_nxt = n - 1 - (base + kSuper + tid);
+        if (i_nxt >= 0) {
+            ent_nxt = list[i_nxt];
+            a_nxt = ldg_f4(p.recA + ent_nxt.x); b_nxt = ldg_f4(p.recB + ent_nxt.x); c_nxt = ldg_f4(p.recC + ent_nxt.x);
         }
 
-        // ---- S0: thread = candidate.  Hit mask over the unit's pixels, (alpha, v) of every hit.
-        uint32_t h = 0;
-        if (tid < m)
-            h = entry_hits_alpha(a_cur, b_cur, bx0, by0, bx1, by1, reinterpret_cast<float*>(sm.M), tid, kSuper, 2);
-        if (h != 0u) {
-            const float4 c = ldg_f4(p.recC + ent.x);
+        // ---- S0: thread = entry.  (alpha, v) of every hit; the forward pass found the hits, the
+        // same float operations reproduce their alpha.
+        const uint32_t h = ent.y;
+        {
             uint32_t bits = h;
             while (bits != 0u) {
                 const int q = __ffs(bits) - 1;
                 bits &= bits - 1;
+                float dx, dy;
+                const float power = pair_power(a_cur, b_cur, (float)(bx0 + (q & 7)), (float)(by0 + (q >> 3)), dx, dy);
+                const float alpha = fminf(0.99f, __fmul_rn(b_cur.w, expf(power)));
                 const float4 dp = sm.pix[q];
-                sm.M[q * kSuper + swz(tid, q)].y = c.x * dp.x + c.y * dp.y + c.z * dp.z + a_cur.w * dp.w + sm.pixa[q];
+                sm.M[q * kSuper + swz(tid, q)] =
+                    make_float2(alpha, c_cur.x * dp.x + c_cur.y * dp.y + c_cur.z * dp.z + a_cur.w * dp.w + sm.pixa[q]);
             }
         }
         // ---- S1: per-pixel hit lists of this warp's 32-entry segment
         const uint32_t mybits = transpose32(h, lane);
         const int any_hit = __syncthreads_or(h != 0u);
-        PHASE_MARK(1);
+        PHASE_MARK(0);
         if (any_hit) {
-            // entries at or behind the pixel's last contributor do not take part (backward.cu:
-            // 561-563).  Ordinals fall along the working set, so per pixel these are the first
-            // slots of the segment: binary search over the segment's ordinals (lane = slot)
-            const int my_ord = (int)ent.y;                    // -1 for an empty slot
-            int lo = 0, hi = 32;
-#pragma unroll
-            for (int it = 0; it < 6; it++) {           // 33 possible answers
-                const int mid = (lo + hi) >> 1;
-                const int v = __shfl_sync(0xffffffffu, my_ord, mid & 31);
-                if (lo < hi) { if (v >= (int)last_contributor) lo = mid + 1; else hi = mid; }
-            }
-            const uint32_t valid = lo >= 32 ? 0u : 0xffffffffu << lo;
+            // slot t holds hit-list entry n - 1 - base - t; entries behind the pixel's last
+            // contributor do not take part (backward.cu:561-563): the first slots of the set
+            const int s_min = (n - 1 - base) - (int)last_hit + 1 - warp * 32;
+            const uint32_t valid = s_min <= 0 ? 0xffffffffu : (s_min >= 32 ? 0u : 0xffffffffu << s_min);
             const float2* Mrow = sm.M + lane * kSuper + warp * 32;
             // ---- S2 pass 1: warp = segment, lane = pixel: the segment as an affine map
             {
@@ -249,7 +194,7 @@ __global__ void __launch_bounds__(kSuper, 3) composite_bwd_kernel(const BwdParam
                 sm.agg[warp][2][lane] = b;
             }
             __syncthreads();
-            PHASE_MARK(2);
+            PHASE_MARK(1);
             // ---- S2 pass 2: compose the segments in front of this one, then walk it for real
             {
                 float T = T_carry, A = A_carry;
@@ -321,7 +266,7 @@ __global__ void __launch_bounds__(kSuper, 3) composite_bwd_kernel(const BwdParam
         }
         __syncthreads();   // shared arrays are reused by the next working set
         PHASE_MARK(3);
-        head += (uint32_t)m;
+        ent = ent_nxt; a_cur = a_nxt; b_cur = b_nxt; c_cur = c_nxt;
     }
     if (tid == 0) atomicMax(&p.tile_clocks[tile], (uint32_t)((clock64() - t_start) >> 10));
 #if VEGS_TILE_DEBUG
@@ -336,14 +281,14 @@ int launch_composite_bwd(const VegsBackwardArgs& a, const GeomView& g, const Img
                          const BinView& b, float4* acc, cudaStream_t stream) {
     BwdParams p;
     p.ranges = im.ranges;
-    p.point_list = b.point_list;
+    p.hitlist = b.hitlist;
     p.tile_order = im.tile_order;
     p.W = a.W; p.H = a.H;
     p.gx = (a.W + kTile - 1) / kTile;
     p.recA = g.recA; p.recB = g.recB; p.recC = g.recC;
     p.bg = a.background;
     p.out_alpha = a.out_alpha;
-    p.n_contrib = im.n_contrib;
+    p.last_hit = im.last_hit;
     p.dL_dcolor = a.dL_dout_color; p.dL_ddepth = a.dL_dout_depth; p.dL_dalpha = a.dL_dout_alpha;
     p.acc = acc;
     const int T = p.gx * ((a.H + kTile - 1) / kTile);

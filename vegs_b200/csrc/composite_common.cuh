@@ -20,11 +20,11 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "common.cuh"
 
 namespace vegs {
 
 constexpr int kUnitW = 8, kUnitH = 4;          // pixel block of one warp
-constexpr int kUnitsPerTile = 8;
 
 // 32x32 bit-matrix transpose across the warp: bit t of the result in lane p = bit p of v in lane t.
 __device__ __forceinline__ uint32_t transpose32(uint32_t v, int lane) {

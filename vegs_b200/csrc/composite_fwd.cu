@@ -58,6 +58,8 @@ struct FwdParams {
     const float* bg;
     float *out_color, *out_depth, *out_quat, *out_scale, *out_alpha;
     uint32_t* n_contrib;
+    uint32_t* last_hit;
+    uint2* hitlist;
     uint32_t* tile_clocks;
     uint32_t* tile_dbg;
 };
@@ -69,7 +71,7 @@ struct FwdSmem {
     uint32_t bits[kWarps][32];      // [segment][pixel]: hits of the pixel inside the segment
     uint32_t stop_at[32];           // first slot the pixel does not blend any more (kSuper = none)
     float part[kWarps][10][32];     // segment partials: rows 0-2 colour, 3-5 scale, 6-9 quaternion
-    uint32_t seg_any[kWarps];       // segment has at least one hit
+    uint32_t seg_bal[kWarps];       // per segment: ballot of the slots with a hit
     uint32_t scan_cnt[2][kWarps];   // survivors per warp of a scan step (double-buffered)
     int all_done;
 };
@@ -82,7 +84,7 @@ struct FwdSmem {
 #define PHASE_MARK(k)
 #endif
 
-__global__ void __launch_bounds__(kSuper) composite_fwd_kernel(const FwdParams p) {
+__global__ void __launch_bounds__(kSuper, 3) composite_fwd_kernel(const FwdParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     FwdSmem& sm = *reinterpret_cast<FwdSmem*>(smem_raw);
 
@@ -110,8 +112,11 @@ __global__ void __launch_bounds__(kSuper) composite_fwd_kernel(const FwdParams p
     float C0 = 0.f, C1 = 0.f, C2 = 0.f, Dacc = 0.f;
     float S0 = 0.f, S1 = 0.f, S2 = 0.f;
     float Qw = 1.f, Qx = 0.f, Qy = 0.f, Qz = 0.f;
-    uint32_t last_contributor = 0;
+    uint32_t last_contributor = 0, last_hit = 0;
     bool done = !inside;
+    // entries with a hit are appended, in list order, to the unit's hit list for the backward pass
+    uint2* hitlist = p.hitlist + ((size_t)kUnitsPerTile * range.x + (size_t)blk * (size_t)n);
+    uint32_t hit_count = 0;
 
     // raw-list pipeline of the scan: ids two steps ahead, box records one step ahead
     int raw_base = 0;
@@ -194,10 +199,22 @@ __global__ void __launch_bounds__(kSuper) composite_fwd_kernel(const FwdParams p
         // ---- S1: per-pixel hit lists of this warp's 32-entry segment
         const uint32_t mybits = transpose32(h, lane);   // lane = pixel, bit = slot inside the segment
         sm.bits[warp][lane] = mybits;
-        const bool seg_any = __any_sync(0xffffffffu, h != 0u);
-        if (lane == 0) sm.seg_any[warp] = seg_any ? 1u : 0u;
+        const uint32_t hit_bal = __ballot_sync(0xffffffffu, h != 0u);
+        if (lane == 0) sm.seg_bal[warp] = hit_bal;
         __syncthreads();
         PHASE_MARK(1);
+        uint32_t seg_mask = 0, hits_before = 0, hits_total = 0;
+#pragma unroll
+        for (int w = 0; w < kWarps; w++) {
+            const uint32_t c = __popc(sm.seg_bal[w]);
+            seg_mask |= (c != 0u ? 1u : 0u) << w;
+            hits_before += (w < warp) ? c : 0u;
+            hits_total += c;
+        }
+        if (h != 0u)
+            hitlist[hit_count + hits_before + __popc(hit_bal & ((1u << lane) - 1u))] = make_uint2(ent.x, h);
+        const uint32_t hit_base = hit_count;
+        hit_count += hits_total;
 
         // ---- S2: warp 0, lane = pixel: sequential transmittance chain over the working set
         if (warp == 0) {
@@ -216,38 +233,41 @@ __global__ void __launch_bounds__(kSuper) composite_fwd_kernel(const FwdParams p
                 // four hits per round: their operands are fetched together, then the chain runs
                 int last_t = -1;
                 bool stopped = false;
+                auto load_hit = [&](int t, float& al, float& dp) {
+                    al = 0.f; dp = 0.f;
+                    if (t >= 0) { al = sm.alphaT[lane * kSuper + swz(t, lane)]; dp = sm.A[t].w; }
+                };
+                auto chain = [&](int t, float al, float dp) {
+                    if (t < 0 || stopped) return;
+                    const float test_T = __fmul_rn(T, __fsub_rn(1.0f, al));
+                    if (test_T < 0.0001f) {      // not blended; the pixel is finished (forward.cu:382-386)
+                        done = true;
+                        stopped = true;
+                        stop = (uint32_t)t;
+                        return;
+                    }
+                    sm.alphaT[lane * kSuper + swz(t, lane)] = T;   // transmittance in front of this hit
+                    // depth is accumulated here, in the reference's running order, so it stays
+                    // bit-identical: depth values are ~1e2, re-associating that sum per segment
+                    // already costs more than the 1e-5 tolerance
+                    Dacc = __fmaf_rn(__fmul_rn(dp, al), T, Dacc);
+                    T = test_T;
+                    last_t = t;
+                };
                 for (;;) {
-                    int tt[4];
-                    float al[4], dp[4];
-#pragma unroll
-                    for (int k = 0; k < 4; k++) tt[k] = next_hit();
-                    if (tt[0] < 0) break;
-#pragma unroll
-                    for (int k = 0; k < 4; k++) {
-                        al[k] = 0.f; dp[k] = 0.f;
-                        if (tt[k] >= 0) { al[k] = sm.alphaT[lane * kSuper + swz(tt[k], lane)]; dp[k] = sm.A[tt[k]].w; }
-                    }
-#pragma unroll
-                    for (int k = 0; k < 4; k++) {
-                        if (tt[k] < 0 || stopped) continue;
-                        const float test_T = __fmul_rn(T, __fsub_rn(1.0f, al[k]));
-                        if (test_T < 0.0001f) {  // not blended; the pixel is finished (forward.cu:382-386)
-                            done = true;
-                            stopped = true;
-                            stop = (uint32_t)tt[k];
-                            continue;
-                        }
-                        sm.alphaT[lane * kSuper + swz(tt[k], lane)] = T;   // transmittance in front of this hit
-                        // depth is accumulated here, in the reference's running order, so it stays
-                        // bit-identical: depth values are ~1e2, re-associating that sum per segment
-                        // already costs more than the 1e-5 tolerance
-                        Dacc = __fmaf_rn(__fmul_rn(dp[k], al[k]), T, Dacc);
-                        T = test_T;
-                        last_t = tt[k];
-                    }
-                    if (stopped || tt[3] < 0) break;
+                    const int t0 = next_hit(), t1 = next_hit(), t2 = next_hit(), t3 = next_hit();
+                    if (t0 < 0) break;
+                    float al0, al1, al2, al3, dp0, dp1, dp2, dp3;
+                    load_hit(t0, al0, dp0); load_hit(t1, al1, dp1); load_hit(t2, al2, dp2); load_hit(t3, al3, dp3);
+                    chain(t0, al0, dp0); chain(t1, al1, dp1); chain(t2, al2, dp2); chain(t3, al3, dp3);
+                    if (stopped || t3 < 0) break;
                 }
-                if (last_t >= 0) last_contributor = sm.ring[(head + last_t) & (kRing - 1)].y + 1u;   // ordinal in the tile's list
+                if (last_t >= 0) {
+                    last_contributor = sm.ring[(head + last_t) & (kRing - 1)].y + 1u;   // ordinal in the tile's list
+                    uint32_t idx = hit_base;                                             // position in the unit's hit list
+                    for (int w2 = 0; w2 < (last_t >> 5); w2++) idx += __popc(sm.seg_bal[w2]);
+                    last_hit = idx + __popc(sm.seg_bal[last_t >> 5] & ((1u << (last_t & 31)) - 1u)) + 1u;
+                }
             } else {
                 stop = 0u;
             }
@@ -259,9 +279,6 @@ __global__ void __launch_bounds__(kSuper) composite_fwd_kernel(const FwdParams p
         PHASE_MARK(2);
 
         // ---- S3: warp = segment, lane = pixel: blend terms of the segment's hits
-        uint32_t seg_mask = 0;
-#pragma unroll
-        for (int w = 0; w < kWarps; w++) seg_mask |= (sm.seg_any[w] != 0u ? 1u : 0u) << w;
         const bool finished = sm.all_done != 0;
         if ((seg_mask >> warp) & 1u) {
             const uint32_t stop = sm.stop_at[lane];
@@ -349,6 +366,7 @@ __global__ void __launch_bounds__(kSuper) composite_fwd_kernel(const FwdParams p
         const size_t pid = (size_t)py * p.W + px;
         p.out_alpha[pid] = 1.0f - T;
         p.n_contrib[pid] = last_contributor;
+        p.last_hit[pid] = last_hit;
         p.out_color[pid] = C0 + T * p.bg[0];
         p.out_color[npix + pid] = C1 + T * p.bg[1];
         p.out_color[2 * npix + pid] = C2 + T * p.bg[2];
@@ -390,6 +408,8 @@ int launch_composite_fwd(const VegsForwardArgs& a, const GeomView& g, const Scra
     p.out_color = a.out_color; p.out_depth = a.out_depth; p.out_quat = a.out_cov_quat;
     p.out_scale = a.out_cov_scale; p.out_alpha = a.out_alpha;
     p.n_contrib = im.n_contrib;
+    p.last_hit = im.last_hit;
+    p.hitlist = b.hitlist;
     p.tile_clocks = im.tile_clocks;
     p.tile_dbg = im.tile_dbg;
     const int T = p.gx * ((a.H + kTile - 1) / kTile);
