@@ -234,6 +234,15 @@ uint64_t vegs_kernel_launch_count(void);
 void vegs_profile_enable(int32_t on);
 int vegs_profile_collect(char* buf, size_t buf_bytes);
 
+/*
+ * Test hook (no reference counterpart).  The instance list carries, next to each Gaussian id, an
+ * 8-bit mask of the compositing units it reaches whenever every id fits 24 bits (P < 2^24); larger
+ * scenes use plain ids and test the box per entry.  on = 0 forces the plain-id path for any P so
+ * the tests can cover it at small sizes; on = 1 restores the default.  Process-wide; takes effect
+ * at the next vegs_forward_prepare.
+ */
+void vegs_debug_unit_masks(int32_t on);
+
 #ifdef __cplusplus
 }
 #endif

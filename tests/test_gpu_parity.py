@@ -73,6 +73,27 @@ def test_against_oracle(P, scale, deg):
     _check_grads(ours, ref["grads"], rtol=3e-3)
 
 
+def test_against_oracle_plain_id_lists():
+    """Scenes with P >= 2^24 cannot carry the unit masks in the list words; the per-entry box-test path
+    they take is forced here at a small size and must give the same result as the default path."""
+    from vegs_b200 import _lib
+    scene = util.scene_with_specials(20000)
+    cam = synth.make_camera(0, scale=0.25)
+    cot = util.np_cotangents(cam.W, cam.H)
+    masked = util.run_ours(scene, cam, sh_degree=3, cot=cot)
+    _lib.load().vegs_debug_unit_masks(0)
+    try:
+        plain = util.run_ours(scene, cam, sh_degree=3, cot=cot)
+    finally:
+        _lib.load().vegs_debug_unit_masks(1)
+    ref = util.run_oracle(scene, cam, sh_degree=3, cot=cot)
+    _check_state_exact(plain, ref, ref["radii"] > 0)
+    for k in ("color", "depth", "alpha", "cov_quat", "cov_scale"):
+        util.assert_bit_equal(plain[k], masked[k], k)
+    util.assert_bit_equal(plain["state"]["n_contrib"], masked["state"]["n_contrib"], "n_contrib")
+    _check_grads(plain, ref["grads"], rtol=3e-3)
+
+
 def test_modes_colors_precomp_and_cov3d_precomp_against_oracle():
     scene = util.scene_with_specials(4000)
     cam = synth.make_camera(0, scale=0.125)

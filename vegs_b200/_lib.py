@@ -76,6 +76,7 @@ SIGNATURES = {
     "vegs_export_tile_clocks": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "vegs_kernel_launch_count": (C.c_uint64, []),
     "vegs_profile_enable": (None, [C.c_int32]),
+    "vegs_debug_unit_masks": (None, [C.c_int32]),
     "vegs_profile_collect": (C.c_int, [C.c_char_p, C.c_size_t]),
 }
 

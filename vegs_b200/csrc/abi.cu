@@ -76,6 +76,12 @@ extern "C" uint64_t vegs_kernel_launch_count(void) { return g_launches.load(); }
 
 extern "C" void vegs_profile_enable(int32_t on) { g_prof_on.store(on != 0); }
 
+static std::atomic<bool> g_unit_masks{true};
+extern "C" void vegs_debug_unit_masks(int32_t on) { g_unit_masks.store(on != 0); }
+namespace vegs {
+bool list_has_unit_masks(int P) { return g_unit_masks.load() && P <= (int)kListIdMask; }
+}
+
 extern "C" int vegs_profile_collect(char* buf, size_t buf_bytes) {
     std::vector<ProfEvent> evs;
     {
@@ -209,7 +215,8 @@ extern "C" int vegs_forward_render(const VegsForwardArgs* a, int32_t num_rendere
             return VEGS_EINVAL;
         }
         const uint32_t nparts = (uint32_t)a->num_rendered_host[1];
-        rc = launch_emit(a->P, order, s.rect, s.chunksum, s.partbase, nparts, gx, k0, v0, R, stream, debug);
+        rc = launch_emit(a->P, order, s.rect, s.chunksum, s.partbase, nparts, gx, k0, v0, R, g.recA, a->W, a->H,
+                         stream, debug);
         if (rc) return rc;
         bool second = false;
         rc = radix_sort_pairs(k0, v0, k1, v1, false, R, nbits, bs.hist, bs.rowtot,

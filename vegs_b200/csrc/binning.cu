@@ -15,6 +15,7 @@
 // order, so a stable sort by tile id alone reproduces the reference's (tile, depth, index) order.
 // Roofline: HBM; algorithmic bytes: 12 per sorted Gaussian (index + rectangle) per pass and
 // 8 per emitted instance.
+#include <cuda_fp16.h>
 #include "common.cuh"
 
 namespace vegs {
@@ -142,7 +143,7 @@ __global__ void __launch_bounds__(kEmitThreads)
 emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__ rect,
             const uint32_t* __restrict__ chunksum, const uint32_t* __restrict__ partbase,
             uint32_t nchunks, int grid_x, uint32_t* __restrict__ tkeys,
-            uint32_t* __restrict__ tvals, uint32_t R) {
+            uint32_t* __restrict__ tvals, uint32_t R, const float4* __restrict__ recA, int W, int H) {
     __shared__ uint32_t s_g[kEmitChunk];
     __shared__ uint2 s_rect[kEmitChunk];
     __shared__ uint32_t s_off[kEmitChunk + 1];
@@ -219,7 +220,37 @@ emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__
         const uint32_t out = gbase + i;
         if (out < R) {
             tkeys[out] = ty * (uint32_t)grid_x + tx;
-            tvals[out] = s_g[lo];
+            uint32_t val = s_g[lo];
+            if (recA != nullptr) {
+                // Which of the tile's eight 8x4 compositing units can the Gaussian reach: the same
+                // box clip as unit_box() (composite_common.cuh), factored into 2 column and 4 row
+                // tests; carried in the top byte of the list word (ids are < 2^24 in this mode).
+                const float4 a = __ldg(recA + val);
+                const uint32_t packed = __float_as_uint(a.z);
+                const float2 e = __half22float2(*reinterpret_cast<const __half2*>(&packed));
+                const float fx0 = a.x - e.x, fx1 = a.x + e.x, fy0 = a.y - e.y, fy1 = a.y + e.y;
+                uint32_t okx = 0, oky = 0;
+#pragma unroll
+                for (int hx = 0; hx < 2; hx++) {
+                    const int bx0 = (int)tx * kTile + hx * 8;
+                    const int bx1 = min(bx0 + 7, W - 1);
+                    const bool ok = bx0 < W && (int)ceilf(fmaxf(fx0, (float)bx0)) <= (int)floorf(fminf(fx1, (float)bx1));
+                    okx |= (ok ? 1u : 0u) << hx;
+                }
+#pragma unroll
+                for (int hy = 0; hy < 4; hy++) {
+                    const int by0 = (int)ty * kTile + hy * 4;
+                    const int by1 = min(by0 + 3, H - 1);
+                    const bool ok = by0 < H && (int)ceilf(fmaxf(fy0, (float)by0)) <= (int)floorf(fminf(fy1, (float)by1));
+                    oky |= (ok ? 1u : 0u) << hy;
+                }
+                uint32_t mask = 0;      // bit blk = (row hy) * 2 + (column hx)
+#pragma unroll
+                for (int hy = 0; hy < 4; hy++)
+                    if ((oky >> hy) & 1u) mask |= okx << (2 * hy);
+                val |= mask << 24;
+            }
+            tvals[out] = val;
         }
     }
 }
@@ -285,11 +316,13 @@ int launch_tile_count(int P, const uint32_t* order, const uint2* rect, uint32_t*
 
 int launch_emit(int P, const uint32_t* order, const uint2* rect, const uint32_t* chunksum,
                 const uint32_t* partbase, uint32_t nparts, int grid_x, uint32_t* tkeys,
-                uint32_t* tvals, uint32_t R, cudaStream_t stream, bool debug) {
+                uint32_t* tvals, uint32_t R, const float4* recA, int W, int H, cudaStream_t stream,
+                bool debug) {
     const uint32_t nchunks = div_up(P, kEmitChunk);
     if (nparts == 0) return VEGS_OK;
     emit_kernel<<<nparts, kEmitThreads, 0, stream>>>(P, order, rect, chunksum, partbase, nchunks,
-                                                     grid_x, tkeys, tvals, R);
+                                                     grid_x, tkeys, tvals, R,
+                                                     list_has_unit_masks(P) ? recA : nullptr, W, H);
     VEGS_LAUNCH_CHECK("emit", stream, debug);
     return VEGS_OK;
 }

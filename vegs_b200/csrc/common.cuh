@@ -43,6 +43,11 @@ constexpr int kRadix = 1 << kRadixBits;
 
 // ---------------------------------------------------------------- emission configuration
 constexpr int kUnitsPerTile = 8;  // compositing units (8x4 pixel blocks) per 16x16 tile
+// Instance list words: Gaussian id, plus - when every id fits 24 bits - in the top byte the mask of
+// the tile's compositing units the Gaussian's conservative box reaches (written by the emission
+// kernel), so a unit rejects an entry from the list word alone.
+constexpr uint32_t kListIdMask = 0x00ffffffu;
+bool list_has_unit_masks(int P);   // abi.cu: P < 2^24 unless disabled through vegs_debug_unit_masks
 constexpr int kEmitChunk = 2048;  // depth-sorted Gaussians per emission block
 
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
@@ -231,7 +236,8 @@ int launch_tile_count(int P, const uint32_t* order, const uint2* rect, uint32_t*
                       uint32_t* partbase, uint32_t* num_rendered_dev, cudaStream_t stream, bool debug);
 int launch_emit(int P, const uint32_t* order, const uint2* rect, const uint32_t* chunksum,
                 const uint32_t* partbase, uint32_t nparts, int grid_x, uint32_t* tkeys,
-                uint32_t* tvals, uint32_t R, cudaStream_t stream, bool debug);
+                uint32_t* tvals, uint32_t R, const float4* recA, int W, int H, cudaStream_t stream,
+                bool debug);
 int launch_tile_ranges(uint32_t R, const uint32_t* tkeys_sorted, uint2* ranges,
                        uint32_t* tile_order, int T, cudaStream_t stream, bool debug);
 

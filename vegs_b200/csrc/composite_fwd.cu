@@ -10,10 +10,11 @@
 // Gaussians, each touching a handful of pixels, and one block walks them while the other SMs
 // idle.  The only truly sequential part of compositing is the transmittance chain
 // T <- T * (1 - alpha) with its saturation test; everything else is parallel.
-//   SCAN  256 raw list entries per step, one per thread: clip the entry's conservative box
-//         (preprocess stage, one 16-byte record) to the unit's 32 pixels; survivors are appended in
-//         list order to a ring of candidates (ballot + prefix over the 8 warps).  Repeated until
-//         two working sets are queued or the list ends.
+//   SCAN  1024 raw list entries per step, four per thread: keep the entries whose conservative box
+//         (preprocess stage) reaches the unit's 32 pixels - one bit of the list word, set by the
+//         emission kernel (binning.cu); survivors are appended in list order to a ring of
+//         candidates (ballot + prefix over the 8 warps).  Repeated until two working sets are
+//         queued or the list ends.
 //   then, per working set of 256 candidates:
 //   S0  entry-parallel: run the reference's exact contribution test on the pixels inside the box,
 //       keep a 32-bit hit mask and each hit's alpha (alpha matrix in shared memory); entries with
@@ -34,7 +35,7 @@
 // bit-identical to the reference (same float operations in the same order).  The colour / scale
 // sums and the quaternion product are associated per 32-candidate segment instead of in one
 // running chain, a last-bit difference far inside the 1e-5 tolerance (values of magnitude <= 1).
-// Roofline: not HBM-bound (16 B per list entry per unit from L2, 16 B more per candidate, 48 B
+// Roofline: not HBM-bound (4 B per list entry per unit from L2, 36 B more per candidate, 48 B
 // more per entry with a hit, 52 B written per pixel); the bound is instruction issue of the
 // per-hit blend and the box tests.
 #include <cfloat>
@@ -47,7 +48,9 @@ namespace {
 
 constexpr int kSuper = 256;                 // candidates per working set = threads per CTA
 constexpr int kWarps = kSuper / 32;
-constexpr int kRing = 1024;                 // candidate ring (>= 3 * kSuper, power of two)
+constexpr int kScanSub = 4;                 // list entries per thread and scan step
+constexpr int kScanStep = kScanSub * kSuper;
+constexpr int kRing = 2048;                 // candidate ring (>= 2 * kSuper + kScanStep, power of two)
 
 struct FwdParams {
     const uint2* ranges;
@@ -67,12 +70,12 @@ struct FwdParams {
 struct FwdSmem {
     float alphaT[32 * kSuper];      // [pixel][slot] (columns XOR-swizzled): alpha after S0, T after S2
     float4 A[kSuper], B[kSuper], C[kSuper], D[kSuper], E[kSuper];   // records of candidates with a hit
-    uint2 ring[kRing];              // candidates in list order: (Gaussian id, ordinal in the tile's list)
+    uint32_t ring[kRing];           // candidates in list order: ordinal in the tile's list
     uint32_t bits[kWarps][32];      // [segment][pixel]: hits of the pixel inside the segment
     uint32_t stop_at[32];           // first slot the pixel does not blend any more (kSuper = none)
     float part[kWarps][10][32];     // segment partials: rows 0-2 colour, 3-5 scale, 6-9 quaternion
     uint32_t seg_bal[kWarps];       // per segment: ballot of the slots with a hit
-    uint32_t scan_cnt[2][kWarps];   // survivors per warp of a scan step (double-buffered)
+    uint32_t scan_cnt[2][kScanSub * kWarps];   // survivors per (sub-step, warp) of a scan step (double-buffered)
     int all_done;
 };
 
@@ -84,6 +87,7 @@ struct FwdSmem {
 #define PHASE_MARK(k)
 #endif
 
+template <bool kMasks>
 __global__ void __launch_bounds__(kSuper, 3) composite_fwd_kernel(const FwdParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     FwdSmem& sm = *reinterpret_cast<FwdSmem*>(smem_raw);
@@ -118,48 +122,71 @@ __global__ void __launch_bounds__(kSuper, 3) composite_fwd_kernel(const FwdParam
     uint2* hitlist = p.hitlist + ((size_t)kUnitsPerTile * range.x + (size_t)blk * (size_t)n);
     uint32_t hit_count = 0;
 
-    // raw-list pipeline of the scan: ids two steps ahead, box records one step ahead
+    // raw-list pipeline of the scan: the list words of the next step are loaded during this one
     int raw_base = 0;
-    int rid_cur = (tid < n) ? (int)list[tid] : -1;
-    float4 ra_cur = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (rid_cur >= 0) ra_cur = ldg_f4(p.recA + rid_cur);
-    int rid_nxt = (kSuper + tid < n) ? (int)list[kSuper + tid] : -1;
+    uint32_t w_cur[kScanSub];
+#pragma unroll
+    for (int j = 0; j < kScanSub; j++) w_cur[j] = (j * kSuper + tid < n) ? list[j * kSuper + tid] : 0u;
     uint32_t head = 0, tail = 0;            // ring positions, same in every thread
     int scan_par = 0;
     // working-set pipeline: this thread's candidate of the next working set, when already queued
-    uint32_t pre_pos = 0xffffffffu;
-    uint2 pre_ent = make_uint2(0u, 0u);
+    uint32_t pre_pos = 0xffffffffu, pre_ord = 0, pre_id = 0;
     float4 pre_a = make_float4(0.f, 0.f, 0.f, 0.f), pre_b = pre_a;
 
     PHASE_INIT;
     for (;;) {
-        // ---- SCAN: queue candidates until two working sets are ready or the list ends
+        // ---- SCAN: queue candidates until two working sets are ready or the list ends.  With unit
+        // masks in the list words (common.cuh) a step looks at 4 x 256 words and nothing else;
+        // without them (ids beyond 24 bits) it gathers the box record of every entry.
         bool scanned = false;
         while (tail - head < 2u * kSuper && raw_base < n) {
-            float4 ra_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (rid_nxt >= 0) ra_nxt = ldg_f4(p.recA + rid_nxt);
-            const int nn = raw_base + 2 * kSuper + tid;
-            const int rid_nn = (nn < n) ? (int)list[nn] : -1;
-            int x0, x1, y0, y1;
-            const bool keep = rid_cur >= 0 && unit_box(ra_cur, bx0, by0, bx1, by1, x0, x1, y0, y1);
-            const uint32_t bal = __ballot_sync(0xffffffffu, keep);
-            if (lane == 0) sm.scan_cnt[scan_par][warp] = __popc(bal);
-            __syncthreads();
-            uint32_t before = 0, total = 0;
+            uint32_t w_nxt[kScanSub];
 #pragma unroll
-            for (int w = 0; w < kWarps; w++) {
-                const uint32_t c = sm.scan_cnt[scan_par][w];
-                before += (w < warp) ? c : 0u;
-                total += c;
+            for (int j = 0; j < kScanSub; j++) {
+                const int r = raw_base + kScanStep + j * kSuper + tid;
+                w_nxt[j] = (r < n) ? list[r] : 0u;
             }
-            if (keep)
-                sm.ring[(tail + before + __popc(bal & ((1u << lane) - 1u))) & (kRing - 1)] =
-                    make_uint2((uint32_t)rid_cur, (uint32_t)(raw_base + tid));
-            tail += total;
-            raw_base += kSuper;
+            bool keep[kScanSub];
+            uint32_t bal[kScanSub];
+            if (kMasks) {
+#pragma unroll
+                for (int j = 0; j < kScanSub; j++) keep[j] = ((w_cur[j] >> (24 + blk)) & 1u) != 0u;
+            } else {
+                float4 ra[kScanSub];
+#pragma unroll
+                for (int j = 0; j < kScanSub; j++) {
+                    ra[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (raw_base + j * kSuper + tid < n) ra[j] = ldg_f4(p.recA + w_cur[j]);
+                }
+#pragma unroll
+                for (int j = 0; j < kScanSub; j++) {
+                    int x0, x1, y0, y1;
+                    keep[j] = raw_base + j * kSuper + tid < n && unit_box(ra[j], bx0, by0, bx1, by1, x0, x1, y0, y1);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < kScanSub; j++) {
+                bal[j] = __ballot_sync(0xffffffffu, keep[j]);
+                if (lane == 0) sm.scan_cnt[scan_par][j * kWarps + warp] = __popc(bal[j]);
+            }
+            __syncthreads();
+            uint32_t run = 0;
+#pragma unroll
+            for (int j = 0; j < kScanSub; j++) {
+#pragma unroll
+                for (int w = 0; w < kWarps; w++) {
+                    if (w == warp && keep[j])
+                        sm.ring[(tail + run + __popc(bal[j] & ((1u << lane) - 1u))) & (kRing - 1)] =
+                            (uint32_t)(raw_base + j * kSuper + tid);
+                    run += sm.scan_cnt[scan_par][j * kWarps + w];
+                }
+            }
+            tail += run;
+            raw_base += kScanStep;
             scan_par ^= 1;
             scanned = true;
-            rid_cur = rid_nxt; ra_cur = ra_nxt; rid_nxt = rid_nn;
+#pragma unroll
+            for (int j = 0; j < kScanSub; j++) w_cur[j] = w_nxt[j];
         }
         const int m = min((int)(tail - head), kSuper);
         if (m == 0) break;                   // list exhausted, nothing queued
@@ -167,23 +194,25 @@ __global__ void __launch_bounds__(kSuper, 3) composite_fwd_kernel(const FwdParam
         PHASE_MARK(0);
 
         // this thread's candidate: prefetched during the previous working set when it was queued by then
-        uint2 ent = make_uint2(0u, 0u);
+        uint32_t ord = 0, id = 0;
         float4 a_cur = make_float4(0.f, 0.f, 0.f, 0.f), b_cur = a_cur;
         if (tid < m) {
             if (pre_pos == head + tid) {
-                ent = pre_ent; a_cur = pre_a; b_cur = pre_b;
+                ord = pre_ord; id = pre_id; a_cur = pre_a; b_cur = pre_b;
             } else {
-                ent = sm.ring[(head + tid) & (kRing - 1)];
-                a_cur = ldg_f4(p.recA + ent.x);
-                b_cur = ldg_f4(p.recB + ent.x);
+                ord = sm.ring[(head + tid) & (kRing - 1)];
+                id = kMasks ? (list[ord] & kListIdMask) : list[ord];
+                a_cur = ldg_f4(p.recA + id);
+                b_cur = ldg_f4(p.recB + id);
             }
         }
         pre_pos = 0xffffffffu;
         if (head + kSuper + tid < tail) {
             pre_pos = head + kSuper + tid;
-            pre_ent = sm.ring[pre_pos & (kRing - 1)];
-            pre_a = ldg_f4(p.recA + pre_ent.x);
-            pre_b = ldg_f4(p.recB + pre_ent.x);
+            pre_ord = sm.ring[pre_pos & (kRing - 1)];
+            pre_id = kMasks ? (list[pre_ord] & kListIdMask) : list[pre_ord];
+            pre_a = ldg_f4(p.recA + pre_id);
+            pre_b = ldg_f4(p.recB + pre_id);
         }
 
         // ---- S0: thread = candidate.  Hit mask over the unit's pixels, alpha of every hit.
@@ -192,9 +221,9 @@ __global__ void __launch_bounds__(kSuper, 3) composite_fwd_kernel(const FwdParam
         if (h != 0u) {
             sm.A[tid] = a_cur;
             sm.B[tid] = b_cur;
-            sm.C[tid] = ldg_f4(p.recC + ent.x);
-            sm.D[tid] = ldg_f4(p.recD + ent.x);
-            sm.E[tid] = ldg_f4(p.recE + ent.x);
+            sm.C[tid] = ldg_f4(p.recC + id);
+            sm.D[tid] = ldg_f4(p.recD + id);
+            sm.E[tid] = ldg_f4(p.recE + id);
         }
         // ---- S1: per-pixel hit lists of this warp's 32-entry segment
         const uint32_t mybits = transpose32(h, lane);   // lane = pixel, bit = slot inside the segment
@@ -212,7 +241,7 @@ __global__ void __launch_bounds__(kSuper, 3) composite_fwd_kernel(const FwdParam
             hits_total += c;
         }
         if (h != 0u)
-            hitlist[hit_count + hits_before + __popc(hit_bal & ((1u << lane) - 1u))] = make_uint2(ent.x, h);
+            hitlist[hit_count + hits_before + __popc(hit_bal & ((1u << lane) - 1u))] = make_uint2(id, h);
         const uint32_t hit_base = hit_count;
         hit_count += hits_total;
 
@@ -263,7 +292,7 @@ __global__ void __launch_bounds__(kSuper, 3) composite_fwd_kernel(const FwdParam
                     if (stopped || t3 < 0) break;
                 }
                 if (last_t >= 0) {
-                    last_contributor = sm.ring[(head + last_t) & (kRing - 1)].y + 1u;   // ordinal in the tile's list
+                    last_contributor = sm.ring[(head + last_t) & (kRing - 1)] + 1u;   // ordinal in the tile's list
                     uint32_t idx = hit_base;                                             // position in the unit's hit list
                     for (int w2 = 0; w2 < (last_t >> 5); w2++) idx += __popc(sm.seg_bal[w2]);
                     last_hit = idx + __popc(sm.seg_bal[last_t >> 5] & ((1u << (last_t & 31)) - 1u)) + 1u;
@@ -415,7 +444,9 @@ int launch_composite_fwd(const VegsForwardArgs& a, const GeomView& g, const Scra
     const int T = p.gx * ((a.H + kTile - 1) / kTile);
     static bool configured = false;
     if (!configured) {
-        VEGS_CUDA_OK(cudaFuncSetAttribute(composite_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        VEGS_CUDA_OK(cudaFuncSetAttribute(composite_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)sizeof(FwdSmem)));
+        VEGS_CUDA_OK(cudaFuncSetAttribute(composite_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)sizeof(FwdSmem)));
         configured = true;
     }
@@ -423,7 +454,10 @@ int launch_composite_fwd(const VegsForwardArgs& a, const GeomView& g, const Scra
 #if VEGS_TILE_DEBUG
     VEGS_CUDA_OK(cudaMemsetAsync(im.tile_dbg, 0, (size_t)8 * T * sizeof(uint32_t), stream));
 #endif
-    composite_fwd_kernel<<<T * kUnitsPerTile, kSuper, sizeof(FwdSmem), stream>>>(p);
+    if (list_has_unit_masks(a.P))
+        composite_fwd_kernel<true><<<T * kUnitsPerTile, kSuper, sizeof(FwdSmem), stream>>>(p);
+    else
+        composite_fwd_kernel<false><<<T * kUnitsPerTile, kSuper, sizeof(FwdSmem), stream>>>(p);
     VEGS_LAUNCH_CHECK("composite_fwd", stream, a.debug);
     return VEGS_OK;
 }

@@ -36,12 +36,12 @@ __global__ void export_gaussians_kernel(int P, const int* __restrict__ radii,
 
 __global__ void export_keys_kernel(const uint2* __restrict__ ranges,
                                    const uint32_t* __restrict__ point_list,
-                                   const float4* __restrict__ recA, uint64_t* __restrict__ keys,
-                                   uint32_t* __restrict__ list_out) {
+                                   const float4* __restrict__ recA, uint32_t id_mask,
+                                   uint64_t* __restrict__ keys, uint32_t* __restrict__ list_out) {
     const uint32_t tile = blockIdx.x;
     const uint2 rg = ranges[tile];
     for (uint32_t i = rg.x + threadIdx.x; i < rg.y; i += blockDim.x) {
-        const uint32_t g = point_list[i];
+        const uint32_t g = point_list[i] & id_mask;   // strip the unit mask byte (common.cuh)
         if (keys) keys[i] = ((uint64_t)tile << 32) | (uint64_t)__float_as_uint(recA[g].w);
         if (list_out) list_out[i] = g;
     }
@@ -62,7 +62,8 @@ int launch_export(const VegsForwardArgs& a, const GeomView& g, const ScratchView
         VEGS_LAUNCH_CHECK("export_gaussians", stream, true);
     }
     if (R > 0 && (keys || point_list)) {
-        export_keys_kernel<<<T, 256, 0, stream>>>(im.ranges, b.point_list, g.recA, keys,
+        export_keys_kernel<<<T, 256, 0, stream>>>(im.ranges, b.point_list, g.recA,
+                                                  list_has_unit_masks(a.P) ? kListIdMask : 0xffffffffu, keys,
                                                   point_list);
         VEGS_LAUNCH_CHECK("export_keys", stream, true);
     }
