@@ -35,7 +35,7 @@ grads = dgr._backward_impl(st, torch.zeros(3, device=dev), sc["means3D"], res[5]
                            sc["shs"], cam.campos, res[4], (P, 1), False)
 T = state["ranges"].shape[0]
 fwd = torch.zeros(T, dtype=torch.int32, device=dev); bwd = torch.zeros(T, dtype=torch.int32, device=dev)
-dbg = torch.zeros(T * 8, dtype=torch.int32, device=dev)
+dbg = torch.zeros(T * 16, dtype=torch.int32, device=dev)
 _lib.check(lib.vegs_export_tile_clocks(st.img.data_ptr(), cam.W, cam.H, fwd.data_ptr(), bwd.data_ptr(), dbg.data_ptr(),
                                        C.c_void_p(torch.cuda.current_stream().cuda_stream)), "clocks")
 torch.cuda.synchronize()
@@ -52,11 +52,13 @@ print("tiles", T, "R", rl.sum(), "sum fwd Mcycles", f.sum() / 1e6, "sum bwd Mcyc
 print("top fwd tiles: (tile, row, len, maxcontrib, fwd max-unit Mcyc, bwd max-unit Mcyc, fwd cyc/entry)")
 for t in order[:12]:
     print(t, t // gx, rl[t], tmax[t], round(f[t] / 1e6, 2), round(b[t] / 1e6, 2), round(f[t] / max(rl[t], 1), 1))
-d = dbg.cpu().numpy().astype(np.int64).reshape(T, 8) * 1024
+draw = dbg.cpu().numpy().astype(np.int64).reshape(T, 16)
+d = draw[:, :8] * 1024
 if d.any():
     print("phase Mcycles of unit 0 of the top tiles: fwd scan(+S4) S0 S2 S3 | bwd S0 pass1 pass2 S3")
     for t in order[:12]:
-        print(t, rl[t], " ".join("%.2f" % (x / 1e6) for x in d[t, :4]), "|", " ".join("%.2f" % (x / 1e6) for x in d[t, 4:]))
+        print(t, rl[t], " ".join("%.2f" % (x / 1e6) for x in d[t, :4]), "|", " ".join("%.2f" % (x / 1e6) for x in d[t, 4:]),
+              "| sets %d cand %d hit-entries %d seg0 pixel-hits %d" % tuple(draw[t, 8:12]))
     print("all tiles:", " ".join("%.1f" % (x / 1e6) for x in d.sum(axis=0)))
 print("len percentiles", np.percentile(rl, [50, 90, 99, 100]))
 print("fwd cycles percentiles (M)", np.percentile(f, [50, 90, 99, 100]) / 1e6)

@@ -215,7 +215,7 @@ extern "C" int vegs_forward_render(const VegsForwardArgs* a, int32_t num_rendere
             return VEGS_EINVAL;
         }
         const uint32_t nparts = (uint32_t)a->num_rendered_host[1];
-        rc = launch_emit(a->P, order, s.rect, s.chunksum, s.partbase, nparts, gx, k0, v0, R, g.recA, a->W, a->H,
+        rc = launch_emit(a->P, order, s.rect, s.chunksum, s.partbase, nparts, gx, k0, v0, R, s.pbox, a->W, a->H,
                          stream, debug);
         if (rc) return rc;
         bool second = false;
@@ -308,6 +308,6 @@ extern "C" int vegs_export_tile_clocks(const void* img, int32_t W, int32_t H, ui
     const size_t T = (size_t)((W + kTile - 1) / kTile) * ((H + kTile - 1) / kTile);
     if (fwd) VEGS_CUDA_OK(cudaMemcpyAsync(fwd, im.tile_clocks, T * 4, cudaMemcpyDeviceToDevice, stream));
     if (bwd) VEGS_CUDA_OK(cudaMemcpyAsync(bwd, im.tile_clocks + T, T * 4, cudaMemcpyDeviceToDevice, stream));
-    if (dbg) VEGS_CUDA_OK(cudaMemcpyAsync(dbg, im.tile_dbg, T * 32, cudaMemcpyDeviceToDevice, stream));
+    if (dbg) VEGS_CUDA_OK(cudaMemcpyAsync(dbg, im.tile_dbg, T * 64, cudaMemcpyDeviceToDevice, stream));
     return VEGS_OK;
 }

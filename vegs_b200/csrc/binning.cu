@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(kEmitThreads)
 emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__ rect,
             const uint32_t* __restrict__ chunksum, const uint32_t* __restrict__ partbase,
             uint32_t nchunks, int grid_x, uint32_t* __restrict__ tkeys,
-            uint32_t* __restrict__ tvals, uint32_t R, const float4* __restrict__ recA, int W, int H) {
+            uint32_t* __restrict__ tvals, uint32_t R, const uint2* __restrict__ pbox, int W, int H) {
     __shared__ uint32_t s_g[kEmitChunk];
     __shared__ uint2 s_rect[kEmitChunk];
     __shared__ uint32_t s_off[kEmitChunk + 1];
@@ -221,28 +221,26 @@ emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__
         if (out < R) {
             tkeys[out] = ty * (uint32_t)grid_x + tx;
             uint32_t val = s_g[lo];
-            if (recA != nullptr) {
-                // Which of the tile's eight 8x4 compositing units can the Gaussian reach: the same
-                // box clip as unit_box() (composite_common.cuh), factored into 2 column and 4 row
-                // tests; carried in the top byte of the list word (ids are < 2^24 in this mode).
-                const float4 a = __ldg(recA + val);
-                const uint32_t packed = __float_as_uint(a.z);
-                const float2 e = __half22float2(*reinterpret_cast<const __half2*>(&packed));
-                const float fx0 = a.x - e.x, fx1 = a.x + e.x, fy0 = a.y - e.y, fy1 = a.y + e.y;
+            if (pbox != nullptr) {
+                // Which of the tile's eight 8x4 compositing units can the Gaussian reach: its pixel
+                // box (preprocess.cu) against 2 unit columns and 4 unit rows - the same outcome as
+                // unit_box() (composite_common.cuh); carried in the top byte of the list word (ids
+                // are < 2^24 in this mode).
+                const uint2 pb = __ldg(pbox + val);
+                const int gx0 = (int)(pb.x & 0xffffu), gx1 = (int)(pb.x >> 16) - 1;
+                const int gy0 = (int)(pb.y & 0xffffu), gy1 = (int)(pb.y >> 16) - 1;
                 uint32_t okx = 0, oky = 0;
 #pragma unroll
                 for (int hx = 0; hx < 2; hx++) {
                     const int bx0 = (int)tx * kTile + hx * 8;
                     const int bx1 = min(bx0 + 7, W - 1);
-                    const bool ok = bx0 < W && (int)ceilf(fmaxf(fx0, (float)bx0)) <= (int)floorf(fminf(fx1, (float)bx1));
-                    okx |= (ok ? 1u : 0u) << hx;
+                    okx |= ((bx0 < W && max(gx0, bx0) <= min(gx1, bx1)) ? 1u : 0u) << hx;
                 }
 #pragma unroll
                 for (int hy = 0; hy < 4; hy++) {
                     const int by0 = (int)ty * kTile + hy * 4;
                     const int by1 = min(by0 + 3, H - 1);
-                    const bool ok = by0 < H && (int)ceilf(fmaxf(fy0, (float)by0)) <= (int)floorf(fminf(fy1, (float)by1));
-                    oky |= (ok ? 1u : 0u) << hy;
+                    oky |= ((by0 < H && max(gy0, by0) <= min(gy1, by1)) ? 1u : 0u) << hy;
                 }
                 uint32_t mask = 0;      // bit blk = (row hy) * 2 + (column hx)
 #pragma unroll
@@ -316,13 +314,13 @@ int launch_tile_count(int P, const uint32_t* order, const uint2* rect, uint32_t*
 
 int launch_emit(int P, const uint32_t* order, const uint2* rect, const uint32_t* chunksum,
                 const uint32_t* partbase, uint32_t nparts, int grid_x, uint32_t* tkeys,
-                uint32_t* tvals, uint32_t R, const float4* recA, int W, int H, cudaStream_t stream,
+                uint32_t* tvals, uint32_t R, const uint2* pbox, int W, int H, cudaStream_t stream,
                 bool debug) {
     const uint32_t nchunks = div_up(P, kEmitChunk);
     if (nparts == 0) return VEGS_OK;
     emit_kernel<<<nparts, kEmitThreads, 0, stream>>>(P, order, rect, chunksum, partbase, nchunks,
                                                      grid_x, tkeys, tvals, R,
-                                                     list_has_unit_masks(P) ? recA : nullptr, W, H);
+                                                     list_has_unit_masks(P) ? pbox : nullptr, W, H);
     VEGS_LAUNCH_CHECK("emit", stream, debug);
     return VEGS_OK;
 }

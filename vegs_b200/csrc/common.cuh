@@ -66,6 +66,7 @@ struct ScratchView {
     float4* recD;
     float4* recE;
     uint2* rect;
+    uint2* pbox;         // pixel box of the Gaussian clipped to the image: (x0 | (x1+1) << 16, y0 | (y1+1) << 16)
     uint32_t* keys0;
     uint32_t* keys1;
     uint32_t* vals0;
@@ -83,7 +84,7 @@ struct ImgView {
     uint2* ranges;
     uint32_t* tile_order;
     uint32_t* tile_clocks;   // [2*T] SM cycles/1024 spent on each tile by composite fwd / bwd (diagnostics)
-    uint32_t* tile_dbg;      // [8*T] extra counters, only written when built with -DVEGS_TILE_DEBUG=1
+    uint32_t* tile_dbg;      // [16*T] extra counters, only written when built with -DVEGS_TILE_DEBUG=1
     size_t bytes;
 };
 
@@ -131,6 +132,7 @@ static inline ScratchView scratch_view(void* base, int P) {
     v.recD = carve<float4>(cur, n);
     v.recE = carve<float4>(cur, n);
     v.rect = carve<uint2>(cur, n);
+    v.pbox = carve<uint2>(cur, n);
     v.keys0 = carve<uint32_t>(cur, n);
     v.keys1 = carve<uint32_t>(cur, n);
     v.vals0 = carve<uint32_t>(cur, n);
@@ -153,7 +155,7 @@ static inline ImgView img_view(void* base, int W, int H) {
     v.ranges = carve<uint2>(cur, T ? T : 1);
     v.tile_order = carve<uint32_t>(cur, T ? T : 1);
     v.tile_clocks = carve<uint32_t>(cur, 2 * (T ? T : 1));
-    v.tile_dbg = carve<uint32_t>(cur, 8 * (T ? T : 1));
+    v.tile_dbg = carve<uint32_t>(cur, 16 * (T ? T : 1));
     v.bytes = (size_t)(cur - reinterpret_cast<char*>(base));
     return v;
 }
@@ -236,7 +238,7 @@ int launch_tile_count(int P, const uint32_t* order, const uint2* rect, uint32_t*
                       uint32_t* partbase, uint32_t* num_rendered_dev, cudaStream_t stream, bool debug);
 int launch_emit(int P, const uint32_t* order, const uint2* rect, const uint32_t* chunksum,
                 const uint32_t* partbase, uint32_t nparts, int grid_x, uint32_t* tkeys,
-                uint32_t* tvals, uint32_t R, const float4* recA, int W, int H, cudaStream_t stream,
+                uint32_t* tvals, uint32_t R, const uint2* pbox, int W, int H, cudaStream_t stream,
                 bool debug);
 int launch_tile_ranges(uint32_t R, const uint32_t* tkeys_sorted, uint2* ranges,
                        uint32_t* tile_order, int T, cudaStream_t stream, bool debug);

@@ -271,7 +271,7 @@ __global__ void __launch_bounds__(kSuper, 3) composite_bwd_kernel(const BwdParam
     if (tid == 0) atomicMax(&p.tile_clocks[tile], (uint32_t)((clock64() - t_start) >> 10));
 #if VEGS_TILE_DEBUG
     if (tid == 0 && blk == 0)
-        for (int k = 0; k < 4; k++) p.tile_dbg[tile * 8 + 4 + k] = (uint32_t)(ph_acc[k] >> 10);
+        for (int k = 0; k < 4; k++) p.tile_dbg[tile * 16 + 4 + k] = (uint32_t)(ph_acc[k] >> 10);
 #endif
 }
 

@@ -80,7 +80,7 @@ struct FwdSmem {
 };
 
 #if VEGS_TILE_DEBUG
-#define PHASE_INIT long long ph_t = clock64(), ph_acc[4] = {0, 0, 0, 0}
+#define PHASE_INIT long long ph_t = clock64(), ph_acc[4] = {0, 0, 0, 0}; uint32_t dbg_sets = 0, dbg_cand = 0, dbg_pix = 0
 #define PHASE_MARK(k) { long long now_; asm volatile("mov.u64 %0, %%clock64;" : "=l"(now_) :: "memory"); ph_acc[k] += now_ - ph_t; ph_t = now_; }
 #else
 #define PHASE_INIT
@@ -244,6 +244,9 @@ __global__ void __launch_bounds__(kSuper, 3) composite_fwd_kernel(const FwdParam
             hitlist[hit_count + hits_before + __popc(hit_bal & ((1u << lane) - 1u))] = make_uint2(id, h);
         const uint32_t hit_base = hit_count;
         hit_count += hits_total;
+#if VEGS_TILE_DEBUG
+        dbg_sets++; dbg_cand += (uint32_t)m; dbg_pix += (uint32_t)__syncthreads_count(0) + __reduce_add_sync(0xffffffffu, (uint32_t)__popc(h));
+#endif
 
         // ---- S2: warp 0, lane = pixel: sequential transmittance chain over the working set
         if (warp == 0) {
@@ -418,7 +421,11 @@ __global__ void __launch_bounds__(kSuper, 3) composite_fwd_kernel(const FwdParam
     if (tid == 0) atomicMax(&p.tile_clocks[tile], (uint32_t)((clock64() - t_start) >> 10));
 #if VEGS_TILE_DEBUG
     if (tid == 0 && blk == 0)
-        for (int k = 0; k < 4; k++) p.tile_dbg[tile * 8 + k] = (uint32_t)(ph_acc[k] >> 10);
+    {
+        for (int k = 0; k < 4; k++) p.tile_dbg[tile * 16 + k] = (uint32_t)(ph_acc[k] >> 10);
+        p.tile_dbg[tile * 16 + 8] = dbg_sets; p.tile_dbg[tile * 16 + 9] = dbg_cand;
+        p.tile_dbg[tile * 16 + 10] = hit_count; p.tile_dbg[tile * 16 + 11] = dbg_pix;   // pixel hits of warp 0's segments only
+    }
 #endif
 }
 
@@ -452,7 +459,7 @@ int launch_composite_fwd(const VegsForwardArgs& a, const GeomView& g, const Scra
     }
     VEGS_CUDA_OK(cudaMemsetAsync(im.tile_clocks, 0, (size_t)2 * T * sizeof(uint32_t), stream));
 #if VEGS_TILE_DEBUG
-    VEGS_CUDA_OK(cudaMemsetAsync(im.tile_dbg, 0, (size_t)8 * T * sizeof(uint32_t), stream));
+    VEGS_CUDA_OK(cudaMemsetAsync(im.tile_dbg, 0, (size_t)16 * T * sizeof(uint32_t), stream));
 #endif
     if (list_has_unit_masks(a.P))
         composite_fwd_kernel<true><<<T * kUnitsPerTile, kSuper, sizeof(FwdSmem), stream>>>(p);

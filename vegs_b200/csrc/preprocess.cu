@@ -40,6 +40,7 @@ struct PreParams {
     int* radii;
     float4 *recA, *recB, *recC, *recD, *recE;
     uint2* rect;
+    uint2* pbox;
     uint8_t* clamped;
     uint32_t* keys;
     const float* view;
@@ -277,6 +278,17 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_fwd_kernel(const PrePa
         }
         const __half2 eh = __floats2half2_rn(ex, ey);   // 1.002 above covers the 2^-11 rounding
         p.recA[idx] = make_float4(pix_x, pix_y, __uint_as_float(*reinterpret_cast<const uint32_t*>(&eh)), depth);
+        {
+            // The same box in whole pixels, clipped to the image, for the emission kernel's unit
+            // masks: float operations of unit_box() (composite_common.cuh) with the image as the block.
+            const float2 e = __half22float2(eh);
+            const int bx0 = (int)ceilf(fmaxf(pix_x - e.x, 0.0f));
+            const int bx1 = (int)floorf(fminf(pix_x + e.x, (float)(p.W - 1)));
+            const int by0 = (int)ceilf(fmaxf(pix_y - e.y, 0.0f));
+            const int by1 = (int)floorf(fminf(pix_y + e.y, (float)(p.H - 1)));
+            p.pbox[idx] = make_uint2((uint32_t)min(bx0, p.W) | ((uint32_t)(max(bx1, -1) + 1) << 16),
+                                     (uint32_t)min(by0, p.H) | ((uint32_t)(max(by1, -1) + 1) << 16));
+        }
         p.recB[idx] = make_float4(conic.x, conic.y, conic.z, opacity);
         p.recC[idx] = make_float4(rgb.x, rgb.y, rgb.z, __fdiv_rn(1.0f, sinf(theta)));
         p.recD[idx] = d4;
@@ -315,7 +327,7 @@ int launch_preprocess_fwd(const VegsForwardArgs& a, const GeomView& g, const Scr
     p.focal_x = a.W / (2.0f * a.tan_fovx);
     p.radii = a.radii;
     p.recA = g.recA; p.recB = g.recB; p.recC = g.recC; p.recD = s.recD; p.recE = s.recE;
-    p.rect = s.rect; p.clamped = g.clamped; p.keys = s.keys0;
+    p.rect = s.rect; p.pbox = s.pbox; p.clamped = g.clamped; p.keys = s.keys0;
     p.shs_vec_ok = a.shs != nullptr && (reinterpret_cast<uintptr_t>(a.shs) & 15u) == 0;
     p.rots_vec_ok = a.rotations != nullptr && (reinterpret_cast<uintptr_t>(a.rotations) & 15u) == 0;
     const int blocks = (a.P + kPreThreads - 1) / kPreThreads;
