@@ -11,11 +11,11 @@ nproc >> gpurun_out/gpu.txt
 for s in $stages; do
   case $s in
     smoke)
-      timeout 600 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" | tee -a gpurun_out/summary.txt ;;
+      timeout 180 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" | tee -a gpurun_out/summary.txt ;;
     tests)
       for grp in "dist2 and not noalloc" "mark_visible or edge or debug" "against_oracle or modes or deterministic" "golden" "reference_live" "full_size" "noalloc"; do
         name=$(echo "$grp" | tr ' ' '_')
-        timeout 900 python -m pytest tests -m gpu -q -k "$grp" -p no:cacheprovider > "gpurun_out/pytest_${name}.log" 2>&1
+        timeout 240 python -m pytest tests -m gpu -q -k "$grp" -p no:cacheprovider > "gpurun_out/pytest_${name}.log" 2>&1
         echo "pytest[$grp] rc=$? $(tail -1 gpurun_out/pytest_${name}.log)" | tee -a gpurun_out/summary.txt
       done ;;
     golden)

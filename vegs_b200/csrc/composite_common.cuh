@@ -57,24 +57,43 @@ __device__ __forceinline__ bool unit_box(const float4 a, int bx0, int by0, int b
     return x0 <= x1 && y0 <= y1;
 }
 
-// Hit mask of one entry (slot `slot` of the working set) over the block's 32 pixels; each hit's
-// alpha is stored at mat[(pixel * stride + swz(slot, pixel)) * words].
+// Hit mask of one entry (slot `slot` of the working set) over the block's 32 pixels; for each hit
+// (1 - alpha, depth * alpha) is stored at mat[pixel * stride + slot].
 // Mask layout: (bit = (y - by0) * 8 + (x - bx0)).
 // a = recA = {x, y, half2(ex, ey), depth}, b = recB = {conic.a, conic.b, conic.c, opacity}.
 // The test is the reference's (cuda_rasterizer/forward.cu:371-381): power <= 0 and
 // min(0.99, opacity * exp(power)) >= 1/255, in its float operation order (power as
 // fma(fma(A*dx, dx, (C*dy)*dy), -0.5, -((B*dx)*dy)), read from the reference's SASS).
-// Pixels outside the precomputed box cannot pass it, so they are not evaluated.
-__device__ __forceinline__ uint32_t entry_hits_alpha(const float4 a, const float4 b, int bx0, int by0,
-                                                     int bx1, int by1, float* mat, int slot, int stride,
-                                                     int words) {
+// Which pixels are put to that test is narrowed conservatively first: to the entry's box, and in
+// each pixel row to the interval where the quadratic can reach -(log(255 opacity) + 0.01)
+// (alpha >= 1/255 needs power >= -log(255 opacity)); an elongated Gaussian fills a small part of
+// its box.  The margins (0.01 in power, 0.02 px, 0.05% of the half width) are orders of magnitude
+// above the float error of the interval; a non-finite interval falls back to the whole row.
+__device__ __forceinline__ uint32_t entry_hits_fwd(const float4 a, const float4 b, int bx0, int by0, int bx1,
+                                                   int by1, float2* mat, int slot, int stride) {
     int x0, x1, y0, y1;
     if (!unit_box(a, bx0, by0, bx1, by1, x0, x1, y0, y1)) return 0u;
+    const float tau = __logf(255.0f * b.w) + 0.01f;
+    const float bb = b.y * b.y;
+    const float det = fmaf(b.x, b.z, -bb) - fmaf(b.y, b.y, -bb);      // compensated A*C - B*B
+    const float inv_a = 1.0f / b.x;
+    const float two_tau_a = 2.0f * tau * b.x;
     uint32_t hits = 0;
     for (int y = y0; y <= y1; y++) {
         const float dy = __fsub_rn(a.y, (float)y);
+        const float disc = fmaf(-det, dy * dy, two_tau_a);
+        if (disc < 0.0f) continue;
+        const float root = sqrtf(disc) * 1.0005f;
+        const float mid = -b.y * dy;
+        const float x_lo = a.x - (mid + root) * inv_a - 0.02f;
+        const float x_hi = a.x - (mid - root) * inv_a + 0.02f;
+        int xs = x0, xe = x1;
+        if (fabsf(x_lo) < 1e9f && fabsf(x_hi) < 1e9f) {              // false for NaN / infinity
+            xs = max(x0, (int)ceilf(x_lo));
+            xe = min(x1, (int)floorf(x_hi));
+        }
         const float cyy = __fmul_rn(__fmul_rn(b.z, dy), dy);
-        for (int x = x0; x <= x1; x++) {
+        for (int x = xs; x <= xe; x++) {
             const float dx = __fsub_rn(a.x, (float)x);
             const float sum = __fmaf_rn(__fmul_rn(b.x, dx), dx, cyy);
             const float power = __fmaf_rn(sum, -0.5f, -__fmul_rn(__fmul_rn(b.y, dx), dy));
@@ -83,7 +102,7 @@ __device__ __forceinline__ uint32_t entry_hits_alpha(const float4 a, const float
             if (alpha < 1.0f / 255.0f) continue;
             const int pix = (y - by0) * kUnitW + (x - bx0);
             hits |= 1u << pix;
-            mat[(pix * stride + swz(slot, pix)) * words] = alpha;
+            mat[pix * stride + slot] = make_float2(__fsub_rn(1.0f, alpha), __fmul_rn(a.w, alpha));
         }
     }
     return hits;

@@ -50,6 +50,7 @@ constexpr int kSuper = 256;                 // candidates per working set = thre
 constexpr int kWarps = kSuper / 32;
 constexpr int kScanSub = 4;                 // list entries per thread and scan step
 constexpr int kScanStep = kScanSub * kSuper;
+constexpr int kRow = kSuper + 1;             // row stride of the pixel x slot matrix
 constexpr int kRing = 2048;                 // candidate ring (>= 2 * kSuper + kScanStep, power of two)
 
 struct FwdParams {
@@ -68,11 +69,13 @@ struct FwdParams {
 };
 
 struct FwdSmem {
-    float alphaT[32 * kSuper];      // [pixel][slot] (columns XOR-swizzled): alpha after S0, T after S2
+    float2 M[32 * kRow + 4];        // [pixel][slot], rows padded by one entry so that lanes reading the same
+                                    // column of their own rows spread over the banks: (1 - alpha, depth * alpha)
+                                    // after S0; S2 replaces the first word by T, the transmittance before the hit
     float4 A[kSuper], B[kSuper], C[kSuper], D[kSuper], E[kSuper];   // records of candidates with a hit
     uint32_t ring[kRing];           // candidates in list order: ordinal in the tile's list
     uint32_t bits[kWarps][32];      // [segment][pixel]: hits of the pixel inside the segment
-    uint32_t stop_at[32];           // first slot the pixel does not blend any more (kSuper = none)
+    uint32_t stop_at[32];           // first (segment * 32 + hit index) the pixel does not blend (kSuper = none)
     float part[kWarps][10][32];     // segment partials: rows 0-2 colour, 3-5 scale, 6-9 quaternion
     uint32_t seg_bal[kWarps];       // per segment: ballot of the slots with a hit
     uint32_t scan_cnt[2][kScanSub * kWarps];   // survivors per (sub-step, warp) of a scan step (double-buffered)
@@ -88,7 +91,7 @@ struct FwdSmem {
 #endif
 
 template <bool kMasks>
-__global__ void __launch_bounds__(kSuper, 3) composite_fwd_kernel(const FwdParams p) {
+__global__ void __launch_bounds__(kSuper, 2) composite_fwd_kernel(const FwdParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     FwdSmem& sm = *reinterpret_cast<FwdSmem*>(smem_raw);
 
@@ -217,7 +220,7 @@ __global__ void __launch_bounds__(kSuper, 3) composite_fwd_kernel(const FwdParam
 
         // ---- S0: thread = candidate.  Hit mask over the unit's pixels, alpha of every hit.
         uint32_t h = 0;
-        if (tid < m) h = entry_hits_alpha(a_cur, b_cur, bx0, by0, bx1, by1, sm.alphaT, tid, kSuper, 1);
+        if (tid < m) h = entry_hits_fwd(a_cur, b_cur, bx0, by0, bx1, by1, sm.M, tid, kRow);
         if (h != 0u) {
             sm.A[tid] = a_cur;
             sm.B[tid] = b_cur;
@@ -225,9 +228,24 @@ __global__ void __launch_bounds__(kSuper, 3) composite_fwd_kernel(const FwdParam
             sm.D[tid] = ldg_f4(p.recD + id);
             sm.E[tid] = ldg_f4(p.recE + id);
         }
-        // ---- S1: per-pixel hit lists of this warp's 32-entry segment
+        // ---- S1: per-pixel hit lists of this warp's 32-entry segment; the pixel's operands are
+        // compacted to the front of the segment's 32 columns (hit j of the segment at column j), in
+        // place: the write position never passes the read position.  The sequential pass then
+        // walks dense arrays instead of chasing bit masks.
         const uint32_t mybits = transpose32(h, lane);   // lane = pixel, bit = slot inside the segment
         sm.bits[warp][lane] = mybits;
+        __syncwarp();                                   // the segment's S0 writes come from this warp
+        {
+            float2* row = sm.M + lane * kRow + warp * 32;
+            uint32_t bits = mybits;
+            int j = 0;
+            while (bits != 0u) {
+                const int sl = __ffs(bits) - 1;
+                bits &= bits - 1;
+                if (sl != j) row[j] = row[sl];
+                j++;
+            }
+        }
         const uint32_t hit_bal = __ballot_sync(0xffffffffu, h != 0u);
         if (lane == 0) sm.seg_bal[warp] = hit_bal;
         __syncthreads();
@@ -250,58 +268,51 @@ __global__ void __launch_bounds__(kSuper, 3) composite_fwd_kernel(const FwdParam
 
         // ---- S2: warp 0, lane = pixel: sequential transmittance chain over the working set
         if (warp == 0) {
-            uint32_t stop = kSuper;
-            if (!done) {
-                // the pixel's hits of all segments as one stream (the loop is latency-bound)
-                int w = 0;
-                uint32_t bits = sm.bits[0][lane];
-                auto next_hit = [&]() -> int {
-                    while (bits == 0u && w < kWarps - 1) bits = sm.bits[++w][lane];
-                    if (bits == 0u) return -1;
-                    const int t = w * 32 + __ffs(bits) - 1;
-                    bits &= bits - 1;
-                    return t;
-                };
-                // four hits per round: their operands are fetched together, then the chain runs
-                int last_t = -1;
-                bool stopped = false;
-                auto load_hit = [&](int t, float& al, float& dp) {
-                    al = 0.f; dp = 0.f;
-                    if (t >= 0) { al = sm.alphaT[lane * kSuper + swz(t, lane)]; dp = sm.A[t].w; }
-                };
-                auto chain = [&](int t, float al, float dp) {
-                    if (t < 0 || stopped) return;
-                    const float test_T = __fmul_rn(T, __fsub_rn(1.0f, al));
-                    if (test_T < 0.0001f) {      // not blended; the pixel is finished (forward.cu:382-386)
-                        done = true;
-                        stopped = true;
-                        stop = (uint32_t)t;
-                        return;
+            // first (segment * 32 + hit index) the pixel does not blend; a finished pixel blends nothing
+            uint32_t stop = done ? 0u : (uint32_t)kSuper;
+            {
+                int last_w = -1, last_j = 0;
+                bool stopped = done;         // every lane stays in the loops below (warp votes)
+#pragma unroll 1
+                for (int w = 0; w < kWarps; w++) {
+                    const int cnt = stopped ? 0 : __popc(sm.bits[w][lane]);
+                    float2* row = sm.M + lane * kRow + w * 32;
+                    // the lanes run in lock step: rounds of four hits until the longest list of the
+                    // segment is done.  A round is branch-free: a slot past the end of the pixel's
+                    // list (or past its saturation) acts as alpha = 0, which leaves T and the depth
+                    // sum exactly unchanged.
+                    const int rounds = (__reduce_max_sync(0xffffffffu, cnt) + 3) >> 2;
+                    for (int r = 0; r < rounds; r++) {
+                        float2 m[4];
+#pragma unroll
+                        for (int k = 0; k < 4; k++) m[k] = row[4 * r + k];   // may run into the next columns: unused
+#pragma unroll
+                        for (int k = 0; k < 4; k++) {
+                            const int j = 4 * r + k;
+                            const bool active = j < cnt && !stopped;
+                            const float test_T = __fmul_rn(T, active ? m[k].x : 1.0f);   // T * (1 - alpha)
+                            // T(1 - alpha) < 1e-4: not blended, the pixel is finished (forward.cu:382-386)
+                            const bool sat = active && test_T < 0.0001f;
+                            if (active && !sat) row[j].x = T;                // transmittance in front of this hit
+                            // depth is accumulated here, in the reference's running order, so it
+                            // stays bit-identical: depth values are ~1e2, re-associating that sum
+                            // per segment already costs more than the 1e-5 tolerance
+                            Dacc = __fmaf_rn((active && !sat) ? m[k].y : 0.0f, T, Dacc);
+                            if (active && !sat) { last_w = w; last_j = j; }
+                            if (sat) { stop = (uint32_t)(w * 32 + j); stopped = true; }
+                            T = sat ? T : test_T;
+                        }
                     }
-                    sm.alphaT[lane * kSuper + swz(t, lane)] = T;   // transmittance in front of this hit
-                    // depth is accumulated here, in the reference's running order, so it stays
-                    // bit-identical: depth values are ~1e2, re-associating that sum per segment
-                    // already costs more than the 1e-5 tolerance
-                    Dacc = __fmaf_rn(__fmul_rn(dp, al), T, Dacc);
-                    T = test_T;
-                    last_t = t;
-                };
-                for (;;) {
-                    const int t0 = next_hit(), t1 = next_hit(), t2 = next_hit(), t3 = next_hit();
-                    if (t0 < 0) break;
-                    float al0, al1, al2, al3, dp0, dp1, dp2, dp3;
-                    load_hit(t0, al0, dp0); load_hit(t1, al1, dp1); load_hit(t2, al2, dp2); load_hit(t3, al3, dp3);
-                    chain(t0, al0, dp0); chain(t1, al1, dp1); chain(t2, al2, dp2); chain(t3, al3, dp3);
-                    if (stopped || t3 < 0) break;
                 }
-                if (last_t >= 0) {
+                done = stopped;
+                if (last_w >= 0) {
+                    // slot of the last blended hit: the (last_j + 1)-th set bit of its segment's mask
+                    const int last_t = last_w * 32 + (int)__fns(sm.bits[last_w][lane], 0, last_j + 1);
                     last_contributor = sm.ring[(head + last_t) & (kRing - 1)] + 1u;   // ordinal in the tile's list
-                    uint32_t idx = hit_base;                                             // position in the unit's hit list
-                    for (int w2 = 0; w2 < (last_t >> 5); w2++) idx += __popc(sm.seg_bal[w2]);
-                    last_hit = idx + __popc(sm.seg_bal[last_t >> 5] & ((1u << (last_t & 31)) - 1u)) + 1u;
+                    uint32_t idx = hit_base;                                           // position in the unit's hit list
+                    for (int w2 = 0; w2 < last_w; w2++) idx += __popc(sm.seg_bal[w2]);
+                    last_hit = idx + __popc(sm.seg_bal[last_w] & ((1u << (last_t & 31)) - 1u)) + 1u;
                 }
-            } else {
-                stop = 0u;
             }
             sm.stop_at[lane] = stop;
             const bool all = __all_sync(0xffffffffu, done);
@@ -317,16 +328,18 @@ __global__ void __launch_bounds__(kSuper, 3) composite_fwd_kernel(const FwdParam
             uint32_t bits = mybits;
             float c0 = 0.f, c1 = 0.f, c2 = 0.f, s0 = 0.f, s1 = 0.f, s2 = 0.f;
             float qw = 1.f, qx = 0.f, qy = 0.f, qz = 0.f;
+            int j = 0;
             while (bits != 0u) {
                 const int t = warp * 32 + __ffs(bits) - 1;
                 bits &= bits - 1;
-                if ((uint32_t)t >= stop) break;
+                if ((uint32_t)(warp * 32 + j) >= stop) break;
                 const float4 a = sm.A[t];    // x, y, half2(ex, ey), depth
                 const float4 bb = sm.B[t];   // conic.a, conic.b, conic.c, opacity
                 float dx, dy;
                 const float power = pair_power(a, bb, pixfx, pixfy, dx, dy);
                 const float alpha = fminf(0.99f, __fmul_rn(bb.w, expf(power)));
-                const float Tb = sm.alphaT[lane * kSuper + swz(t, lane)];
+                const float Tb = sm.M[lane * kRow + warp * 32 + j].x;
+                j++;
                 const float4 c = sm.C[t];    // r, g, b, 1 / sin(theta)
                 const float4 d = sm.D[t];    // scale xyz, rot.r
                 const float4 e = sm.E[t];    // rot xyz, theta
