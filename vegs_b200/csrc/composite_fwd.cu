@@ -10,7 +10,7 @@
 // Gaussians, each touching a handful of pixels, and one block walks them while the other SMs
 // idle.  The only truly sequential part of compositing is the transmittance chain
 // T <- T * (1 - alpha) with its saturation test; everything else is parallel.
-//   SCAN  1024 raw list entries per step, four per thread: keep the entries whose conservative box
+//   SCAN  512 raw list entries per step, two per thread: keep the entries whose conservative box
 //         (preprocess stage) reaches the unit's 32 pixels - one bit of the list word, set by the
 //         emission kernel (binning.cu); survivors are appended in list order to a ring of
 //         candidates (ballot + prefix over the 8 warps).  Repeated until two working sets are
@@ -48,10 +48,10 @@ namespace {
 
 constexpr int kSuper = 256;                 // candidates per working set = threads per CTA
 constexpr int kWarps = kSuper / 32;
-constexpr int kScanSub = 4;                 // list entries per thread and scan step
+constexpr int kScanSub = 2;                 // list entries per thread and scan step
 constexpr int kScanStep = kScanSub * kSuper;
 constexpr int kRow = kSuper + 1;             // row stride of the pixel x slot matrix
-constexpr int kRing = 2048;                 // candidate ring (>= 2 * kSuper + kScanStep, power of two)
+constexpr int kRing = 1024;                 // candidate ring (>= 2 * kSuper + kScanStep, power of two)
 
 struct FwdParams {
     const uint2* ranges;
@@ -73,7 +73,7 @@ struct FwdSmem {
                                     // column of their own rows spread over the banks: (1 - alpha, depth * alpha)
                                     // after S0; S2 replaces the first word by T, the transmittance before the hit
     float4 A[kSuper], B[kSuper], C[kSuper], D[kSuper], E[kSuper];   // records of candidates with a hit
-    uint32_t ring[kRing];           // candidates in list order: ordinal in the tile's list
+    uint2 ring[kRing];              // candidates in list order: (Gaussian id, ordinal in the tile's list)
     uint32_t bits[kWarps][32];      // [segment][pixel]: hits of the pixel inside the segment
     uint32_t stop_at[32];           // first (segment * 32 + hit index) the pixel does not blend (kSuper = none)
     float part[kWarps][10][32];     // segment partials: rows 0-2 colour, 3-5 scale, 6-9 quaternion
@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(kSuper, 2) composite_fwd_kernel(const FwdParam
     PHASE_INIT;
     for (;;) {
         // ---- SCAN: queue candidates until two working sets are ready or the list ends.  With unit
-        // masks in the list words (common.cuh) a step looks at 4 x 256 words and nothing else;
+        // masks in the list words (common.cuh) a step looks at 2 x 256 words and nothing else;
         // without them (ids beyond 24 bits) it gathers the box record of every entry.
         bool scanned = false;
         while (tail - head < 2u * kSuper && raw_base < n) {
@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(kSuper, 2) composite_fwd_kernel(const FwdParam
                 for (int w = 0; w < kWarps; w++) {
                     if (w == warp && keep[j])
                         sm.ring[(tail + run + __popc(bal[j] & ((1u << lane) - 1u))) & (kRing - 1)] =
-                            (uint32_t)(raw_base + j * kSuper + tid);
+                            make_uint2(kMasks ? (w_cur[j] & kListIdMask) : w_cur[j], (uint32_t)(raw_base + j * kSuper + tid));
                     run += sm.scan_cnt[scan_par][j * kWarps + w];
                 }
             }
@@ -203,8 +203,8 @@ __global__ void __launch_bounds__(kSuper, 2) composite_fwd_kernel(const FwdParam
             if (pre_pos == head + tid) {
                 ord = pre_ord; id = pre_id; a_cur = pre_a; b_cur = pre_b;
             } else {
-                ord = sm.ring[(head + tid) & (kRing - 1)];
-                id = kMasks ? (list[ord] & kListIdMask) : list[ord];
+                const uint2 ent = sm.ring[(head + tid) & (kRing - 1)];
+                id = ent.x; ord = ent.y;
                 a_cur = ldg_f4(p.recA + id);
                 b_cur = ldg_f4(p.recB + id);
             }
@@ -212,21 +212,26 @@ __global__ void __launch_bounds__(kSuper, 2) composite_fwd_kernel(const FwdParam
         pre_pos = 0xffffffffu;
         if (head + kSuper + tid < tail) {
             pre_pos = head + kSuper + tid;
-            pre_ord = sm.ring[pre_pos & (kRing - 1)];
-            pre_id = kMasks ? (list[pre_ord] & kListIdMask) : list[pre_ord];
+            const uint2 ent = sm.ring[pre_pos & (kRing - 1)];
+            pre_id = ent.x; pre_ord = ent.y;
             pre_a = ldg_f4(p.recA + pre_id);
             pre_b = ldg_f4(p.recB + pre_id);
         }
 
         // ---- S0: thread = candidate.  Hit mask over the unit's pixels, alpha of every hit.
+        // The blend records are requested first so that their latency hides behind the hit test
+        // (nearly every candidate has a hit).
         uint32_t h = 0;
-        if (tid < m) h = entry_hits_fwd(a_cur, b_cur, bx0, by0, bx1, by1, sm.M, tid, kRow);
-        if (h != 0u) {
-            sm.A[tid] = a_cur;
-            sm.B[tid] = b_cur;
-            sm.C[tid] = ldg_f4(p.recC + id);
-            sm.D[tid] = ldg_f4(p.recD + id);
-            sm.E[tid] = ldg_f4(p.recE + id);
+        if (tid < m) {
+            const float4 c_rec = ldg_f4(p.recC + id), d_rec = ldg_f4(p.recD + id), e_rec = ldg_f4(p.recE + id);
+            h = entry_hits_fwd(a_cur, b_cur, bx0, by0, bx1, by1, sm.M, tid, kRow);
+            if (h != 0u) {
+                sm.A[tid] = a_cur;
+                sm.B[tid] = b_cur;
+                sm.C[tid] = c_rec;
+                sm.D[tid] = d_rec;
+                sm.E[tid] = e_rec;
+            }
         }
         // ---- S1: per-pixel hit lists of this warp's 32-entry segment; the pixel's operands are
         // compacted to the front of the segment's 32 columns (hit j of the segment at column j), in
@@ -239,11 +244,20 @@ __global__ void __launch_bounds__(kSuper, 2) composite_fwd_kernel(const FwdParam
             float2* row = sm.M + lane * kRow + warp * 32;
             uint32_t bits = mybits;
             int j = 0;
+            // four per round: all reads of a round come before its writes (slots >= their targets)
             while (bits != 0u) {
-                const int sl = __ffs(bits) - 1;
-                bits &= bits - 1;
-                if (sl != j) row[j] = row[sl];
-                j++;
+                int sl[4];
+                float2 v[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    sl[k] = bits != 0u ? __ffs(bits) - 1 : -1;
+                    bits &= bits - 1;       // 0 stays 0
+                    if (sl[k] >= 0) v[k] = row[sl[k]];
+                }
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    if (sl[k] >= 0 && sl[k] != j + k) row[j + k] = v[k];
+                j += 4;
             }
         }
         const uint32_t hit_bal = __ballot_sync(0xffffffffu, h != 0u);
@@ -308,7 +322,7 @@ __global__ void __launch_bounds__(kSuper, 2) composite_fwd_kernel(const FwdParam
                 if (last_w >= 0) {
                     // slot of the last blended hit: the (last_j + 1)-th set bit of its segment's mask
                     const int last_t = last_w * 32 + (int)__fns(sm.bits[last_w][lane], 0, last_j + 1);
-                    last_contributor = sm.ring[(head + last_t) & (kRing - 1)] + 1u;   // ordinal in the tile's list
+                    last_contributor = sm.ring[(head + last_t) & (kRing - 1)].y + 1u;   // ordinal in the tile's list
                     uint32_t idx = hit_base;                                           // position in the unit's hit list
                     for (int w2 = 0; w2 < last_w; w2++) idx += __popc(sm.seg_bal[w2]);
                     last_hit = idx + __popc(sm.seg_bal[last_w] & ((1u << (last_t & 31)) - 1u)) + 1u;
