@@ -139,7 +139,8 @@ const char* vegs_last_error(void);
 size_t vegs_geom_bytes(int32_t P);
 size_t vegs_scratch_bytes(int32_t P);
 size_t vegs_img_bytes(int32_t W, int32_t H);
-size_t vegs_binning_bytes(int64_t R);
+size_t vegs_binning_bytes(int64_t R);   /* 68 B per instance: the sorted list + room for the per-unit hit lists the
+                                         * forward pass leaves for the backward (worst case; ~10 % is written) */
 size_t vegs_bin_scratch_bytes(int64_t R, int32_t W, int32_t H);
 size_t vegs_bwd_scratch_bytes(int32_t P);
 
@@ -147,8 +148,9 @@ size_t vegs_bwd_scratch_bytes(int32_t P);
  * Forward, stage 1: per-Gaussian preprocess, depth sort, tile-count scan.
  * Replaces FORWARD::preprocess + InclusiveSum + the num_rendered read-back
  * (cuda_rasterizer/rasterizer_impl.cu:253-286).  Enqueues an asynchronous copy of num_rendered
- * into args->num_rendered_host; the caller synchronises `stream`, reads it, allocates
- * binning / bin_scratch, and calls vegs_forward_render.
+ * into args->num_rendered_host[0] (and of the emission work-item count into [1]); the caller
+ * synchronises `stream`, reads [0], allocates binning / bin_scratch, and calls
+ * vegs_forward_render.
  */
 int vegs_forward_prepare(const VegsForwardArgs* args, void* stream);
 
