@@ -107,7 +107,11 @@ __device__ __forceinline__ float3 sh_to_rgb(const float* sh, int deg, float dx, 
     return make_float3(fmaxf(c[0], 0.0f), fmaxf(c[1], 0.0f), fmaxf(c[2], 0.0f));
 }
 
+// kM: SH coefficients per Gaussian when known at compile time (1, 4, 9, 16), 0 = read p.M.  The
+// staging loop divides element indices by the row length; with a constant that is a multiply.
+template <int kM>
 __global__ void __launch_bounds__(kPreThreads) preprocess_fwd_kernel(const PreParams p) {
+    const int M = kM ? kM : p.M;
     __shared__ float s_sh[kPreWarps][32 * kShStrideMax];
     __shared__ Camera c_cam;
     load_camera(c_cam, p.view, p.proj, p.campos);
@@ -194,13 +198,13 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_fwd_kernel(const PrePa
             rgb.z = p.colors_precomp[3 * (size_t)idx + 2];
         }
     } else {
-        const int rowlen = 3 * p.M;
+        const int rowlen = 3 * M;
         const unsigned vis = __ballot_sync(0xffffffffu, visible);
         if (vis != 0u) {
             const float ddx = mx - c_cam.campos[0];
             const float ddy = my - c_cam.campos[1];
             const float ddz = mz - c_cam.campos[2];
-            if (p.M <= kMaxStageCoeffs) {
+            if (M <= kMaxStageCoeffs) {
                 const int stride = rowlen | 1;
                 float* srow = s_sh[warp];
                 const bool full = (warp_base + 32 <= p.P);
@@ -331,7 +335,13 @@ int launch_preprocess_fwd(const VegsForwardArgs& a, const GeomView& g, const Scr
     p.shs_vec_ok = a.shs != nullptr && (reinterpret_cast<uintptr_t>(a.shs) & 15u) == 0;
     p.rots_vec_ok = a.rotations != nullptr && (reinterpret_cast<uintptr_t>(a.rotations) & 15u) == 0;
     const int blocks = (a.P + kPreThreads - 1) / kPreThreads;
-    preprocess_fwd_kernel<<<blocks, kPreThreads, 0, stream>>>(p);
+    switch (a.M) {
+        case 16: preprocess_fwd_kernel<16><<<blocks, kPreThreads, 0, stream>>>(p); break;
+        case 9:  preprocess_fwd_kernel<9><<<blocks, kPreThreads, 0, stream>>>(p); break;
+        case 4:  preprocess_fwd_kernel<4><<<blocks, kPreThreads, 0, stream>>>(p); break;
+        case 1:  preprocess_fwd_kernel<1><<<blocks, kPreThreads, 0, stream>>>(p); break;
+        default: preprocess_fwd_kernel<0><<<blocks, kPreThreads, 0, stream>>>(p); break;
+    }
     VEGS_LAUNCH_CHECK("preprocess_fwd", stream, a.debug);
     return VEGS_OK;
 }

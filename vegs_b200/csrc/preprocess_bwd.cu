@@ -165,7 +165,11 @@ __device__ __forceinline__ float3 sh_backward(float* row, int deg, int M, float 
     return r;
 }
 
+// kM: SH coefficients per Gaussian when known at compile time (1, 4, 9, 16), 0 = read p.M.  The
+// staging loops divide element indices by the row length; with a constant that is a multiply.
+template <int kM>
 __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbParams p) {
+    const int M = kM ? kM : p.M;
     __shared__ float s_sh[kPbWarps][32 * kShStrideMax];
     __shared__ Camera cam;
     load_camera(cam, p.view, p.proj, p.campos);
@@ -335,7 +339,7 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
 
     // ---- SH backward (row staged in shared memory, coalesced both ways)
     if (p.shs != nullptr && p.dL_dsh != nullptr) {
-        const int rowlen = 3 * p.M;
+        const int rowlen = 3 * M;
         const unsigned vis = __ballot_sync(0xffffffffu, visible);
         float dRGB[3] = {0.f, 0.f, 0.f};
         if (visible) {
@@ -345,7 +349,7 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
             dRGB[2] = (cb & 4u) ? 0.f : dcol[2];
         }
         const float dox = mx - cam.campos[0], doy = my - cam.campos[1], doz = mz - cam.campos[2];
-        if (p.M <= kMaxStageCoeffs) {
+        if (M <= kMaxStageCoeffs) {
             const int stride = rowlen | 1;
             float* srow = s_sh[warp];
             float* myrow = srow + lane * stride;
@@ -377,7 +381,7 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
             }
             __syncwarp();
             if (visible) {
-                const float3 dm = sh_backward(myrow, p.D, p.M, dox, doy, doz, dRGB);
+                const float3 dm = sh_backward(myrow, p.D, M, dox, doy, doz, dRGB);
                 dmean[0] += dm.x; dmean[1] += dm.y; dmean[2] += dm.z;
             } else {
                 for (int k = 0; k < rowlen; k++) myrow[k] = 0.0f;
@@ -405,7 +409,7 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
             if (visible) {
                 const float* src = p.shs + (size_t)idx * rowlen;
                 for (int k = 0; k < 48; k++) dst[k] = src[k];
-                const float3 dm = sh_backward(dst, p.D, p.M, dox, doy, doz, dRGB);
+                const float3 dm = sh_backward(dst, p.D, M, dox, doy, doz, dRGB);
                 dmean[0] += dm.x; dmean[1] += dm.y; dmean[2] += dm.z;
             } else {
                 for (int k = 0; k < rowlen; k++) dst[k] = 0.0f;
@@ -453,7 +457,13 @@ int launch_preprocess_bwd(const VegsBackwardArgs& a, const GeomView& g, const fl
     p.dsh_vec_ok = a.dL_dsh != nullptr && (reinterpret_cast<uintptr_t>(a.dL_dsh) & 15u) == 0;
     p.rots_vec_ok = a.rotations != nullptr && (reinterpret_cast<uintptr_t>(a.rotations) & 15u) == 0;
     const int blocks = (a.P + kPbThreads - 1) / kPbThreads;
-    preprocess_bwd_kernel<<<blocks, kPbThreads, 0, stream>>>(p);
+    switch (a.M) {
+        case 16: preprocess_bwd_kernel<16><<<blocks, kPbThreads, 0, stream>>>(p); break;
+        case 9:  preprocess_bwd_kernel<9><<<blocks, kPbThreads, 0, stream>>>(p); break;
+        case 4:  preprocess_bwd_kernel<4><<<blocks, kPbThreads, 0, stream>>>(p); break;
+        case 1:  preprocess_bwd_kernel<1><<<blocks, kPbThreads, 0, stream>>>(p); break;
+        default: preprocess_bwd_kernel<0><<<blocks, kPbThreads, 0, stream>>>(p); break;
+    }
     VEGS_LAUNCH_CHECK("preprocess_bwd", stream, a.debug);
     return VEGS_OK;
 }
