@@ -85,10 +85,14 @@ class ClockSampler:
         return out
 
 
+FUSED_ACCUM = True      # views 2..n of a step add into .grad inside the backward kernel (--no-fused-accum)
+
+
 def load_rasterizer(impl: str):
     """(module, kind): the GaussianRasterizer implementation under test."""
     if impl == "ours":
         import vegs_b200.diff_gaussian_rasterization as m
+        m.set_fused_grad_accumulation(FUSED_ACCUM)
         return m, "vegs_b200"
     import util
     if util.reference_available():
@@ -254,7 +258,11 @@ def main():
     ap.add_argument("--views", type=int, default=8)
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-fused-accum", action="store_true",
+                    help="let autograd add each view's gradient to .grad instead of the backward kernel")
     args = ap.parse_args()
+    global FUSED_ACCUM
+    FUSED_ACCUM = not args.no_fused_accum
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -303,7 +311,9 @@ def main():
                                      "GaussianRasterizer + grad/densification-stat all-reduce (BASELINE config 3)",
                             P=args.P, views_per_step=args.views, image=[wl.W, wl.H], parallelism=f"view-parallel x{world}",
                             l2="inputs (1.4 GB of parameters per view) exceed the 126 MB L2; no explicit flush",
-                            impl=kind),
+                            impl=kind,
+                            grad_accumulation=("fused into the backward kernel (set_fused_grad_accumulation)"
+                                               if args.impl == "ours" and FUSED_ACCUM else "autograd add per view")),
                 e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=wl.h2d_bytes * len(wl.my_views) // args.views * world,
                          d2h_bytes_per_step=4 * world),
                 gpu_launches=int(launches) if args.impl == "ours" else 0, clocks=clocks)
@@ -329,8 +339,19 @@ def main():
         for k in groups:
             gbs = bts[k] / (groups[k] * 1e-3) / 1e9 if groups[k] > 0 else 0.0
             per[k] = dict(ms_per_view=groups[k], algorithmic_bytes=bts[k], gbs=gbs, frac=gbs / peak)
+        # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
+        # (profiles/ncu_traffic.json, written by scripts/ncu_summary.py); None when there is none
+        traffic, traffic_src = None, None
+        try:
+            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic.json")) as f:
+                tj = json.load(f)
+            if dom in tj.get("bytes_per_launch", {}):
+                traffic, traffic_src = tj["bytes_per_launch"][dom], tj.get("source")
+        except (OSError, ValueError):
+            pass
         line["roofline"] = dict(bound="hbm", kernel=dom, achieved=per[dom]["gbs"], peak=peak, unit="GB/s",
-                                frac=per[dom]["frac"], traffic=None, peak_source=peak_src,
+                                frac=per[dom]["frac"], traffic=traffic, traffic_source=traffic_src,
+                                peak_source=peak_src,
                                 how="CUDA events recorded by the library after every launch on the launching stream, "
                                     "one extra step after the timed region")
         line["kernels"] = per

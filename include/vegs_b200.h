@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define VEGS_ABI_VERSION 1
+#define VEGS_ABI_VERSION 2
 
 enum {
     VEGS_OK = 0,
@@ -129,7 +129,21 @@ typedef struct VegsBackwardArgs {
     float* dL_dscales;        /* [P,3] */
     float* dL_drotations;     /* [P,4] */
     float* dL_dcov3D;         /* [P,6] */
+    /* Fused gradient accumulation (no reference counterpart; the reference's caller adds the
+     * returned gradient to .grad in a separate pass).  For every VEGS_ACC_* bit set, the matching
+     * output pointer must hold valid data and receives old + gradient (rows of Gaussians with
+     * radii == 0 are left untouched); for bits not set the output is overwritten as above.
+     * dL_dmeans2D is always overwritten. */
+    uint32_t accumulate_mask;
 } VegsBackwardArgs;
+
+#define VEGS_ACC_MEANS3D   1u
+#define VEGS_ACC_SH        2u
+#define VEGS_ACC_COLORS    4u
+#define VEGS_ACC_OPACITY   8u
+#define VEGS_ACC_SCALES    16u
+#define VEGS_ACC_ROTATIONS 32u
+#define VEGS_ACC_COV3D     64u
 
 /* Library / ABI identification. */
 int vegs_abi_version(void);

@@ -13,7 +13,7 @@ for s in $stages; do
     smoke)
       timeout 180 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" | tee -a gpurun_out/summary.txt ;;
     tests)
-      for grp in "dist2 and not noalloc" "mark_visible or edge or debug" "against_oracle or modes or deterministic" "golden" "reference_live" "full_size" "noalloc"; do
+      for grp in "dist2 and not noalloc" "mark_visible or edge or debug" "against_oracle or modes or deterministic or fused" "golden" "reference_live" "full_size" "noalloc"; do
         name=$(echo "$grp" | tr ' ' '_')
         timeout 240 python -m pytest tests -m gpu -q -k "$grp" -p no:cacheprovider > "gpurun_out/pytest_${name}.log" 2>&1
         echo "pytest[$grp] rc=$? $(tail -1 gpurun_out/pytest_${name}.log)" | tee -a gpurun_out/summary.txt

@@ -37,5 +37,22 @@ with open(f'profiles/r01_ncu_full_composite_{tag}.md', 'w') as f:
     for w in want:
         if w in idx:
             f.write(f'| {w} | {units[idx[w]]} | ' + ' | '.join(r[idx[w]] for r in rows[2:]) + ' |\n')
+# DRAM traffic per launch (read + write) of the captured kernels, for bench.py's roofline.traffic
+import json, os
+tr = {}
+scale = {'byte': 1.0, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
+for r in rows[2:]:
+    name = r[idx['Kernel Name']]
+    key = 'composite_fwd' if 'composite_fwd' in name else 'composite_bwd' if 'composite_bwd' in name else None
+    if key and key not in tr:
+        tr[key] = (float(r[idx['dram__bytes_read.sum']]) * scale[units[idx['dram__bytes_read.sum']]]
+                   + float(r[idx['dram__bytes_write.sum']]) * scale[units[idx['dram__bytes_write.sum']]])
+old = {}
+if os.path.exists('profiles/ncu_traffic.json'):
+    old = json.load(open('profiles/ncu_traffic.json')).get('bytes_per_launch', {})
+old.update(tr)
+json.dump({'bytes_per_launch': old,
+           'source': f'ncu --set full --clock-control none, dram__bytes_read.sum + dram__bytes_write.sum, one launch (view 0 of the 6 M scene), capture "{tag}"'},
+          open('profiles/ncu_traffic.json', 'w'), indent=1)
 print(open(f'profiles/r01_ncu_launches_6M_{tag}.md').read()[:1800])
 print(open(f'profiles/r01_ncu_full_composite_{tag}.md').read())

@@ -29,7 +29,9 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/vegs_b200.h but not exported"
     assert set(names) == set(_lib.SIGNATURES), "ctypes signature table out of sync with the header"
-    assert lib.vegs_abi_version() == 1
+    import re
+    hdr = open(os.path.join(ROOT, "include", "vegs_b200.h")).read()
+    assert lib.vegs_abi_version() == int(re.search(r"#define VEGS_ABI_VERSION (\d+)", hdr).group(1))
 
 
 def test_struct_layout_matches_header_order():
@@ -47,7 +49,7 @@ def test_struct_layout_matches_header_order():
             for part in decl.replace("*", " ").split(",") if False else [decl]:
                 pass
             # "const float* a" / "int32_t W, H" / "float tan_fovx, tan_fovy"
-            tail = re.sub(r"^(const\s+)?(float|int32_t|void|uint8_t)\s*\**", "", decl).strip()
+            tail = re.sub(r"^(const\s+)?(float|int32_t|uint32_t|void|uint8_t)\s*\**", "", decl).strip()
             fields += [x.strip().lstrip("*").strip() for x in tail.split(",")]
         assert fields == [f[0] for f in cls._fields_], sname
 

@@ -94,6 +94,43 @@ def test_against_oracle_plain_id_lists():
     _check_grads(plain, ref["grads"], rtol=3e-3)
 
 
+def test_fused_grad_accumulation_equals_autograd_accumulation():
+    """Three views accumulated into .grad: with set_fused_grad_accumulation the backward kernel adds
+    into the leaves' .grad itself; the result must equal autograd's separate add (up to the order of
+    the blend stage's floating-point reductions, which differs from run to run)."""
+    import torch
+    import vegs_b200.diff_gaussian_rasterization as dgr
+    dev = torch.device("cuda")
+    scene = util.scene_with_specials(30000)
+    cams = [synth.make_camera(v, scale=0.25) for v in range(3)]
+
+    def accumulate(fused):
+        dgr.set_fused_grad_accumulation(fused)
+        try:
+            t = {k: v.to(dev).clone().requires_grad_(True) for k, v in scene.items() if k in
+                 ("means3D", "opacities", "shs", "scales", "rotations")}
+            for i, cam in enumerate(cams):
+                rs = dgr.GaussianRasterizationSettings(
+                    image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+                    bg=torch.tensor([0.1, 0.2, 0.3], device=dev), scale_modifier=1.0,
+                    viewmatrix=cam.viewmatrix.to(dev), projmatrix=cam.projmatrix.to(dev), sh_degree=3,
+                    campos=cam.campos.to(dev), prefiltered=False, debug=False)
+                means2D = torch.zeros_like(t["means3D"], requires_grad=True)
+                color, depth, quat, scale, alpha, radii = dgr.GaussianRasterizer(rs)(
+                    means3D=t["means3D"], means2D=means2D, opacities=t["opacities"], shs=t["shs"],
+                    scales=t["scales"], rotations=t["rotations"])
+                ((color * (0.5 + i)).sum() + depth.mean() + alpha.sum()).backward()
+                assert means2D.grad is not None
+            return {k: v.grad.detach().cpu().numpy() for k, v in t.items()}
+        finally:
+            dgr.set_fused_grad_accumulation(False)
+
+    plain, fused = accumulate(False), accumulate(True)
+    for k in plain:
+        assert np.abs(plain[k]).max() > 0, k
+        util.grad_close(fused[k], plain[k], f"accumulated grad {k}", rtol=1e-5)
+
+
 def test_modes_colors_precomp_and_cov3d_precomp_against_oracle():
     scene = util.scene_with_specials(4000)
     cam = synth.make_camera(0, scale=0.125)

@@ -50,6 +50,7 @@ class VegsBackwardArgs(C.Structure):
         ("dL_dmeans3D", C.c_void_p), ("dL_dmeans2D", C.c_void_p), ("dL_dsh", C.c_void_p),
         ("dL_dcolors", C.c_void_p), ("dL_dopacity", C.c_void_p), ("dL_dscales", C.c_void_p),
         ("dL_drotations", C.c_void_p), ("dL_dcov3D", C.c_void_p),
+        ("accumulate_mask", C.c_uint32),
     ]
 
 
@@ -97,7 +98,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if a declared symbol is not exported
         fn.restype = res
         fn.argtypes = args
-    if lib.vegs_abi_version() != 1:
+    if lib.vegs_abi_version() != 2:
         raise ImportError("libvegs_b200.so ABI version mismatch; rebuild it")
     _lib = lib
     return lib

@@ -54,6 +54,7 @@ struct PbParams {
     float* dL_drots;
     float* dL_dcov3D;
     bool shs_vec_ok, dsh_vec_ok, rots_vec_ok;
+    uint32_t accum;      // VEGS_ACC_* bits: those outputs receive old + gradient
 };
 
 __device__ __forceinline__ float4 ldg_stream4(const float4* p) {
@@ -387,6 +388,7 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
                 for (int k = 0; k < rowlen; k++) myrow[k] = 0.0f;
             }
             __syncwarp();
+            const bool acc_sh = (p.accum & VEGS_ACC_SH) != 0u;
             if (full && p.dsh_vec_ok) {
                 float4* dst = reinterpret_cast<float4*>(p.dL_dsh + (size_t)warp_base * rowlen);
                 for (int f = lane; f < nvec; f += 32) {
@@ -397,14 +399,22 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
                         const int r = e / rowlen;
                         vv[k] = srow[r * stride + (e - r * rowlen)];
                     }
+                    if (acc_sh) {
+                        // rows of culled Gaussians add nothing: leave chunks that only touch them alone
+                        const int r0 = (4 * f) / rowlen, r1 = (4 * f + 3) / rowlen;
+                        if ((((vis >> r0) | (vis >> r1)) & 1u) == 0u) continue;
+                        const float4 o = dst[f];
+                        vv[0] += o.x; vv[1] += o.y; vv[2] += o.z; vv[3] += o.w;
+                    }
                     dst[f] = make_float4(vv[0], vv[1], vv[2], vv[3]);
                 }
-            } else if (in_range) {
+            } else if (in_range && (!acc_sh || visible)) {
                 float* dst = p.dL_dsh + (size_t)idx * rowlen;
-                for (int k = 0; k < rowlen; k++) dst[k] = myrow[k];
+                for (int k = 0; k < rowlen; k++) dst[k] = acc_sh ? dst[k] + myrow[k] : myrow[k];
             }
         } else if (in_range) {
             // M > 16: no staging; work in the output row directly
+            // (accumulation is refused for M > 16 by the launcher)
             float* dst = p.dL_dsh + (size_t)idx * rowlen;
             if (visible) {
                 const float* src = p.shs + (size_t)idx * rowlen;
@@ -417,23 +427,23 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
         }
     }
 
-    // ---- dense outputs
+    // ---- dense outputs: overwritten, or added to (visible rows only) where accumulation is requested
     if (in_range) {
         const size_t i3 = 3 * (size_t)idx;
-        if (p.dL_dmeans3D) { p.dL_dmeans3D[i3] = dmean[0]; p.dL_dmeans3D[i3 + 1] = dmean[1]; p.dL_dmeans3D[i3 + 2] = dmean[2]; }
-        if (p.dL_dmeans2D) { p.dL_dmeans2D[i3] = dm2d[0]; p.dL_dmeans2D[i3 + 1] = dm2d[1]; p.dL_dmeans2D[i3 + 2] = 0.0f; }
-        if (p.dL_dcolors) { p.dL_dcolors[i3] = dcol[0]; p.dL_dcolors[i3 + 1] = dcol[1]; p.dL_dcolors[i3 + 2] = dcol[2]; }
-        if (p.dL_dopacity) p.dL_dopacity[idx] = dopac;
-        if (p.dL_dscales) { p.dL_dscales[i3] = dscale[0]; p.dL_dscales[i3 + 1] = dscale[1]; p.dL_dscales[i3 + 2] = dscale[2]; }
-        if (p.dL_drots) {
-            float* d = p.dL_drots + 4 * (size_t)idx;
-            d[0] = drot[0]; d[1] = drot[1]; d[2] = drot[2]; d[3] = drot[3];
-        }
-        if (p.dL_dcov3D) {
-            float* d = p.dL_dcov3D + 6 * (size_t)idx;
-#pragma unroll
-            for (int k = 0; k < 6; k++) d[k] = dcov[k];
-        }
+        auto put = [&](float* dst, int n, const float* v, uint32_t bit) {
+            if (dst == nullptr) return;
+            const bool acc = (p.accum & bit) != 0u;
+            if (acc && !visible) return;
+            for (int k = 0; k < n; k++) dst[k] = acc ? dst[k] + v[k] : v[k];
+        };
+        const float dm2[3] = {dm2d[0], dm2d[1], 0.0f};
+        put(p.dL_dmeans3D ? p.dL_dmeans3D + i3 : nullptr, 3, dmean, VEGS_ACC_MEANS3D);
+        put(p.dL_dmeans2D ? p.dL_dmeans2D + i3 : nullptr, 3, dm2, 0u);
+        put(p.dL_dcolors ? p.dL_dcolors + i3 : nullptr, 3, dcol, VEGS_ACC_COLORS);
+        put(p.dL_dopacity ? p.dL_dopacity + idx : nullptr, 1, &dopac, VEGS_ACC_OPACITY);
+        put(p.dL_dscales ? p.dL_dscales + i3 : nullptr, 3, dscale, VEGS_ACC_SCALES);
+        put(p.dL_drots ? p.dL_drots + 4 * (size_t)idx : nullptr, 4, drot, VEGS_ACC_ROTATIONS);
+        put(p.dL_dcov3D ? p.dL_dcov3D + 6 * (size_t)idx : nullptr, 6, dcov, VEGS_ACC_COV3D);
     }
 }
 
@@ -456,6 +466,11 @@ int launch_preprocess_bwd(const VegsBackwardArgs& a, const GeomView& g, const fl
     p.shs_vec_ok = a.shs != nullptr && (reinterpret_cast<uintptr_t>(a.shs) & 15u) == 0;
     p.dsh_vec_ok = a.dL_dsh != nullptr && (reinterpret_cast<uintptr_t>(a.dL_dsh) & 15u) == 0;
     p.rots_vec_ok = a.rotations != nullptr && (reinterpret_cast<uintptr_t>(a.rotations) & 15u) == 0;
+    p.accum = a.accumulate_mask;
+    if ((p.accum & VEGS_ACC_SH) && a.M > kMaxStageCoeffs) {
+        set_error("vegs_backward: VEGS_ACC_SH needs M <= %d", kMaxStageCoeffs);
+        return VEGS_EINVAL;
+    }
     const int blocks = (a.P + kPbThreads - 1) / kPbThreads;
     switch (a.M) {
         case 16: preprocess_bwd_kernel<16><<<blocks, kPbThreads, 0, stream>>>(p); break;

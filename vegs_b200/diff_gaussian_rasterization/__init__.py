@@ -197,10 +197,37 @@ def export_state(st: _State, radii: torch.Tensor):
     return out
 
 
+_ACC_BITS = dict(means3D=1, sh=2, colors=4, opacity=8, scales=16, rotations=32, cov3D=64)   # VEGS_ACC_*
+_fused_grad_accumulation = False
+
+
+def set_fused_grad_accumulation(enabled: bool) -> None:
+    """Opt-in extension (no reference counterpart) for loops that accumulate several views into
+    `.grad` before an optimiser step.  When enabled, the backward pass adds its result straight into
+    the existing `.grad` of every rasterizer input that is a leaf tensor (float32, contiguous, same
+    shape) instead of returning a fresh tensor for autograd to add in a separate pass over the
+    parameters; inputs without a `.grad` yet, and non-leaf inputs, take the normal route.  Hooks
+    registered on those leaves' gradient accumulation do not fire for the fused inputs."""
+    global _fused_grad_accumulation
+    _fused_grad_accumulation = bool(enabled)
+
+
+def _accum_target(t, shape):
+    """`.grad` of leaf `t` if the backward kernel may add into it, else None."""
+    if not _fused_grad_accumulation or t is None or not isinstance(t, torch.Tensor):
+        return None
+    if not (t.is_leaf and t.requires_grad) or t.grad is None:
+        return None
+    g = t.grad
+    ok = (g.dtype == torch.float32 and g.is_cuda and g.device == t.device and g.is_contiguous()
+          and tuple(g.shape) == tuple(shape) and not g.requires_grad)
+    return g if ok else None
+
+
 def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotations,
                    scale_modifier, cov3Ds_precomp, viewmatrix, projmatrix, tanfovx, tanfovy,
                    grad_color, grad_depth, grad_cov_quat, grad_cov_scale, grad_alpha, sh, campos,
-                   out_alpha, opacities_shape, debug):
+                   out_alpha, opacities_shape, debug, leaves=None):
     lib = _lib.load()
     device = means3D.device
     P, M = st.P, st.M
@@ -232,14 +259,30 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
         rotations = _dev_f32(rotations, device, "rotations")
         cov3Ds_precomp = _dev_f32(cov3Ds_precomp, device, "cov3D_precomp")
 
-        dmeans3D = torch.empty((P, 3), **f32)
+        # outputs: a fresh tensor, or (fused accumulation) the leaf's existing .grad, added to in place
+        leaves = leaves or {}
+        acc_mask = 0
+        fused = {}
+
+        def out(name, shape, wanted=True):
+            nonlocal acc_mask
+            if not wanted:
+                return None
+            tgt = _accum_target(leaves.get(name), shape) if M <= 16 or name != "sh" else None
+            if tgt is not None:
+                acc_mask |= _ACC_BITS[name]
+                fused[name] = True
+                return tgt
+            return torch.empty(shape, **f32)
+
+        dmeans3D = out("means3D", (P, 3))
         dmeans2D = torch.empty((P, 3), **f32)
-        dopac = torch.empty(opacities_shape, **f32)
-        dsh = torch.empty((P, M, 3), **f32) if have_sh else None
-        dcolors = None if have_sh else torch.empty((P, 3), **f32)
-        dscales = torch.empty((P, 3), **f32) if have_sr else None
-        drots = torch.empty((P, 4), **f32) if have_sr else None
-        dcov = torch.empty((P, 6), **f32) if have_cov else None
+        dopac = out("opacity", tuple(opacities_shape))
+        dsh = out("sh", (P, M, 3), have_sh)
+        dcolors = out("colors", (P, 3), not have_sh)
+        dscales = out("scales", (P, 3), have_sr)
+        drots = out("rotations", (P, 4), have_sr)
+        dcov = out("cov3D", (P, 6), have_cov)
         bwd_scratch = torch.empty(lib.vegs_bwd_scratch_bytes(P), dtype=torch.uint8, device=device)
 
         b = _lib.VegsBackwardArgs()
@@ -268,8 +311,12 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
         b.dL_dopacity = dopac.data_ptr()
         b.dL_dscales, b.dL_drotations = _ptr(dscales), _ptr(drots)
         b.dL_dcov3D = _ptr(dcov)
+        b.accumulate_mask = acc_mask
         _lib.check(lib.vegs_backward(C.byref(b), C.c_void_p(stream.cuda_stream)), "vegs_backward")
-    return dmeans3D, dmeans2D, dsh, dcolors, dopac, dscales, drots, dcov
+    # inputs whose .grad already received the result get no gradient from autograd
+    nf = lambda name, t: None if name in fused else t
+    return (nf("means3D", dmeans3D), dmeans2D, nf("sh", dsh), nf("colors", dcolors), nf("opacity", dopac),
+            nf("scales", dscales), nf("rotations", drots), nf("cov3D", dcov))
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
@@ -304,6 +351,9 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.opacities_shape = tuple(opacities.shape)
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh,
                               alpha)
+        # the input objects themselves, to find leaves whose .grad the backward may add into
+        ctx.leaves = dict(means3D=means3D, sh=sh, colors=colors_precomp, opacity=opacities, scales=scales,
+                          rotations=rotations, cov3D=cov3Ds_precomp) if _fused_grad_accumulation else None
         ctx.mark_non_differentiable(radii)
         return color, depth, cov_quat, cov_scale, alpha, radii
 
@@ -319,13 +369,13 @@ class _RasterizeGaussians(torch.autograd.Function):
         if rs.debug:
             cpu_args = cpu_deep_copy_tuple(args[1:])
             try:
-                grads = _backward_impl(*args)
+                grads = _backward_impl(*args, leaves=ctx.leaves)
             except Exception as ex:
                 torch.save(cpu_args, "snapshot_bw.dump")
                 print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
                 raise ex
         else:
-            grads = _backward_impl(*args)
+            grads = _backward_impl(*args, leaves=ctx.leaves)
         (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales,
          grad_rotations, grad_cov3Ds_precomp) = grads
         return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities,
