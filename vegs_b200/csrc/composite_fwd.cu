@@ -26,7 +26,7 @@
 //       n_contrib, plus the depth sum — a handful of instructions per hit
 //   S3  pixel-parallel per 32-candidate segment (8 warps, lane = pixel): colour and scale sums and
 //       the slerp quaternion product of the segment's hits with the T values from S2
-//   S4  warp 0 folds the eight segment partials into the pixel state, in list order
+//   S4  warps 0 and 1 fold the eight segment partials into the pixel state, in list order
 // so the expensive work (exp, sin, cos, quaternion product per contribution) is spread over 8
 // warps per pixel block and 64 warps per tile, the fixed costs of a working set are paid per 256
 // candidates rather than per 256 list entries, units are issued longest-list-first, and a unit
@@ -82,6 +82,23 @@ struct FwdSmem {
     int all_done;
 };
 
+// sin and cos of x in [0, pi] (w * theta of the slerp: w in [0, 1], theta = acos(.)), ~1 ulp: one
+// Cody-Waite reduction to [-pi/4, pi/4] shared by both, Cephes single-precision polynomials.  The
+// library sinf + cosf pair reduces twice and carries a large-argument path that cannot occur here.
+__device__ __forceinline__ void sincos_0_pi(float x, float& s, float& c) {
+    const float j = rintf(x * 0.636619772f);                 // 0, 1 or 2 quarter turns
+    float r = fmaf(j, -1.5703125f, x);
+    r = fmaf(j, -4.837512969970703125e-4f, r);
+    r = fmaf(j, -7.54978995489188e-8f, r);
+    const float r2 = r * r;
+    const float sp = fmaf(fmaf(fmaf(-1.9515295891e-4f, r2, 8.3321608736e-3f), r2, -1.6666654611e-1f), r2 * r, r);
+    const float cp = fmaf(fmaf(fmaf(2.443315711809948e-5f, r2, -1.388731625493765e-3f), r2, 4.166664568298827e-2f),
+                          r2 * r2, fmaf(-0.5f, r2, 1.0f));
+    const int q = (int)j;
+    s = (q == 1) ? cp : (q == 2 ? -sp : sp);
+    c = (q == 1) ? -sp : (q == 2 ? -cp : cp);
+}
+
 #if VEGS_TILE_DEBUG
 #define PHASE_INIT long long ph_t = clock64(), ph_acc[4] = {0, 0, 0, 0}; uint32_t dbg_sets = 0, dbg_cand = 0, dbg_pix = 0
 #define PHASE_MARK(k) { long long now_; asm volatile("mov.u64 %0, %%clock64;" : "=l"(now_) :: "memory"); ph_acc[k] += now_ - ph_t; ph_t = now_; }
@@ -114,7 +131,7 @@ __global__ void __launch_bounds__(kSuper, 2) composite_fwd_kernel(const FwdParam
     const int n = (int)(range.y - range.x);
     const uint32_t* list = p.point_list + range.x;
 
-    // pixel state, meaningful in warp 0 only
+    // pixel state: T, depth, quaternion, contributor counts in warp 0; colour and scale sums in warp 1
     float T = 1.0f;
     float C0 = 0.f, C1 = 0.f, C2 = 0.f, Dacc = 0.f;
     float S0 = 0.f, S1 = 0.f, S2 = 0.f;
@@ -376,9 +393,8 @@ __global__ void __launch_bounds__(kSuper, 2) composite_fwd_kernel(const FwdParam
                     // glm::mix: (sin((1-w) theta) * identity + sin(w theta) * q) / sin(theta).  With
                     // rot.r = cos(theta) the real part is cos(w theta) identically, and 1 / sin(theta)
                     // is precomputed per Gaussian: no divisions
-                    // (sinf + cosf measured faster than sincosf, which returns through local memory)
-                    const float wt = __fmul_rn(wgt, e.w);
-                    const float sn1 = sinf(wt), cs1 = cosf(wt);
+                    float sn1, cs1;
+                    sincos_0_pi(__fmul_rn(wgt, e.w), sn1, cs1);
                     const float k = __fmul_rn(sn1, c.w);
                     rw = cs1;
                     rx = __fmul_rn(e.x, k);
@@ -400,14 +416,22 @@ __global__ void __launch_bounds__(kSuper, 2) composite_fwd_kernel(const FwdParam
         __syncthreads();
         PHASE_MARK(3);
 
-        // ---- S4: warp 0 folds the segment partials into the pixel state, in list order.  The other
-        // warps already start the next scan / working set (they only write arrays S4 does not read).
-        if (warp == 0) {
+        // ---- S4: the segment partials are folded into the pixel state, in list order: warp 0 (which
+        // also owns T and the depth sum) folds the quaternion, warp 1 the colour and scale sums.  The
+        // other warps already start the next scan / working set (they only write arrays S4 does
+        // not read).
+        if (warp == 1) {
             for (int w = 0; w < kWarps; w++) {
                 if (((seg_mask >> w) & 1u) == 0u) continue;
                 float (*pp)[32] = sm.part[w];
                 C0 += pp[0][lane]; C1 += pp[1][lane]; C2 += pp[2][lane];
                 S0 += pp[3][lane]; S1 += pp[4][lane]; S2 += pp[5][lane];
+            }
+        }
+        if (warp == 0) {
+            for (int w = 0; w < kWarps; w++) {
+                if (((seg_mask >> w) & 1u) == 0u) continue;
+                float (*pp)[32] = sm.part[w];
                 const float rw = pp[6][lane], rx = pp[7][lane], ry = pp[8][lane], rz = pp[9][lane];
                 const float nw = Qw * rw - Qx * rx - Qy * ry - Qz * rz;
                 const float nx = Qw * rx + Qx * rw + Qy * rz - Qz * ry;
@@ -420,15 +444,26 @@ __global__ void __launch_bounds__(kSuper, 2) composite_fwd_kernel(const FwdParam
         head += (uint32_t)m;
     }
 
+    // final transmittance to warp 1 (stop_at is free now), which owns the colour sums
+    if (warp == 0) sm.stop_at[lane] = __float_as_uint(T);
+    __syncthreads();
+    if (warp == 1 && inside) {
+        const size_t npix = (size_t)p.W * p.H;
+        const size_t pid = (size_t)py * p.W + px;
+        const float T_fin = __uint_as_float(sm.stop_at[lane]);
+        p.out_color[pid] = C0 + T_fin * p.bg[0];
+        p.out_color[npix + pid] = C1 + T_fin * p.bg[1];
+        p.out_color[2 * npix + pid] = C2 + T_fin * p.bg[2];
+        p.out_scale[pid] = S0;
+        p.out_scale[npix + pid] = S1;
+        p.out_scale[2 * npix + pid] = S2;
+    }
     if (warp == 0 && inside) {
         const size_t npix = (size_t)p.W * p.H;
         const size_t pid = (size_t)py * p.W + px;
         p.out_alpha[pid] = 1.0f - T;
         p.n_contrib[pid] = last_contributor;
         p.last_hit[pid] = last_hit;
-        p.out_color[pid] = C0 + T * p.bg[0];
-        p.out_color[npix + pid] = C1 + T * p.bg[1];
-        p.out_color[2 * npix + pid] = C2 + T * p.bg[2];
         p.out_depth[pid] = Dacc;
         // glm::normalize(quat): identity when the length is not positive
         const float len = sqrtf(Qw * Qw + Qx * Qx + Qy * Qy + Qz * Qz);
@@ -441,9 +476,6 @@ __global__ void __launch_bounds__(kSuper, 2) composite_fwd_kernel(const FwdParam
         p.out_quat[npix + pid] = ox;
         p.out_quat[2 * npix + pid] = oy;
         p.out_quat[3 * npix + pid] = oz;
-        p.out_scale[pid] = S0;
-        p.out_scale[npix + pid] = S1;
-        p.out_scale[2 * npix + pid] = S2;
     }
     if (tid == 0) atomicMax(&p.tile_clocks[tile], (uint32_t)((clock64() - t_start) >> 10));
 #if VEGS_TILE_DEBUG
