@@ -30,9 +30,9 @@ for s in $stages; do
       timeout 1200 python scripts/bench_configs.py > gpurun_out/configs.json 2> gpurun_out/configs.err; echo "configs rc=$?" | tee -a gpurun_out/summary.txt ;;
     sweep)
       # super-batch size of the compositing kernels (threads per CTA): rebuild and time each
-      for sz in ${VEGS_SWEEP:-128 64}; do
+      for sz in ${VEGS_SWEEP:-128}; do
         touch vegs_b200/csrc/composite_fwd.cu vegs_b200/csrc/composite_bwd.cu
-        VEGS_NVCC_EXTRA="-DVEGS_FWD_SUPER=$sz -DVEGS_BWD_SUPER=$sz" python vegs_b200/build.py > gpurun_out/sweep_build_$sz.log 2>&1
+        VEGS_NVCC_EXTRA="-DVEGS_FWD_SUPER=$sz" python vegs_b200/build.py > gpurun_out/sweep_build_$sz.log 2>&1
         timeout 600 python bench.py --steps 6 --warmup 3 --no-cpu-baseline > gpurun_out/sweep_$sz.json 2> gpurun_out/sweep_$sz.err
         echo "sweep $sz rc=$?" | tee -a gpurun_out/summary.txt
         timeout 600 python -m pytest tests -m gpu -q -k "against_oracle or golden" -p no:cacheprovider > gpurun_out/sweep_pytest_$sz.log 2>&1

@@ -46,12 +46,16 @@ namespace vegs {
 
 namespace {
 
-constexpr int kSuper = 256;                 // candidates per working set = threads per CTA
+#ifndef VEGS_FWD_SUPER
+#define VEGS_FWD_SUPER 256
+#endif
+constexpr int kSuper = VEGS_FWD_SUPER;      // candidates per working set = threads per CTA
 constexpr int kWarps = kSuper / 32;
+constexpr int kMinCtas = kSuper == 256 ? 2 : 4;
 constexpr int kScanSub = 2;                 // list entries per thread and scan step
 constexpr int kScanStep = kScanSub * kSuper;
 constexpr int kRow = kSuper + 1;             // row stride of the pixel x slot matrix
-constexpr int kRing = 1024;                 // candidate ring (>= 2 * kSuper + kScanStep, power of two)
+constexpr int kRing = 4 * kSuper;            // candidate ring (>= 2 * kSuper + kScanStep, power of two)
 
 struct FwdParams {
     const uint2* ranges;
@@ -108,7 +112,7 @@ __device__ __forceinline__ void sincos_0_pi(float x, float& s, float& c) {
 #endif
 
 template <bool kMasks>
-__global__ void __launch_bounds__(kSuper, 2) composite_fwd_kernel(const FwdParams p) {
+__global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const FwdParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     FwdSmem& sm = *reinterpret_cast<FwdSmem*>(smem_raw);
 
