@@ -40,16 +40,6 @@ for s in $stages; do
       done
       touch vegs_b200/csrc/composite_fwd.cu vegs_b200/csrc/composite_bwd.cu
       python vegs_b200/build.py > gpurun_out/sweep_build_default.log 2>&1 ;;
-    exp)
-      # A/B of experimental compile-time switches in the compositing kernels
-      for flag in ${VEGS_EXP:-NOPIPE SIN2 ENDBAR}; do
-        touch vegs_b200/csrc/composite_fwd.cu vegs_b200/csrc/composite_bwd.cu
-        VEGS_NVCC_EXTRA="-DVEGS_EXP_$flag" python vegs_b200/build.py > gpurun_out/exp_build_$flag.log 2>&1
-        timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/exp_$flag.json 2> gpurun_out/exp_$flag.err
-        echo "exp $flag rc=$?" | tee -a gpurun_out/summary.txt
-      done
-      touch vegs_b200/csrc/composite_fwd.cu vegs_b200/csrc/composite_bwd.cu
-      python vegs_b200/build.py > gpurun_out/exp_build_default.log 2>&1 ;;
     tilestats)
       touch vegs_b200/csrc/composite_fwd.cu vegs_b200/csrc/composite_bwd.cu
       VEGS_TILE_DEBUG=1 python vegs_b200/build.py > gpurun_out/dbg_build.log 2>&1

@@ -103,6 +103,10 @@ __device__ __forceinline__ void sincos_0_pi(float x, float& s, float& c) {
     c = (q == 1) ? -sp : (q == 2 ? -cp : cp);
 }
 
+__device__ __forceinline__ void prefetch_l2(const void* ptr) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
+}
+
 #if VEGS_TILE_DEBUG
 #define PHASE_INIT long long ph_t = clock64(), ph_acc[4] = {0, 0, 0, 0}; uint32_t dbg_sets = 0, dbg_cand = 0, dbg_pix = 0
 #define PHASE_MARK(k) { long long now_; asm volatile("mov.u64 %0, %%clock64;" : "=l"(now_) :: "memory"); ph_acc[k] += now_ - ph_t; ph_t = now_; }
@@ -199,9 +203,15 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
             for (int j = 0; j < kScanSub; j++) {
 #pragma unroll
                 for (int w = 0; w < kWarps; w++) {
-                    if (w == warp && keep[j])
+                    if (w == warp && keep[j]) {
+                        const uint32_t gid = kMasks ? (w_cur[j] & kListIdMask) : w_cur[j];
                         sm.ring[(tail + run + __popc(bal[j] & ((1u << lane) - 1u))) & (kRing - 1)] =
-                            make_uint2(kMasks ? (w_cur[j] & kListIdMask) : w_cur[j], (uint32_t)(raw_base + j * kSuper + tid));
+                            make_uint2(gid, (uint32_t)(raw_base + j * kSuper + tid));
+                        // the candidate's records will be gathered by another thread one or two
+                        // working sets from now: start them on their way to L2
+                        prefetch_l2(p.recA + gid); prefetch_l2(p.recB + gid); prefetch_l2(p.recC + gid);
+                        prefetch_l2(p.recD + gid); prefetch_l2(p.recE + gid);
+                    }
                     run += sm.scan_cnt[scan_par][j * kWarps + w];
                 }
             }
@@ -310,6 +320,7 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
                 bool stopped = done;         // every lane stays in the loops below (warp votes)
 #pragma unroll 1
                 for (int w = 0; w < kWarps; w++) {
+                    if (((seg_mask >> w) & 1u) == 0u) continue;     // no hit in this segment at all
                     const int cnt = stopped ? 0 : __popc(sm.bits[w][lane]);
                     float2* row = sm.M + lane * kRow + w * 32;
                     // the lanes run in lock step: rounds of four hits until the longest list of the
