@@ -129,10 +129,21 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_fwd_kernel(const PrePa
     int radius = 0;
     int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
 
+    // Every per-Gaussian input is requested up front (nine in ten Gaussians survive the culls):
+    // the loads overlap instead of queueing behind the depth test.
+    float in_sx = 0.f, in_sy = 0.f, in_sz = 0.f, in_op = 0.f;
+    float4 in_q = make_float4(1.f, 0.f, 0.f, 0.f);
     if (in_range) {
         mx = p.means[3 * (size_t)idx + 0];
         my = p.means[3 * (size_t)idx + 1];
         mz = p.means[3 * (size_t)idx + 2];
+        if (p.scales != nullptr) {
+            in_sx = p.scales[3 * (size_t)idx + 0];
+            in_sy = p.scales[3 * (size_t)idx + 1];
+            in_sz = p.scales[3 * (size_t)idx + 2];
+        }
+        if (p.rots != nullptr) in_q = load_quat(p.rots, idx, p.rots_vec_ok);
+        in_op = p.opac[idx];
         depth = affine_row(c_cam.view, 2, 6, 10, 14, mx, my, mz);
         // Near cull, the only frustum test (auxiliary.h:154); NaN depth passes, as in the reference.
         if (!(depth <= 0.2f)) {
@@ -148,11 +159,7 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_fwd_kernel(const PrePa
 #pragma unroll
                 for (int k = 0; k < 6; k++) c3[k] = p.cov3D_precomp[6 * (size_t)idx + k];
             } else {
-                const float sx = p.scales[3 * (size_t)idx + 0];
-                const float sy = p.scales[3 * (size_t)idx + 1];
-                const float sz = p.scales[3 * (size_t)idx + 2];
-                const float4 q = load_quat(p.rots, idx, p.rots_vec_ok);
-                cov3d_from_scale_rot(sx, sy, sz, p.mod, q.x, q.y, q.z, q.w, c3);
+                cov3d_from_scale_rot(in_sx, in_sy, in_sz, p.mod, in_q.x, in_q.y, in_q.z, in_q.w, c3);
             }
             Cov2DTerms tt;
             const float3 cov = cov2d_project(mx, my, mz, p.focal_x, p.focal_y, p.tan_fovx,
@@ -173,7 +180,7 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_fwd_kernel(const PrePa
                 tile_rect(pix_x, pix_y, radius, p.gx, p.gy, x0, y0, x1, y1);
                 if ((x1 - x0) * (y1 - y0) != 0) {
                     visible = true;
-                    opacity = p.opac[idx];
+                    opacity = in_op;
                 }
             }
         }
@@ -244,15 +251,10 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_fwd_kernel(const PrePa
     if (visible) {
         float4 d4 = make_float4(0.f, 0.f, 0.f, 1.f);   // scale 0, identity rotation when absent
         float4 e4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (p.scales != nullptr) {
-            d4.x = p.scales[3 * (size_t)idx + 0];
-            d4.y = p.scales[3 * (size_t)idx + 1];
-            d4.z = p.scales[3 * (size_t)idx + 2];
-        }
+        if (p.scales != nullptr) { d4.x = in_sx; d4.y = in_sy; d4.z = in_sz; }
         if (p.rots != nullptr) {
-            const float4 q = load_quat(p.rots, idx, p.rots_vec_ok);
-            d4.w = q.x;
-            e4.x = q.y; e4.y = q.z; e4.z = q.w;
+            d4.w = in_q.x;
+            e4.x = in_q.y; e4.y = in_q.z; e4.z = in_q.w;
         }
         const float theta = acosf(d4.w);
         e4.w = theta;

@@ -180,7 +180,26 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
     const int idx = blockIdx.x * kPbThreads + threadIdx.x;
     const int warp_base = idx - lane;
     const bool in_range = idx < p.P;
-    const bool visible = in_range && p.radii[idx] > 0;
+    // Every per-Gaussian input is requested before the visibility test (nine in ten Gaussians are
+    // visible): the loads overlap instead of queueing behind the radius.
+    float in_m[3] = {0.f, 0.f, 0.f}, in_s[3] = {0.f, 0.f, 0.f};
+    float4 in_q = make_float4(1.f, 0.f, 0.f, 0.f);
+    float4 in_a0 = make_float4(0.f, 0.f, 0.f, 0.f), in_a1 = in_a0, in_a2 = in_a0;
+    int in_radius = 0;
+    if (in_range) {
+        in_radius = p.radii[idx];
+#pragma unroll
+        for (int k = 0; k < 3; k++) in_m[k] = p.means[3 * (size_t)idx + k];
+        in_a0 = p.acc[3 * (size_t)idx + 0];
+        in_a1 = p.acc[3 * (size_t)idx + 1];
+        in_a2 = p.acc[3 * (size_t)idx + 2];
+        if (p.cov3D_precomp == nullptr) {
+#pragma unroll
+            for (int k = 0; k < 3; k++) in_s[k] = p.scales[3 * (size_t)idx + k];
+            in_q = load_quat(p.rots, idx, p.rots_vec_ok);
+        }
+    }
+    const bool visible = in_range && in_radius > 0;
 
     float dmean[3] = {0.f, 0.f, 0.f};
     float dm2d[2] = {0.f, 0.f};
@@ -192,12 +211,10 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
     float mx = 0.f, my = 0.f, mz = 0.f;
 
     if (visible) {
-        mx = p.means[3 * (size_t)idx + 0];
-        my = p.means[3 * (size_t)idx + 1];
-        mz = p.means[3 * (size_t)idx + 2];
-        const float4 a0 = p.acc[3 * (size_t)idx + 0];  // dmean2D.xy, dconic.xx, dconic.xy
-        const float4 a1 = p.acc[3 * (size_t)idx + 1];  // dconic.yy, dopacity, dcol.r, dcol.g
-        const float4 a2 = p.acc[3 * (size_t)idx + 2];  // dcol.b, ddepth
+        mx = in_m[0]; my = in_m[1]; mz = in_m[2];
+        const float4 a0 = in_a0;  // dmean2D.xy, dconic.xx, dconic.xy
+        const float4 a1 = in_a1;  // dconic.yy, dopacity, dcol.r, dcol.g
+        const float4 a2 = in_a2;  // dcol.b, ddepth
         dm2d[0] = a0.x; dm2d[1] = a0.y;
         const float dcx = a0.z, dcy = a0.w, dcz = a1.x;
         dopac = a1.y;
@@ -212,10 +229,8 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
 #pragma unroll
             for (int k = 0; k < 6; k++) c3[k] = p.cov3D_precomp[6 * (size_t)idx + k];
         } else {
-            sx = p.scales[3 * (size_t)idx + 0];
-            sy = p.scales[3 * (size_t)idx + 1];
-            sz = p.scales[3 * (size_t)idx + 2];
-            q = load_quat(p.rots, idx, p.rots_vec_ok);
+            sx = in_s[0]; sy = in_s[1]; sz = in_s[2];
+            q = in_q;
             cov3d_from_scale_rot(sx, sy, sz, p.mod, q.x, q.y, q.z, q.w, c3);
         }
 
