@@ -2,11 +2,13 @@
 //
 // Work decomposition of both kernels: the unit of work is one 8x4 pixel block of a 16x16 tile
 // (8 blocks per tile), processed by one 8-warp CTA that walks the tile's depth-sorted instance list;
-// units are independent and issued longest-list-first.  The CTA first SCANS the raw list 256
-// entries at a time (one 16-byte record per entry: clip the Gaussian's conservative box, half
-// extents from the preprocess stage, to the block) and appends the survivors, in list order, to a
-// ring of candidates; whenever 256 candidates are queued (or the list ends) it PROCESSES them as
-// one working set, alternating between two views of the same problem:
+// units are independent and issued longest-list-first.  The forward CTA first SCANS the raw list
+// (does the Gaussian's conservative box, half extents from the preprocess stage, reach the block?
+// - one bit of the list word, or a 16-byte record per entry when ids need all 32 bits) and appends
+// the survivors, in list order, to a ring of candidates; whenever 256 candidates are queued (or
+// the list ends) it PROCESSES them as one working set.  The backward CTA walks the hit list the
+// forward left for its unit, 256 entries per working set.  A working set alternates between two
+// views of the same problem:
 //   entry-parallel   thread t owns candidate t: it evaluates the reference's exact contribution
 //                    test on the few pixels inside the clipped box, giving a 32-bit hit mask over
 //                    the block's pixels and each hit's alpha;

@@ -16,14 +16,16 @@
 //         candidates (ballot + prefix over the 8 warps).  Repeated until two working sets are
 //         queued or the list ends.
 //   then, per working set of 256 candidates:
-//   S0  entry-parallel: run the reference's exact contribution test on the pixels inside the box,
-//       keep a 32-bit hit mask and each hit's alpha (alpha matrix in shared memory); entries with
-//       a hit stage their packed records
-//   S1  each warp bit-transposes its 32 hit masks into per-pixel hit lists
+//   S0  entry-parallel: run the reference's exact contribution test on the pixels inside the box
+//       (each pixel row narrowed to the interval the quadratic can reach), keep a 32-bit hit mask
+//       and (1 - alpha, depth * alpha) of each hit in a 32 x 257 shared matrix; entries with a hit
+//       stage their packed records and are appended to the unit's hit list for the backward pass
+//   S1  each warp bit-transposes its 32 hit masks into per-pixel hit lists and compacts each
+//       pixel's operands to the front of its row segment
 //   S2  warp 0, lane = pixel: the sequential chain over that pixel's hits of the working set, in
 //       list order and in the reference's float operation order: T before each hit, the
 //       saturation point (T(1-alpha) < 1e-4 stops the pixel, that Gaussian is not blended),
-//       n_contrib, plus the depth sum — a handful of instructions per hit
+//       n_contrib, plus the depth sum — branch-free rounds of four hits over dense arrays
 //   S3  pixel-parallel per 32-candidate segment (8 warps, lane = pixel): colour and scale sums and
 //       the slerp quaternion product of the segment's hits with the T values from S2
 //   S4  warps 0 and 1 fold the eight segment partials into the pixel state, in list order
