@@ -294,7 +294,11 @@ int launch_composite_bwd(const VegsBackwardArgs& a, const GeomView& g, const Img
     const int T = p.gx * ((a.H + kTile - 1) / kTile);
     p.tile_clocks = const_cast<uint32_t*>(im.tile_clocks) + T;
     p.tile_dbg = const_cast<uint32_t*>(im.tile_dbg);
-    static bool configured = false;
+    // opt-in shared memory size is a per-device function attribute
+    static bool configured_dev[64] = {};
+    int dev = 0;
+    VEGS_CUDA_OK(cudaGetDevice(&dev));
+    bool& configured = configured_dev[dev & 63];
     if (!configured) {
         VEGS_CUDA_OK(cudaFuncSetAttribute(composite_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)sizeof(BwdSmem)));

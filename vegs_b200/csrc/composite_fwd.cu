@@ -525,7 +525,11 @@ int launch_composite_fwd(const VegsForwardArgs& a, const GeomView& g, const Scra
     p.tile_clocks = im.tile_clocks;
     p.tile_dbg = im.tile_dbg;
     const int T = p.gx * ((a.H + kTile - 1) / kTile);
-    static bool configured = false;
+    // opt-in shared memory size is a per-device function attribute
+    static bool configured_dev[64] = {};
+    int dev = 0;
+    VEGS_CUDA_OK(cudaGetDevice(&dev));
+    bool& configured = configured_dev[dev & 63];
     if (!configured) {
         VEGS_CUDA_OK(cudaFuncSetAttribute(composite_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)sizeof(FwdSmem)));
