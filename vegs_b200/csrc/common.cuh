@@ -2,10 +2,10 @@
 //
 // Data layout in HBM (all sub-arrays 256-byte aligned inside caller-provided byte buffers):
 //
-//   geom    (kept for backward)  recA,recB,recC : float4[P]   packed per-Gaussian records
+//   geom    (kept for backward)  recA,recB,recC : float4, interleaved per Gaussian (64-byte stride)
 //                                clamped        : uint8[P]    SH clamp bits (bit c = channel c)
 //                                counters       : uint32[64]  [0] = num_rendered
-//   scratch (forward only)       recD,recE      : float4[P]   scale / rotation / slerp constants
+//   scratch (forward only)       recD,recE      : float4, interleaved per Gaussian (32-byte stride)
 //                                rect           : uint2[P]    tile rectangle (min | max<<16)
 //                                keys0/1,vals0/1: uint32[P]   depth-sort ping-pong
 //                                hist, rowtot, chunk sums
@@ -43,6 +43,11 @@ constexpr int kRadix = 1 << kRadixBits;
 
 // ---------------------------------------------------------------- emission configuration
 constexpr int kUnitsPerTile = 8;  // compositing units (8x4 pixel blocks) per 16x16 tile
+// Packed records are interleaved per Gaussian so that a gather touches whole 32-byte sectors:
+// geom holds {recA, recB, recC, pad} (64 B), scratch holds {recD, recE} (32 B).  recX[g] lives at
+// recX + stride * g with these strides (in float4 units).
+constexpr int kGeomRecStride = 4;
+constexpr int kScratchRecStride = 2;
 // Instance list words: Gaussian id, plus - when every id fits 24 bits - in the top byte the mask of
 // the tile's compositing units the Gaussian's conservative box reaches (written by the emission
 // kernel), so a unit rejects an entry from the list word alone.
@@ -116,9 +121,9 @@ static inline GeomView geom_view(void* base, int P) {
     GeomView v;
     char* cur = reinterpret_cast<char*>(base);
     size_t n = (size_t)(P > 0 ? P : 1);
-    v.recA = carve<float4>(cur, n);
-    v.recB = carve<float4>(cur, n);
-    v.recC = carve<float4>(cur, n);
+    v.recA = carve<float4>(cur, (size_t)kGeomRecStride * n);   // interleaved {A, B, C, pad}
+    v.recB = v.recA + 1;
+    v.recC = v.recA + 2;
     v.clamped = carve<uint8_t>(cur, n);
     v.counters = carve<uint32_t>(cur, 64);
     v.bytes = (size_t)(cur - reinterpret_cast<char*>(base));
@@ -129,8 +134,8 @@ static inline ScratchView scratch_view(void* base, int P) {
     ScratchView v;
     char* cur = reinterpret_cast<char*>(base);
     size_t n = (size_t)(P > 0 ? P : 1);
-    v.recD = carve<float4>(cur, n);
-    v.recE = carve<float4>(cur, n);
+    v.recD = carve<float4>(cur, (size_t)kScratchRecStride * n);   // interleaved {D, E}
+    v.recE = v.recD + 1;
     v.rect = carve<uint2>(cur, n);
     v.pbox = carve<uint2>(cur, n);
     v.keys0 = carve<uint32_t>(cur, n);

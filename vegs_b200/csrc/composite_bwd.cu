@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(kSuper, 3) composite_bwd_kernel(const BwdParam
     float4 a_cur = make_float4(0.f, 0.f, 0.f, 0.f), b_cur = a_cur, c_cur = a_cur;
     if (n - 1 - tid >= 0) {
         ent = list[n - 1 - tid];
-        a_cur = ldg_f4(p.recA + ent.x); b_cur = ldg_f4(p.recB + ent.x); c_cur = ldg_f4(p.recC + ent.x);
+        a_cur = ldg_f4(p.recA + (size_t)kGeomRecStride * ent.x); b_cur = ldg_f4(p.recB + (size_t)kGeomRecStride * ent.x); c_cur = ldg_f4(p.recC + (size_t)kGeomRecStride * ent.x);
     }
 
     PHASE_INIT;
@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(kSuper, 3) composite_bwd_kernel(const BwdParam
         const int i_nxt = n - 1 - (base + kSuper + tid);
         if (i_nxt >= 0) {
             ent_nxt = list[i_nxt];
-            a_nxt = ldg_f4(p.recA + ent_nxt.x); b_nxt = ldg_f4(p.recB + ent_nxt.x); c_nxt = ldg_f4(p.recC + ent_nxt.x);
+            a_nxt = ldg_f4(p.recA + (size_t)kGeomRecStride * ent_nxt.x); b_nxt = ldg_f4(p.recB + (size_t)kGeomRecStride * ent_nxt.x); c_nxt = ldg_f4(p.recC + (size_t)kGeomRecStride * ent_nxt.x);
         }
 
         // ---- S0: thread = entry.  (alpha, v) of every hit; the forward pass found the hits, the

@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
 #pragma unroll
                 for (int j = 0; j < kScanSub; j++) {
                     ra[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (raw_base + j * kSuper + tid < n) ra[j] = ldg_f4(p.recA + w_cur[j]);
+                    if (raw_base + j * kSuper + tid < n) ra[j] = ldg_f4(p.recA + (size_t)kGeomRecStride * w_cur[j]);
                 }
 #pragma unroll
                 for (int j = 0; j < kScanSub; j++) {
@@ -211,8 +211,10 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
                             make_uint2(gid, (uint32_t)(raw_base + j * kSuper + tid));
                         // the candidate's records will be gathered by another thread one or two
                         // working sets from now: start them on their way to L2
-                        prefetch_l2(p.recA + gid); prefetch_l2(p.recB + gid); prefetch_l2(p.recC + gid);
-                        prefetch_l2(p.recD + gid); prefetch_l2(p.recE + gid);
+                        // ({A, B}, {C, pad} and {D, E} are one 32-byte sector each)
+                        prefetch_l2(p.recA + (size_t)kGeomRecStride * gid);
+                        prefetch_l2(p.recC + (size_t)kGeomRecStride * gid);
+                        prefetch_l2(p.recD + (size_t)kScratchRecStride * gid);
                     }
                     run += sm.scan_cnt[scan_par][j * kWarps + w];
                 }
@@ -238,8 +240,8 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
             } else {
                 const uint2 ent = sm.ring[(head + tid) & (kRing - 1)];
                 id = ent.x; ord = ent.y;
-                a_cur = ldg_f4(p.recA + id);
-                b_cur = ldg_f4(p.recB + id);
+                a_cur = ldg_f4(p.recA + (size_t)kGeomRecStride * id);
+                b_cur = ldg_f4(p.recB + (size_t)kGeomRecStride * id);
             }
         }
         pre_pos = 0xffffffffu;
@@ -247,8 +249,8 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
             pre_pos = head + kSuper + tid;
             const uint2 ent = sm.ring[pre_pos & (kRing - 1)];
             pre_id = ent.x; pre_ord = ent.y;
-            pre_a = ldg_f4(p.recA + pre_id);
-            pre_b = ldg_f4(p.recB + pre_id);
+            pre_a = ldg_f4(p.recA + (size_t)kGeomRecStride * pre_id);
+            pre_b = ldg_f4(p.recB + (size_t)kGeomRecStride * pre_id);
         }
 
         // ---- S0: thread = candidate.  Hit mask over the unit's pixels, alpha of every hit.
@@ -256,7 +258,7 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
         // (nearly every candidate has a hit).
         uint32_t h = 0;
         if (tid < m) {
-            const float4 c_rec = ldg_f4(p.recC + id), d_rec = ldg_f4(p.recD + id), e_rec = ldg_f4(p.recE + id);
+            const float4 c_rec = ldg_f4(p.recC + (size_t)kGeomRecStride * id), d_rec = ldg_f4(p.recD + (size_t)kScratchRecStride * id), e_rec = ldg_f4(p.recE + (size_t)kScratchRecStride * id);
             h = entry_hits_fwd(a_cur, b_cur, bx0, by0, bx1, by1, sm.M, tid, kRow);
             if (h != 0u) {
                 sm.A[tid] = a_cur;

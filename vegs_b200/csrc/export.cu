@@ -22,7 +22,10 @@ __global__ void export_gaussians_kernel(int P, const int* __restrict__ radii,
     const bool vis = radii[i] > 0;
     float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a, c = a;
     uint2 r = make_uint2(0u, 0u);
-    if (vis) { a = recA[i]; b = recB[i]; c = recC[i]; r = rect[i]; }
+    if (vis) {
+        const size_t gi = (size_t)kGeomRecStride * i;
+        a = recA[gi]; b = recB[gi]; c = recC[gi]; r = rect[i];
+    }
     if (tiles_touched)
         tiles_touched[i] = ((r.x >> 16) - (r.x & 0xffffu)) * ((r.y >> 16) - (r.y & 0xffffu));
     if (depths) depths[i] = a.w;
@@ -42,7 +45,7 @@ __global__ void export_keys_kernel(const uint2* __restrict__ ranges,
     const uint2 rg = ranges[tile];
     for (uint32_t i = rg.x + threadIdx.x; i < rg.y; i += blockDim.x) {
         const uint32_t g = point_list[i] & id_mask;   // strip the unit mask byte (common.cuh)
-        if (keys) keys[i] = ((uint64_t)tile << 32) | (uint64_t)__float_as_uint(recA[g].w);
+        if (keys) keys[i] = ((uint64_t)tile << 32) | (uint64_t)__float_as_uint(recA[(size_t)kGeomRecStride * g].w);
         if (list_out) list_out[i] = g;
     }
 }

@@ -283,7 +283,7 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_fwd_kernel(const PrePa
             }
         }
         const __half2 eh = __floats2half2_rn(ex, ey);   // 1.002 above covers the 2^-11 rounding
-        p.recA[idx] = make_float4(pix_x, pix_y, __uint_as_float(*reinterpret_cast<const uint32_t*>(&eh)), depth);
+        p.recA[(size_t)kGeomRecStride * idx] = make_float4(pix_x, pix_y, __uint_as_float(*reinterpret_cast<const uint32_t*>(&eh)), depth);
         {
             // The same box in whole pixels, clipped to the image, for the emission kernel's unit
             // masks: float operations of unit_box() (composite_common.cuh) with the image as the block.
@@ -295,10 +295,11 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_fwd_kernel(const PrePa
             p.pbox[idx] = make_uint2((uint32_t)min(bx0, p.W) | ((uint32_t)(max(bx1, -1) + 1) << 16),
                                      (uint32_t)min(by0, p.H) | ((uint32_t)(max(by1, -1) + 1) << 16));
         }
-        p.recB[idx] = make_float4(conic.x, conic.y, conic.z, opacity);
-        p.recC[idx] = make_float4(rgb.x, rgb.y, rgb.z, __fdiv_rn(1.0f, sinf(theta)));
-        p.recD[idx] = d4;
-        p.recE[idx] = e4;
+        p.recB[(size_t)kGeomRecStride * idx] = make_float4(conic.x, conic.y, conic.z, opacity);
+        p.recC[(size_t)kGeomRecStride * idx] = make_float4(rgb.x, rgb.y, rgb.z, __fdiv_rn(1.0f, sinf(theta)));
+        p.recC[(size_t)kGeomRecStride * idx + 1] = make_float4(0.f, 0.f, 0.f, 0.f);   // pad: whole sectors are written
+        p.recD[(size_t)kScratchRecStride * idx] = d4;
+        p.recE[(size_t)kScratchRecStride * idx] = e4;
         p.clamped[idx] = (uint8_t)clampbits;
     }
 }
