@@ -24,7 +24,7 @@ namespace {
 
 constexpr int kEmitThreads = 256;
 constexpr uint32_t kEmitPart = 8192;   // instances emitted by one CTA
-constexpr int kEmitPerThread = kEmitChunk / kEmitThreads;  // 8
+constexpr int kEmitPerThread = kEmitChunk / kEmitThreads;  // 4
 
 __device__ __forceinline__ uint32_t rect_tiles(uint2 r) {
     const uint32_t w = (r.x >> 16) - (r.x & 0xffffu);
@@ -53,7 +53,7 @@ tile_count_kernel(int P, const uint32_t* __restrict__ order, const uint2* __rest
 #pragma unroll
     for (int j = 0; j < kEmitPerThread; j++) {
         const uint32_t s = base + j * kEmitThreads + threadIdx.x;
-        if (s < (uint32_t)P) sum += rect_tiles(rect[order[s]]);
+        if (s < (uint32_t)P) sum += rect_tiles(rect[(size_t)kRectStride * order[s]]);
     }
     const uint32_t tot = block_reduce_sum(sum, s_warp);
     if (threadIdx.x == 0) chunksum[blockIdx.x] = tot;
@@ -145,7 +145,7 @@ emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__
             uint32_t nchunks, int grid_x, uint32_t* __restrict__ tkeys,
             uint32_t* __restrict__ tvals, uint32_t R, const uint2* __restrict__ pbox, int W, int H) {
     __shared__ uint32_t s_g[kEmitChunk];
-    __shared__ uint2 s_rect[kEmitChunk];
+    __shared__ uint4 s_rect[kEmitChunk];   // tile rect (x, y) and pixel box (z, w) of the chunk's Gaussians
     __shared__ uint32_t s_off[kEmitChunk + 1];
     __shared__ uint32_t s_warp[kEmitThreads / 32];
 
@@ -164,7 +164,7 @@ emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__
     const uint32_t i_end = min(n_inst, i_begin + kEmitPart);
     if (i_begin >= n_inst) return;
 
-    // Thread t owns sorted positions base + 8t .. base + 8t + 7 (position order = depth order).
+    // Thread t owns kEmitPerThread consecutive sorted positions (position order = depth order).
     uint32_t cnt[kEmitPerThread];
     uint32_t tsum = 0;
 #pragma unroll
@@ -172,14 +172,14 @@ emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__
         const uint32_t l = threadIdx.x * kEmitPerThread + j;
         const uint32_t s = base + l;
         uint32_t g = 0;
-        uint2 r = make_uint2(0u, 0u);
+        uint4 r = make_uint4(0u, 0u, 0u, 0u);
         if (s < (uint32_t)P) {
             g = order[s];
-            r = rect[g];
+            r = reinterpret_cast<const uint4*>(rect)[g];
         }
         s_g[l] = g;
         s_rect[l] = r;
-        cnt[j] = rect_tiles(r);
+        cnt[j] = rect_tiles(make_uint2(r.x, r.y));
         tsum += cnt[j];
     }
     // exclusive scan of the per-thread sums over the block
@@ -212,7 +212,7 @@ emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__
             const uint32_t mid = (lo + hi) >> 1;
             if (s_off[mid] <= i) lo = mid; else hi = mid;
         }
-        const uint2 r = s_rect[lo];
+        const uint4 r = s_rect[lo];
         const uint32_t k = i - s_off[lo];
         const uint32_t x0 = r.x & 0xffffu, w = (r.x >> 16) - x0, y0 = r.y & 0xffffu;
         const uint32_t ty = y0 + k / w;
@@ -226,7 +226,7 @@ emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__
                 // box (preprocess.cu) against 2 unit columns and 4 unit rows - the same outcome as
                 // unit_box() (composite_common.cuh); carried in the top byte of the list word (ids
                 // are < 2^24 in this mode).
-                const uint2 pb = __ldg(pbox + val);
+                const uint2 pb = make_uint2(r.z, r.w);
                 const int gx0 = (int)(pb.x & 0xffffu), gx1 = (int)(pb.x >> 16) - 1;
                 const int gy0 = (int)(pb.y & 0xffffu), gy1 = (int)(pb.y >> 16) - 1;
                 uint32_t okx = 0, oky = 0;

@@ -48,12 +48,13 @@ constexpr int kUnitsPerTile = 8;  // compositing units (8x4 pixel blocks) per 16
 // recX + stride * g with these strides (in float4 units).
 constexpr int kGeomRecStride = 4;
 constexpr int kScratchRecStride = 2;
+constexpr int kRectStride = 2;    // {tile rect, pixel box} per Gaussian, in uint2 units
 // Instance list words: Gaussian id, plus - when every id fits 24 bits - in the top byte the mask of
 // the tile's compositing units the Gaussian's conservative box reaches (written by the emission
 // kernel), so a unit rejects an entry from the list word alone.
 constexpr uint32_t kListIdMask = 0x00ffffffu;
 bool list_has_unit_masks(int P);   // abi.cu: P < 2^24 unless disabled through vegs_debug_unit_masks
-constexpr int kEmitChunk = 2048;  // depth-sorted Gaussians per emission block
+constexpr int kEmitChunk = 1024;  // depth-sorted Gaussians per emission block
 
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 static inline uint32_t div_up(uint64_t a, uint64_t b) { return (uint32_t)((a + b - 1) / b); }
@@ -136,8 +137,8 @@ static inline ScratchView scratch_view(void* base, int P) {
     size_t n = (size_t)(P > 0 ? P : 1);
     v.recD = carve<float4>(cur, (size_t)kScratchRecStride * n);   // interleaved {D, E}
     v.recE = v.recD + 1;
-    v.rect = carve<uint2>(cur, n);
-    v.pbox = carve<uint2>(cur, n);
+    v.rect = carve<uint2>(cur, (size_t)kRectStride * n);   // interleaved {rect, pbox}: one 16-byte record
+    v.pbox = v.rect + 1;
     v.keys0 = carve<uint32_t>(cur, n);
     v.keys1 = carve<uint32_t>(cur, n);
     v.vals0 = carve<uint32_t>(cur, n);

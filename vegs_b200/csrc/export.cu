@@ -24,7 +24,7 @@ __global__ void export_gaussians_kernel(int P, const int* __restrict__ radii,
     uint2 r = make_uint2(0u, 0u);
     if (vis) {
         const size_t gi = (size_t)kGeomRecStride * i;
-        a = recA[gi]; b = recB[gi]; c = recC[gi]; r = rect[i];
+        a = recA[gi]; b = recB[gi]; c = recC[gi]; r = rect[(size_t)kRectStride * i];
     }
     if (tiles_touched)
         tiles_touched[i] = ((r.x >> 16) - (r.x & 0xffffu)) * ((r.y >> 16) - (r.y & 0xffffu));

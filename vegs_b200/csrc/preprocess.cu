@@ -190,7 +190,7 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_fwd_kernel(const PrePa
     if (in_range) {
         p.radii[idx] = visible ? radius : 0;
         p.keys[idx] = visible ? __float_as_uint(depth) : 0xFFFFFFFFu;
-        p.rect[idx] = visible ? make_uint2((uint32_t)x0 | ((uint32_t)x1 << 16),
+        p.rect[(size_t)kRectStride * idx] = visible ? make_uint2((uint32_t)x0 | ((uint32_t)x1 << 16),
                                            (uint32_t)y0 | ((uint32_t)y1 << 16))
                               : make_uint2(0u, 0u);
     }
@@ -292,7 +292,7 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_fwd_kernel(const PrePa
             const int bx1 = (int)floorf(fminf(pix_x + e.x, (float)(p.W - 1)));
             const int by0 = (int)ceilf(fmaxf(pix_y - e.y, 0.0f));
             const int by1 = (int)floorf(fminf(pix_y + e.y, (float)(p.H - 1)));
-            p.pbox[idx] = make_uint2((uint32_t)min(bx0, p.W) | ((uint32_t)(max(bx1, -1) + 1) << 16),
+            p.pbox[(size_t)kRectStride * idx] = make_uint2((uint32_t)min(bx0, p.W) | ((uint32_t)(max(bx1, -1) + 1) << 16),
                                      (uint32_t)min(by0, p.H) | ((uint32_t)(max(by1, -1) + 1) << 16));
         }
         p.recB[(size_t)kGeomRecStride * idx] = make_float4(conic.x, conic.y, conic.z, opacity);
