@@ -129,6 +129,17 @@ class Workload:
             scale_modifier=1.0, viewmatrix=cam.viewmatrix, projmatrix=cam.projmatrix, sh_degree=3,
             campos=cam.campos, prefiltered=False, debug=False)
 
+    def _stage_target(self, v):
+        """Host -> device copy of view v's target planes on the copy stream; (tensor, ready event)."""
+        if not hasattr(self, "copy_stream"):
+            self.copy_stream = torch.cuda.Stream(self.device)
+        with torch.cuda.stream(self.copy_stream):
+            t = self.host_targets[v].to(self.device, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self.copy_stream)
+        t.record_stream(torch.cuda.current_stream(self.device))
+        return t, ev
+
     def step(self, mod, resident: bool, reduce: bool = True):
         """One optimisation step's rasterizer work: local views fwd+bwd, stats, all-reduce."""
         p = self.params
@@ -136,8 +147,18 @@ class Workload:
             t.grad = None
         stats = self.vdist.DensificationStats(self.P, self.device)
         total = torch.zeros((), device=self.device)
-        for v in self.my_views:
-            tgt = self.dev_targets[v] if resident else self.host_targets[v].to(self.device, non_blocking=True)
+        # e2e leg: each view's target planes come from pinned host memory inside the step; the copy of
+        # view i+1 runs on a side stream while view i is rendered (what a data loader would do)
+        pending = None
+        if not resident and self.my_views:
+            pending = self._stage_target(self.my_views[0])
+        for i, v in enumerate(self.my_views):
+            if resident:
+                tgt = self.dev_targets[v]
+            else:
+                tgt, ev = pending
+                torch.cuda.current_stream(self.device).wait_event(ev)
+                pending = self._stage_target(self.my_views[i + 1]) if i + 1 < len(self.my_views) else None
             means2D = torch.zeros_like(p["means3D"], requires_grad=True)
             rast = mod.GaussianRasterizer(self.settings(mod, self.cams[v]))
             color, depth, quat, scale, alpha, radii = rast(
