@@ -146,6 +146,8 @@ class Workload:
         for t in p.values():
             t.grad = None
         stats = self.vdist.DensificationStats(self.P, self.device)
+        if FUSED_ACCUM:
+            stats.attach(mod)     # vegs_b200: statistics updated inside the backward kernel
         total = torch.zeros((), device=self.device)
         # e2e leg: each view's target planes come from pinned host memory inside the step; the copy of
         # view i+1 runs on a side stream while view i is rendered (what a data loader would do)
@@ -169,6 +171,7 @@ class Workload:
             loss.backward()
             stats.add_view(means2D.grad, radii)
             total = total + loss.detach()
+        stats.detach(mod)
         if self.world > 1 and reduce:
             self.flat = self.vdist.allreduce_step(p, stats, flat=self.flat)
         if not resident:
@@ -333,7 +336,8 @@ def main():
                             P=args.P, views_per_step=args.views, image=[wl.W, wl.H], parallelism=f"view-parallel x{world}",
                             l2="inputs (1.4 GB of parameters per view) exceed the 126 MB L2; no explicit flush",
                             impl=kind,
-                            grad_accumulation=("fused into the backward kernel (set_fused_grad_accumulation)"
+                            grad_accumulation=("gradient accumulation and densification statistics fused into the backward kernel "
+                                               "(set_fused_grad_accumulation, set_densification_accumulators)"
                                                if args.impl == "ours" and FUSED_ACCUM else "autograd add per view")),
                 e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=wl.h2d_bytes * len(wl.my_views) // args.views * world,
                          d2h_bytes_per_step=4 * world),

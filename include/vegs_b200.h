@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define VEGS_ABI_VERSION 2
+#define VEGS_ABI_VERSION 3
 
 enum {
     VEGS_OK = 0,
@@ -135,6 +135,15 @@ typedef struct VegsBackwardArgs {
      * radii == 0 are left untouched); for bits not set the output is overwritten as above.
      * dL_dmeans2D is always overwritten. */
     uint32_t accumulate_mask;
+    /* Fused densification statistics (no reference counterpart; the reference's caller computes
+     * them from the returned means2D gradient and radii, scene/gaussian_model.py:411-413 and
+     * train.py:300-301).  When stat_grad_accum is not NULL, for every Gaussian with radii > 0:
+     *   stat_grad_accum[i] += || dL_dmeans2D[i].xy ||,  stat_denom[i] += 1,
+     *   stat_max_radii[i]   = max(stat_max_radii[i], radii[i])
+     * All three [P] float, all three or none. */
+    float* stat_grad_accum;
+    float* stat_denom;
+    float* stat_max_radii;
 } VegsBackwardArgs;
 
 #define VEGS_ACC_MEANS3D   1u

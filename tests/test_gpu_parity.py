@@ -131,6 +131,42 @@ def test_fused_grad_accumulation_equals_autograd_accumulation():
         util.grad_close(fused[k], plain[k], f"accumulated grad {k}", rtol=1e-5)
 
 
+def test_fused_densification_statistics_equal_the_separate_passes():
+    """set_densification_accumulators: the backward kernel's own update of xyz_gradient_accum / denom /
+    max_radii2D over three views equals DensificationStats.add_view on the returned tensors."""
+    import torch
+    import vegs_b200.diff_gaussian_rasterization as dgr
+    from vegs_b200 import dist as vdist
+    dev = torch.device("cuda")
+    scene = util.scene_with_specials(30000)
+    P = scene["means3D"].shape[0]
+    t = {k: v.to(dev) for k, v in scene.items() if k in ("means3D", "opacities", "shs", "scales", "rotations")}
+    fused, plain = vdist.DensificationStats(P, dev), vdist.DensificationStats(P, dev)
+    assert fused.attach(dgr)
+    try:
+        for i in range(3):
+            cam = synth.make_camera(i, scale=0.25)
+            rs = dgr.GaussianRasterizationSettings(
+                image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+                bg=torch.zeros(3, device=dev), scale_modifier=1.0, viewmatrix=cam.viewmatrix.to(dev),
+                projmatrix=cam.projmatrix.to(dev), sh_degree=3, campos=cam.campos.to(dev),
+                prefiltered=False, debug=False)
+            means2D = torch.zeros_like(t["means3D"], requires_grad=True)
+            color, depth, quat, scale, alpha, radii = dgr.GaussianRasterizer(rs)(
+                means3D=t["means3D"], means2D=means2D, opacities=t["opacities"], shs=t["shs"],
+                scales=t["scales"], rotations=t["rotations"])
+            (color.sum() + depth.mean()).backward()
+            plain.add_view(means2D.grad, radii)
+            fused.add_view(means2D.grad, radii)          # no-op while attached
+    finally:
+        fused.detach(dgr)
+    assert float(plain.denom.sum()) > 0
+    util.assert_bit_equal(fused.denom.cpu().numpy(), plain.denom.cpu().numpy(), "denom")
+    util.assert_bit_equal(fused.max_radii2D.cpu().numpy(), plain.max_radii2D.cpu().numpy(), "max_radii2D")
+    util.grad_close(fused.xyz_gradient_accum.cpu().numpy(), plain.xyz_gradient_accum.cpu().numpy(),
+                    "xyz_gradient_accum", rtol=1e-6)
+
+
 def test_modes_colors_precomp_and_cov3d_precomp_against_oracle():
     scene = util.scene_with_specials(4000)
     cam = synth.make_camera(0, scale=0.125)

@@ -51,6 +51,7 @@ class VegsBackwardArgs(C.Structure):
         ("dL_dcolors", C.c_void_p), ("dL_dopacity", C.c_void_p), ("dL_dscales", C.c_void_p),
         ("dL_drotations", C.c_void_p), ("dL_dcov3D", C.c_void_p),
         ("accumulate_mask", C.c_uint32),
+        ("stat_grad_accum", C.c_void_p), ("stat_denom", C.c_void_p), ("stat_max_radii", C.c_void_p),
     ]
 
 
@@ -98,7 +99,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if a declared symbol is not exported
         fn.restype = res
         fn.argtypes = args
-    if lib.vegs_abi_version() != 2:
+    if lib.vegs_abi_version() != 3:
         raise ImportError("libvegs_b200.so ABI version mismatch; rebuild it")
     _lib = lib
     return lib

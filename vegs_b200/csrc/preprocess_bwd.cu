@@ -55,6 +55,7 @@ struct PbParams {
     float* dL_dcov3D;
     bool shs_vec_ok, dsh_vec_ok, rots_vec_ok;
     uint32_t accum;      // VEGS_ACC_* bits: those outputs receive old + gradient
+    float *stat_grad, *stat_denom, *stat_maxr;   // fused densification statistics, or NULL
 };
 
 __device__ __forceinline__ float4 ldg_stream4(const float4* p) {
@@ -459,6 +460,13 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
         put(p.dL_dscales ? p.dL_dscales + i3 : nullptr, 3, dscale, VEGS_ACC_SCALES);
         put(p.dL_drots ? p.dL_drots + 4 * (size_t)idx : nullptr, 4, drot, VEGS_ACC_ROTATIONS);
         put(p.dL_dcov3D ? p.dL_dcov3D + 6 * (size_t)idx : nullptr, 6, dcov, VEGS_ACC_COV3D);
+        // densification statistics of the reference's training loop (scene/gaussian_model.py:411-413,
+        // train.py:300-301), for the Gaussians this view rendered
+        if (p.stat_grad != nullptr && visible) {
+            p.stat_grad[idx] += sqrtf(dm2d[0] * dm2d[0] + dm2d[1] * dm2d[1]);
+            p.stat_denom[idx] += 1.0f;
+            p.stat_maxr[idx] = fmaxf(p.stat_maxr[idx], (float)in_radius);
+        }
     }
 }
 
@@ -482,6 +490,11 @@ int launch_preprocess_bwd(const VegsBackwardArgs& a, const GeomView& g, const fl
     p.dsh_vec_ok = a.dL_dsh != nullptr && (reinterpret_cast<uintptr_t>(a.dL_dsh) & 15u) == 0;
     p.rots_vec_ok = a.rotations != nullptr && (reinterpret_cast<uintptr_t>(a.rotations) & 15u) == 0;
     p.accum = a.accumulate_mask;
+    p.stat_grad = a.stat_grad_accum; p.stat_denom = a.stat_denom; p.stat_maxr = a.stat_max_radii;
+    if ((p.stat_grad != nullptr) != (p.stat_denom != nullptr) || (p.stat_grad != nullptr) != (p.stat_maxr != nullptr)) {
+        set_error("vegs_backward: stat_grad_accum, stat_denom and stat_max_radii go together");
+        return VEGS_EINVAL;
+    }
     if ((p.accum & VEGS_ACC_SH) && a.M > kMaxStageCoeffs) {
         set_error("vegs_backward: VEGS_ACC_SH needs M <= %d", kMaxStageCoeffs);
         return VEGS_EINVAL;

@@ -212,6 +212,29 @@ def set_fused_grad_accumulation(enabled: bool) -> None:
     _fused_grad_accumulation = bool(enabled)
 
 
+_densification_accumulators = None
+
+
+def set_densification_accumulators(xyz_gradient_accum=None, denom=None, max_radii2D=None) -> None:
+    """Opt-in extension (no reference counterpart).  Registers the three per-Gaussian statistics
+    buffers of VEGS's densification (`scene/gaussian_model.py:154-172`: `xyz_gradient_accum` [P,1],
+    `denom` [P,1], `max_radii2D` [P]; float32, CUDA, contiguous).  Every following backward pass then
+    updates them itself for the Gaussians its view rendered (radii > 0):
+    `xyz_gradient_accum += ||means2D.grad[:, :2]||`, `denom += 1`, `max_radii2D = max(., radii)` - what
+    `train.py:300-301` + `add_densification_stats` do in separate passes over all Gaussians.
+    Call with no arguments to stop."""
+    global _densification_accumulators
+    if xyz_gradient_accum is None:
+        _densification_accumulators = None
+        return
+    for t in (xyz_gradient_accum, denom, max_radii2D):
+        if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+            raise ValueError("densification accumulators must be contiguous float32 CUDA tensors")
+    if not (xyz_gradient_accum.numel() == denom.numel() == max_radii2D.numel()):
+        raise ValueError("densification accumulators must have one element per Gaussian")
+    _densification_accumulators = (xyz_gradient_accum, denom, max_radii2D)
+
+
 def _accum_target(t, shape):
     """`.grad` of leaf `t` if the backward kernel may add into it, else None."""
     if not _fused_grad_accumulation or t is None or not isinstance(t, torch.Tensor):
@@ -312,6 +335,11 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
         b.dL_dscales, b.dL_drotations = _ptr(dscales), _ptr(drots)
         b.dL_dcov3D = _ptr(dcov)
         b.accumulate_mask = acc_mask
+        if _densification_accumulators is not None:
+            sg, sd, sr = _densification_accumulators
+            if sg.numel() != P or sg.device != device:
+                raise RuntimeError("densification accumulators do not match this call (P or device)")
+            b.stat_grad_accum, b.stat_denom, b.stat_max_radii = sg.data_ptr(), sd.data_ptr(), sr.data_ptr()
         _lib.check(lib.vegs_backward(C.byref(b), C.c_void_p(stream.cuda_stream)), "vegs_backward")
     # inputs whose .grad already received the result get no gradient from autograd
     nf = lambda name, t: None if name in fused else t

@@ -35,8 +35,25 @@ class DensificationStats:
         self.denom = torch.zeros((P, 1), device=device)
         self.max_radii2D = torch.zeros((P,), device=device)
 
+    def attach(self, rasterizer_module) -> bool:
+        """Let the backward kernel of `rasterizer_module` update these buffers itself
+        (vegs_b200's set_densification_accumulators); False if the module cannot (the reference)."""
+        reg = getattr(rasterizer_module, "set_densification_accumulators", None)
+        self.fused = reg is not None
+        if self.fused:
+            reg(self.xyz_gradient_accum, self.denom, self.max_radii2D)
+        return self.fused
+
+    def detach(self, rasterizer_module) -> None:
+        if getattr(self, "fused", False):
+            rasterizer_module.set_densification_accumulators()
+            self.fused = False
+
     def add_view(self, viewspace_grad: torch.Tensor, radii: torch.Tensor) -> None:
-        """train.py:300-301 + add_densification_stats for one rendered view."""
+        """train.py:300-301 + add_densification_stats for one rendered view (no-op when the
+        backward kernel already did it, see attach)."""
+        if getattr(self, "fused", False):
+            return
         vis = radii > 0
         self.max_radii2D = torch.where(vis, torch.maximum(self.max_radii2D, radii.to(self.max_radii2D.dtype)),
                                        self.max_radii2D)
