@@ -327,6 +327,17 @@ def main():
     ms_e2e = timed(lambda: wl.step(mod, False), args.steps, 1, device, world)
     e2e_value = args.views / (ms_e2e / args.steps / 1000.0)
 
+    # for transparency: the same step with the two opt-in fusions off (autograd adds each view's
+    # gradient, the caller computes the densification statistics), i.e. the plain drop-in module
+    unfused_value = None
+    if args.impl == "ours" and FUSED_ACCUM:
+        FUSED_ACCUM = False
+        mod.set_fused_grad_accumulation(False)
+        ms_u = timed(lambda: wl.step(mod, True), 2, 1, device, world)
+        unfused_value = args.views / (ms_u / 2 / 1000.0)
+        FUSED_ACCUM = True
+        mod.set_fused_grad_accumulation(True)
+
     line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
                 ms_per_step=ms_step, higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32",
                 data="synthetic",
@@ -342,6 +353,8 @@ def main():
                 e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=wl.h2d_bytes * len(wl.my_views) // args.views * world,
                          d2h_bytes_per_step=4 * world),
                 gpu_launches=int(launches) if args.impl == "ours" else 0, clocks=clocks)
+    if unfused_value is not None:
+        line["value_without_fusions"] = unfused_value
     if args.impl == "reference":
         line["impl"] = "reference"
         line["cpu_baseline"] = dict(value=value, unit=UNIT, cores=0, kind="reference",

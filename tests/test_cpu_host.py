@@ -183,3 +183,12 @@ def test_scene_generator_is_seeded_and_shaped():
     assert torch.allclose(a["rotations"].norm(dim=1), torch.ones(5000), atol=1e-5)
     assert (a["rotations"][:, 0] >= 0).all() and (a["opacities"] > 0).all() and (a["opacities"] < 1).all()
     assert a["scales"][:, 0].max() < 1e-4 and a["scales"][:, 1:].min() > 0.01
+
+
+def test_entry_scripts_compile():
+    """bench.py / __graft_entry__.py / the scripts are only run on the GPU box: catch syntax errors here."""
+    import py_compile
+    paths = [os.path.join(ROOT, "bench.py"), os.path.join(ROOT, "__graft_entry__.py")]
+    paths += [os.path.join(ROOT, "scripts", f) for f in os.listdir(os.path.join(ROOT, "scripts")) if f.endswith(".py")]
+    for path in paths:
+        py_compile.compile(path, doraise=True)
