@@ -108,3 +108,50 @@ def test_two_rank_step_equals_single_rank(tmp_path):
     assert torch.allclose(got["accum"], stats.xyz_gradient_accum, rtol=1e-6, atol=1e-6)
     assert torch.equal(got["denom"], stats.denom)
     assert torch.equal(got["maxr"], stats.max_radii2D)
+
+
+def test_densification_stats_attach_falls_back_for_modules_without_the_extension():
+    """attach() registers the buffers with a module that offers set_densification_accumulators and
+    leaves add_view as the path for one that does not (the reference's module)."""
+    P = 16
+
+    class WithExtension:
+        registered = None
+
+        @staticmethod
+        def set_densification_accumulators(a=None, b=None, c=None):
+            WithExtension.registered = None if a is None else (a, b, c)
+
+    class Reference:
+        pass
+
+    radii = torch.tensor([0, 3] * (P // 2), dtype=torch.int32)
+    grad = torch.ones(P, 3)
+
+    s = vdist.DensificationStats(P, "cpu")
+    assert s.attach(Reference) is False
+    s.add_view(grad, radii)
+    assert float(s.denom.sum()) == P // 2 and float(s.max_radii2D.max()) == 3.0
+    assert torch.allclose(s.xyz_gradient_accum[radii > 0], torch.full((P // 2, 1), 2.0 ** 0.5))
+
+    f = vdist.DensificationStats(P, "cpu")
+    assert f.attach(WithExtension) is True
+    assert WithExtension.registered[0] is f.xyz_gradient_accum and WithExtension.registered[2] is f.max_radii2D
+    f.add_view(grad, radii)                      # the kernel would have done it: no-op
+    assert float(f.denom.sum()) == 0.0
+    f.detach(WithExtension)
+    assert WithExtension.registered is None
+    f.add_view(grad, radii)
+    assert float(f.denom.sum()) == P // 2
+
+
+def test_extension_setters_validate_their_arguments():
+    import pytest
+    import vegs_b200.diff_gaussian_rasterization as dgr
+    cpu = torch.zeros(4, 1)
+    with pytest.raises(ValueError):
+        dgr.set_densification_accumulators(cpu, cpu, torch.zeros(4))     # not CUDA tensors
+    dgr.set_densification_accumulators()                                  # clearing always works
+    dgr.set_fused_grad_accumulation(True)
+    assert dgr._accum_target(torch.zeros(3, requires_grad=True), (3,)) is None   # leaf without .grad yet
+    dgr.set_fused_grad_accumulation(False)
