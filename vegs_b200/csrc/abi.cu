@@ -59,8 +59,8 @@ static int validate_common(int P, int D, int M, int W, int H) {
         set_error("M=%d SH coefficients cannot hold degree %d", M, D);
         return VEGS_EINVAL;
     }
-    if ((W + kTile - 1) / kTile > 65535 || (H + kTile - 1) / kTile > 65535) {
-        set_error("image too large for 16-bit tile coordinates");
+    if (W > 65535 || H > 65535) {
+        set_error("image too large: tile rectangles and pixel boxes are packed in 16-bit coordinates (W, H <= 65535)");
         return VEGS_EINVAL;
     }
     return VEGS_OK;
