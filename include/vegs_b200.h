@@ -47,7 +47,7 @@ typedef struct VegsForwardArgs {
     int32_t P;            /* number of Gaussians */
     int32_t D;            /* active SH degree (0..3) */
     int32_t M;            /* SH coefficients stored per Gaussian (sh.size(1)); 0 if shs == NULL */
-    int32_t W, H;         /* image size in pixels */
+    int32_t W, H;         /* image size in pixels, each <= 65535 */
     /* inputs */
     const float* background;     /* [3] */
     const float* means3D;        /* [P,3] */
