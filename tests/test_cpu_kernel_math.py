@@ -212,3 +212,59 @@ def test_box_extents_contain_every_contributing_pixel():
         checked += int(hit.sum())
     assert checked > 50000
     assert missed == 0
+
+
+def test_unit_masks_from_pixel_boxes_equal_the_per_entry_box_test():
+    """binning.cu derives, per tile instance, the mask of compositing units the Gaussian reaches from
+    the integer pixel box the preprocess stage stores; the scan of P >= 2^24 scenes instead clips
+    the float box per entry (unit_box).  Both must keep exactly the same entries, including for
+    off-screen, huge, infinite and NaN boxes."""
+    rng = np.random.default_rng(3)
+    f = np.float32
+    W, H = 1408, 376
+    n = 200000
+    x = rng.uniform(-300, W + 300, n).astype(f)
+    y = rng.uniform(-300, H + 300, n).astype(f)
+    ex = (10 ** rng.uniform(-2, 3, n)).astype(np.float16).astype(f)
+    ey = (10 ** rng.uniform(-2, 3, n)).astype(np.float16).astype(f)
+    special = rng.integers(0, 40, n)
+    ex[special == 0] = np.inf; ey[special == 1] = np.inf
+    ex[special == 2] = -1.0; ey[special == 2] = -1.0
+    x[special == 3] = np.nan; y[special == 4] = np.nan
+    x[special == 5] = 3e9; y[special == 6] = -3e9
+
+    def to_int(v):                       # cvt.rzi.s32.f32 semantics: saturate, NaN -> 0
+        v = np.where(np.isnan(v), 0.0, v.astype(np.float64))
+        return np.clip(np.trunc(v), -2 ** 31, 2 ** 31 - 1).astype(np.int64)
+
+    def fmax(a, b):                      # fmaxf / fminf return the non-NaN operand
+        return np.where(np.isnan(a), b, np.where(np.isnan(b), a, np.maximum(a, b)))
+
+    def fmin(a, b):
+        return np.where(np.isnan(a), b, np.where(np.isnan(b), a, np.minimum(a, b)))
+
+    with np.errstate(invalid="ignore", over="ignore"):
+        lo_x, hi_x, lo_y, hi_y = (x - ex).astype(f), (x + ex).astype(f), (y - ey).astype(f), (y + ey).astype(f)
+        # preprocess.cu: the box clipped to the image, in whole pixels
+        gx0 = np.minimum(to_int(np.ceil(fmax(lo_x, f(0)))), W)
+        gx1 = np.maximum(to_int(np.floor(fmin(hi_x, f(W - 1)))), -1)
+        gy0 = np.minimum(to_int(np.ceil(fmax(lo_y, f(0)))), H)
+        gy1 = np.maximum(to_int(np.floor(fmin(hi_y, f(H - 1)))), -1)
+        tiles = rng.integers(0, [(W + 15) // 16, (H + 15) // 16], (n, 2))
+        for blk in range(8):
+            bx0 = tiles[:, 0] * 16 + (blk & 1) * 8
+            by0 = tiles[:, 1] * 16 + (blk >> 1) * 4
+            bx1 = np.minimum(bx0 + 7, W - 1)
+            by1 = np.minimum(by0 + 3, H - 1)
+            on_image = (bx0 < W) & (by0 < H)
+            # composite_common.cuh unit_box
+            ux0 = to_int(np.ceil(fmax(lo_x, bx0.astype(f))))
+            ux1 = to_int(np.floor(fmin(hi_x, bx1.astype(f))))
+            uy0 = to_int(np.ceil(fmax(lo_y, by0.astype(f))))
+            uy1 = to_int(np.floor(fmin(hi_y, by1.astype(f))))
+            keep_box = on_image & (ux0 <= ux1) & (uy0 <= uy1)
+            # binning.cu mask bit
+            keep_mask = on_image & (np.maximum(gx0, bx0) <= np.minimum(gx1, bx1)) \
+                & (np.maximum(gy0, by0) <= np.minimum(gy1, by1))
+            assert np.array_equal(keep_box, keep_mask), f"unit {blk}: {int((keep_box != keep_mask).sum())} differ"
+    assert keep_box.sum() > 100
