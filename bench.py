@@ -6,7 +6,14 @@ synthetic drive split round-robin over the ranks (strong scaling: the batch is f
 forward and a backward through the drop-in GaussianRasterizer with a loss on colour + covariance
 maps, local gradient accumulation, per-view densification statistics, then one all-reduce
 (vegs_b200/dist.py).  `--impl reference` runs the same step with the reference's own CUDA
-extension from baseline/_ref (falls back to the CPU oracle port when that cannot be imported).
+extension from baseline/_ref (falls back to the CPU oracle port when that cannot be imported); that
+process never imports vegs_b200's rasterizer module nor maps libvegs_b200.so.
+
+Both arms time the SAME step: the plain drop-in module, autograd's per-view gradient add, the
+caller's densification-statistic passes (`value`, `e2e`).  The vegs_b200 arm additionally reports
+`value_fused` / `e2e_fused`: the same step with this package's two per-instance extensions
+(gradient accumulation and statistics inside the backward kernel, .grad tensors as views of the
+all-reduce buffer), which the reference's callers do not have.
 
 One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for how each field is obtained.
 """
@@ -85,14 +92,10 @@ class ClockSampler:
         return out
 
 
-FUSED_ACCUM = True      # views 2..n of a step add into .grad inside the backward kernel (--no-fused-accum)
-
-
 def load_rasterizer(impl: str):
     """(module, kind): the GaussianRasterizer implementation under test."""
     if impl == "ours":
         import vegs_b200.diff_gaussian_rasterization as m
-        m.set_fused_grad_accumulation(FUSED_ACCUM)
         return m, "vegs_b200"
     import util
     if util.reference_available():
@@ -121,6 +124,7 @@ class Workload:
         self.bg = torch.zeros(3, device=device)
         self.my_views = vdist.shard_views(args.views, rank, world)
         self.flat = None
+        self.buf = None
         self.h2d_bytes = sum(self.host_targets[v].numel() * 4 for v in range(args.views))
 
     def settings(self, mod, cam):
@@ -134,35 +138,49 @@ class Workload:
         if not hasattr(self, "copy_stream"):
             self.copy_stream = torch.cuda.Stream(self.device)
         with torch.cuda.stream(self.copy_stream):
-            t = self.host_targets[v].to(self.device, non_blocking=True)
+            t = self.host_targets[v % len(self.host_targets)].to(self.device, non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(self.copy_stream)
         t.record_stream(torch.cuda.current_stream(self.device))
         return t, ev
 
-    def step(self, mod, resident: bool, reduce: bool = True):
-        """One optimisation step's rasterizer work: local views fwd+bwd, stats, all-reduce."""
+    def step(self, mod, resident: bool, reduce: bool = True, fused: bool = False, views=None):
+        """One optimisation step's rasterizer work: local views fwd+bwd, stats, all-reduce.
+
+        fused=False  the plain drop-in module (either arm): autograd adds each view's gradient to
+                     .grad, the caller computes the densification statistics per view
+                     (train.py:300-301), the all-reduce buffer is packed from the .grad tensors.
+        fused=True   vegs_b200's per-instance extensions: .grad tensors and the step's statistics
+                     are views of one persistent flat buffer, the backward kernel assigns (first
+                     view) / adds (later views) into them and updates the statistics itself.
+        """
         p = self.params
-        for t in p.values():
-            t.grad = None
-        stats = self.vdist.DensificationStats(self.P, self.device)
-        if FUSED_ACCUM:
-            stats.attach(mod)     # vegs_b200: statistics updated inside the backward kernel
+        my_views = self.my_views if views is None else views
+        if fused:
+            if self.buf is None:
+                self.buf = self.vdist.FlatGradBuffer(p)
+            self.buf.begin_step()
+            stats = self.buf.step_stats
+        else:
+            for t in p.values():
+                t.grad = None
+            stats = self.vdist.DensificationStats(self.P, self.device)
         total = torch.zeros((), device=self.device)
         # e2e leg: each view's target planes come from pinned host memory inside the step; the copy of
         # view i+1 runs on a side stream while view i is rendered (what a data loader would do)
         pending = None
-        if not resident and self.my_views:
-            pending = self._stage_target(self.my_views[0])
-        for i, v in enumerate(self.my_views):
+        if not resident and my_views:
+            pending = self._stage_target(my_views[0])
+        for i, v in enumerate(my_views):
             if resident:
-                tgt = self.dev_targets[v]
+                tgt = self.dev_targets[v % len(self.dev_targets)]
             else:
                 tgt, ev = pending
                 torch.cuda.current_stream(self.device).wait_event(ev)
-                pending = self._stage_target(self.my_views[i + 1]) if i + 1 < len(self.my_views) else None
+                pending = self._stage_target(my_views[i + 1]) if i + 1 < len(my_views) else None
             means2D = torch.zeros_like(p["means3D"], requires_grad=True)
-            rast = mod.GaussianRasterizer(self.settings(mod, self.cams[v]))
+            ext = self.buf.rasterizer_kwargs(mod, first=(i == 0)) if fused else {}
+            rast = mod.GaussianRasterizer(self.settings(mod, self.cams[v % len(self.cams)]), **ext)
             color, depth, quat, scale, alpha, radii = rast(
                 means3D=p["means3D"], means2D=means2D, opacities=p["opacities"], shs=p["shs"],
                 scales=p["scales"], rotations=p["rotations"])
@@ -171,9 +189,11 @@ class Workload:
             loss.backward()
             stats.add_view(means2D.grad, radii)
             total = total + loss.detach()
-        stats.detach(mod)
         if self.world > 1 and reduce:
-            self.flat = self.vdist.allreduce_step(p, stats, flat=self.flat)
+            if fused:
+                self.buf.allreduce()
+            else:
+                self.flat = self.vdist.allreduce_step(p, stats, flat=self.flat)
         if not resident:
             return float(total.item())   # device -> host read of the step's result
         return total
@@ -262,6 +282,36 @@ def cpu_baseline_oracle(args, n_views_sample=1):
                        f"{int(1408 * args.scale)}x{int(376 * args.scale)}, oracle/vegs_oracle.c with OpenMP")
 
 
+def cpu_baseline_dense_torch(n_chunks=8, chunk=256):
+    """The second baseline BASELINE.json names: the dense PyTorch-CPU compositing evaluator
+    (oracle/dense_torch.py, every Gaussian x every pixel, autograd backward) at config 1 (100 k
+    Gaussians, 352x94), all host cores.  O(P * Npix): a bounded sample of n_chunks * chunk pixels
+    spread over the image is timed (fwd+bwd per chunk) and scaled to whole views."""
+    from oracle import dense_torch
+    from vegs_b200 import synth
+    torch.set_num_threads(os.cpu_count() or 1)
+    sc = synth.make_scene(100_000, seed=7)
+    cam = synth.make_camera(0, scale=0.25)
+    npix = cam.W * cam.H
+    t_total = 0.0
+    for k in range(n_chunks):
+        t = {n: v.clone().requires_grad_(True) for n, v in sc.items()}
+        s0 = (npix // (n_chunks + 1)) * (k + 1)
+        t0 = time.time()
+        out = dense_torch.render_dense(
+            t["means3D"], t["opacities"], shs=t["shs"], scales=t["scales"], rotations=t["rotations"],
+            viewmatrix=cam.viewmatrix, projmatrix=cam.projmatrix, campos=cam.campos, bg=torch.zeros(3),
+            W=cam.W, H=cam.H, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, sh_degree=3, quat_map=False,
+            pixel_chunk=chunk, pixel_range=(s0, s0 + chunk))
+        (out["color"].sum() + out["depth"].sum() + out["alpha"].sum() + out["cov_scale"].sum()).backward()
+        t_total += time.time() - t0
+    frac = n_chunks * chunk / npix
+    return dict(value=frac / t_total, unit="views/s", cores=torch.get_num_threads(), kind="port",
+                config="BASELINE config 1: 100000 Gaussians SH-3, 352x94, fwd+bwd",
+                sample=f"{n_chunks} x {chunk} of the {npix} pixels (every Gaussian against every sampled pixel, "
+                       f"float32, autograd backward, quaternion map left out), scaled by {1 / frac:.1f} to a whole view")
+
+
 def emit(line: dict) -> None:
     """The ONE JSON line on the real stdout (everything else, e.g. NCCL's version banner, was
     redirected to stderr at start-up)."""
@@ -282,11 +332,9 @@ def main():
     ap.add_argument("--views", type=int, default=8)
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-fused-accum", action="store_true",
-                    help="let autograd add each view's gradient to .grad instead of the backward kernel")
+    ap.add_argument("--no-fused-leg", action="store_true",
+                    help="skip the extra value_fused / e2e_fused measurement of the vegs_b200 arm")
     args = ap.parse_args()
-    global FUSED_ACCUM
-    FUSED_ACCUM = not args.no_fused_accum
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -313,30 +361,24 @@ def main():
         import torch.distributed as dist
         import datetime
         dist.init_process_group("nccl", device_id=device, timeout=datetime.timedelta(seconds=180))
-    from vegs_b200 import _lib
+    ours = args.impl == "ours"
+    _lib = None
+    if ours:
+        # only the vegs_b200 arm may map libvegs_b200.so: the reference process must stay free of it
+        from vegs_b200 import _lib
     wl = Workload(args, device, rank, world)
 
-    launches0 = _lib.launch_count()
+    launches0 = _lib.launch_count() if ours else 0
     sampler = ClockSampler(local_rank) if rank == 0 else None
     ms = timed(lambda: wl.step(mod, True), args.steps, args.warmup, device, world)
     clocks = sampler.stop() if sampler else None
-    launches = (_lib.launch_count() - launches0) * args.steps // (args.steps + args.warmup)
+    launches = (_lib.launch_count() - launches0) * args.steps // (args.steps + args.warmup) if ours else 0
     ms_step = ms / args.steps
     value = args.views / (ms_step / 1000.0)
 
-    ms_e2e = timed(lambda: wl.step(mod, False), args.steps, 1, device, world)
+    ms_e2e = timed(lambda: wl.step(mod, False), args.steps, 3, device, world)
     e2e_value = args.views / (ms_e2e / args.steps / 1000.0)
-
-    # for transparency: the same step with the two opt-in fusions off (autograd adds each view's
-    # gradient, the caller computes the densification statistics), i.e. the plain drop-in module
-    unfused_value = None
-    if args.impl == "ours" and FUSED_ACCUM:
-        FUSED_ACCUM = False
-        mod.set_fused_grad_accumulation(False)
-        ms_u = timed(lambda: wl.step(mod, True), 2, 1, device, world)
-        unfused_value = args.views / (ms_u / 2 / 1000.0)
-        FUSED_ACCUM = True
-        mod.set_fused_grad_accumulation(True)
+    h2d = wl.h2d_bytes * len(wl.my_views) // args.views * world
 
     line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
                 ms_per_step=ms_step, higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32",
@@ -346,15 +388,29 @@ def main():
                                      "GaussianRasterizer + grad/densification-stat all-reduce (BASELINE config 3)",
                             P=args.P, views_per_step=args.views, image=[wl.W, wl.H], parallelism=f"view-parallel x{world}",
                             l2="inputs (1.4 GB of parameters per view) exceed the 126 MB L2; no explicit flush",
-                            impl=kind,
-                            grad_accumulation=("gradient accumulation and densification statistics fused into the backward kernel "
-                                               "(set_fused_grad_accumulation, set_densification_accumulators)"
-                                               if args.impl == "ours" and FUSED_ACCUM else "autograd add per view")),
-                e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=wl.h2d_bytes * len(wl.my_views) // args.views * world,
-                         d2h_bytes_per_step=4 * world),
-                gpu_launches=int(launches) if args.impl == "ours" else 0, clocks=clocks)
-    if unfused_value is not None:
-        line["value_without_fusions"] = unfused_value
+                            grad_accumulation="autograd add per view, densification statistics by the caller "
+                                              "(the reference's own calling convention, identical in both arms)"),
+                rasterizer=kind,
+                e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=4 * world),
+                gpu_launches=int(launches), clocks=clocks)
+
+    if ours and not args.no_fused_leg:
+        # the same step with this package's per-instance extensions (fused gradient accumulation into
+        # views of the all-reduce buffer + fused densification statistics): reported beside, not
+        # instead of, the drop-in figure, because the reference's callers cannot use them
+        ms_f = timed(lambda: wl.step(mod, True, fused=True), args.steps, 3, device, world)
+        line["value_fused"] = args.views / (ms_f / args.steps / 1000.0)
+        ms_fe = timed(lambda: wl.step(mod, False, fused=True), args.steps, 2, device, world)
+        line["e2e_fused"] = dict(value=args.views / (ms_fe / args.steps / 1000.0), unit=UNIT,
+                                 h2d_bytes_per_step=h2d, d2h_bytes_per_step=4 * world)
+        line["fused_what"] = ("GaussianRasterizer(settings, fused_grad_accumulation=..., densification_accumulators=...): "
+                              ".grad tensors and the step statistics are views of one flat all-reduce buffer")
+    if world > 1:
+        # weak scaling beside the fixed-batch figure: every rank renders 8 views per step (8 x N per step)
+        wv = list(range(rank * args.views, (rank + 1) * args.views))
+        ms_w = timed(lambda: wl.step(mod, True, views=wv), max(2, args.steps // 4), 1, device, world)
+        line["weak_scaling"] = dict(views_per_step=args.views * world,
+                                    value=args.views * world / (ms_w / max(2, args.steps // 4) / 1000.0), unit=UNIT)
     if args.impl == "reference":
         line["impl"] = "reference"
         line["cpu_baseline"] = dict(value=value, unit=UNIT, cores=0, kind="reference",
@@ -400,6 +456,7 @@ def main():
                                      frac=view_bytes / (ms_step / nv * 1e-3) / 1e9 / peak)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_oracle(args, 1)
+            line["cpu_baseline_dense_torch"] = cpu_baseline_dense_torch()
     if rank == 0:
         emit(line)
     if world > 1:

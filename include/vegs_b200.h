@@ -11,7 +11,9 @@
  * Every function returns 0 on success and a non-zero VEGS_E* code on failure; nothing throws or
  * aborts across the ABI.  vegs_last_error() returns a thread-local message for the last failure.
  * The library never allocates device memory: all state and scratch buffers are passed in, sized by
- * the *_bytes() queries below.  `stream` is a cudaStream_t passed as void*.
+ * the *_bytes() queries below (one exception, stated where it is declared: vegs_dist2_noalloc
+ * uses an array built into the library image).  `stream` is a cudaStream_t passed as void*; the
+ * CUDA device it belongs to must be the calling thread's current device.
  *
  * All paths cited below are relative to the reference tree (deepshwang/vegs).
  */
@@ -62,7 +64,9 @@ typedef struct VegsForwardArgs {
     const float* campos;         /* [3] */
     float scale_modifier;
     float tan_fovx, tan_fovy;
-    int32_t prefiltered;
+    int32_t prefiltered;         /* accepted for interface parity and ignored: the reference traps the
+                                  * kernel (printf + __trap, auxiliary.h:154-160) when it is set and a
+                                  * point fails the near cull; here such points are simply culled */
     int32_t debug;               /* non-zero: synchronise and check after every stage */
     /* outputs (rasterize_points.cu:69-76); every element is written by the kernels */
     float* out_color;     /* [3,H,W] */
@@ -79,8 +83,8 @@ typedef struct VegsForwardArgs {
     void* scratch;        /* vegs_scratch_bytes(P) */
     void* bin_scratch;    /* vegs_bin_scratch_bytes(R,W,H); only needed by vegs_forward_render */
     /* TWO host words (pinned memory), written asynchronously on `stream` by vegs_forward_prepare:
-     * [0] = num_rendered, [1] = number of emission work items.  Keep both untouched until
-     * vegs_forward_render has been called: it reads [1] on the host. */
+     * [0] = num_rendered, [1] = number of emission work items (informational).  The library never
+     * reads them back: num_rendered travels through the argument of vegs_forward_render. */
     int32_t* num_rendered_host;
 } VegsForwardArgs;
 
@@ -114,9 +118,9 @@ typedef struct VegsBackwardArgs {
     const float* dL_dout_cov_quat;  /* [4,H,W]  (ignored, see above) */
     const float* dL_dout_cov_scale; /* [3,H,W]  (ignored, see above) */
     const float* dL_dout_alpha;     /* [1,H,W] */
-    /* state from the forward */
+    /* state from the forward (img is not const: the backward leaves per-tile diagnostics in it) */
     const void* geom;
-    const void* img;
+    void* img;
     const void* binning;
     /* scratch: packed per-Gaussian blend-stage accumulators, vegs_bwd_scratch_bytes(P) */
     void* bwd_scratch;
@@ -185,7 +189,8 @@ int vegs_forward_prepare(const VegsForwardArgs* args, void* stream);
 int vegs_forward_render(const VegsForwardArgs* args, int32_t num_rendered, void* stream);
 
 /*
- * Backward: blend-stage gradients (warp-reduced atomics) then the per-Gaussian stage.
+ * Backward: blend-stage gradients (each compositing unit sums an entry's gradient over its pixels in
+ * registers and issues three 16-byte vector reductions per entry) then the per-Gaussian stage.
  * Replaces CudaRasterizer::Rasterizer::backward (cuda_rasterizer/rasterizer_impl.cu:356-481).
  */
 int vegs_backward(const VegsBackwardArgs* args, void* stream);
@@ -219,7 +224,8 @@ int vegs_dist2(int32_t P, const float* points, float* out, void* workspace, size
  * more than VEGS_DIST2_NOALLOC_MAX_POINTS points are refused with VEGS_ESIZE (use vegs_dist2).
  *
  * The first call on each device looks up the array's device address (a one-time set-up with that
- * device current); make that first call before starting any stream capture.  No call allocates or
+ * device current: the calling thread's current device must be the one `stream` belongs to, as for
+ * every entry point here); make that first call before starting any stream capture.  No call allocates or
  * frees memory.  All calls on a device share the one array, and it keeps whatever the previous
  * call left in it; nothing in it needs to be zero on entry, but two calls whose kernels overlap on
  * the GPU (different streams, or different host threads) race on it and give wrong results — run

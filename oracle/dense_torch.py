@@ -47,9 +47,11 @@ def eval_sh(deg, sh, dirs):
 
 def render_dense(means3D, opacities, *, shs=None, colors_precomp=None, scales=None, rotations=None,
                  viewmatrix, projmatrix, campos, bg, W, H, tanfovx, tanfovy, sh_degree=3,
-                 scale_modifier=1.0, quat_map=True, pixel_chunk=4096):
+                 scale_modifier=1.0, quat_map=True, pixel_chunk=4096, pixel_range=None):
     """Returns dict(color [3,H,W], depth [1,H,W], alpha [1,H,W], cov_scale [3,H,W],
-    cov_quat [4,H,W] (no gradient, as in the reference), radii [P], n_contrib [H,W])."""
+    cov_quat [4,H,W] (no gradient, as in the reference), radii [P], n_contrib [H,W]).
+    With pixel_range=(first, last) only that run of row-major pixel indices is evaluated and the
+    image outputs come back flattened ([3,n], [1,n], ...): bench.py's bounded CPU-baseline sample."""
     dt = means3D.dtype
     P = means3D.shape[0]
     view, proj = viewmatrix.to(dt), projmatrix.to(dt)
@@ -128,8 +130,10 @@ def render_dense(means3D, opacities, *, shs=None, colors_precomp=None, scales=No
     ys, xs = torch.meshgrid(torch.arange(H), torch.arange(W), indexing="ij")
     pix_x = xs.reshape(-1).to(dt)
     pix_y = ys.reshape(-1).to(dt)
-    for s0 in range(0, npix, pixel_chunk):
-        fx, fy = pix_x[s0:s0 + pixel_chunk, None], pix_y[s0:s0 + pixel_chunk, None]
+    p_first, p_last = (0, npix) if pixel_range is None else pixel_range
+    for s0 in range(p_first, p_last, pixel_chunk):
+        s1 = min(s0 + pixel_chunk, p_last)
+        fx, fy = pix_x[s0:s1, None], pix_y[s0:s1, None]
         n = fx.shape[0]
         with torch.no_grad():
             tix, tiy = torch.floor(fx / 16), torch.floor(fy / 16)
@@ -184,6 +188,10 @@ def render_dense(means3D, opacities, *, shs=None, colors_precomp=None, scales=No
     qn = quat.norm(dim=1, keepdim=True)
     ident = torch.zeros_like(quat); ident[:, 0] = 1
     quat = torch.where(qn > 0, quat / qn.clamp_min(1e-300), ident)
+    if pixel_range is not None:
+        return dict(color=torch.cat(out_color, 0).t(), depth=torch.cat(out_depth, 0)[None],
+                    alpha=torch.cat(out_alpha, 0)[None], cov_scale=torch.cat(out_scale, 0).t(),
+                    cov_quat=quat[p_first:p_last].t(), radii=radii, n_contrib=torch.cat(out_ncontrib, 0))
     return dict(color=torch.cat(out_color, 0).t().reshape(3, H, W),
                 depth=torch.cat(out_depth, 0).reshape(1, H, W),
                 alpha=torch.cat(out_alpha, 0).reshape(1, H, W),

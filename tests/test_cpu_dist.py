@@ -110,17 +110,14 @@ def test_two_rank_step_equals_single_rank(tmp_path):
     assert torch.equal(got["maxr"], stats.max_radii2D)
 
 
-def test_densification_stats_attach_falls_back_for_modules_without_the_extension():
-    """attach() registers the buffers with a module that offers set_densification_accumulators and
+def test_densification_stats_kwargs_fall_back_for_modules_without_the_extension():
+    """rasterizer_kwargs() hands the buffers to a module that offers per-instance extensions and
     leaves add_view as the path for one that does not (the reference's module)."""
     P = 16
 
     class WithExtension:
-        registered = None
-
-        @staticmethod
-        def set_densification_accumulators(a=None, b=None, c=None):
-            WithExtension.registered = None if a is None else (a, b, c)
+        class RasterizerOptions:
+            pass
 
     class Reference:
         pass
@@ -129,29 +126,91 @@ def test_densification_stats_attach_falls_back_for_modules_without_the_extension
     grad = torch.ones(P, 3)
 
     s = vdist.DensificationStats(P, "cpu")
-    assert s.attach(Reference) is False
+    assert s.rasterizer_kwargs(Reference) == {} and s.fused is False
+    ids = (id(s.xyz_gradient_accum), id(s.denom), id(s.max_radii2D))
     s.add_view(grad, radii)
+    assert ids == (id(s.xyz_gradient_accum), id(s.denom), id(s.max_radii2D)), "tensors keep their identity"
     assert float(s.denom.sum()) == P // 2 and float(s.max_radii2D.max()) == 3.0
     assert torch.allclose(s.xyz_gradient_accum[radii > 0], torch.full((P // 2, 1), 2.0 ** 0.5))
 
     f = vdist.DensificationStats(P, "cpu")
-    assert f.attach(WithExtension) is True
-    assert WithExtension.registered[0] is f.xyz_gradient_accum and WithExtension.registered[2] is f.max_radii2D
+    kw = f.rasterizer_kwargs(WithExtension)
+    assert f.fused and kw["densification_accumulators"][0] is f.xyz_gradient_accum
+    assert kw["densification_accumulators"][2] is f.max_radii2D
     f.add_view(grad, radii)                      # the kernel would have done it: no-op
     assert float(f.denom.sum()) == 0.0
-    f.detach(WithExtension)
-    assert WithExtension.registered is None
-    f.add_view(grad, radii)
-    assert float(f.denom.sum()) == P // 2
 
 
-def test_extension_setters_validate_their_arguments():
+def test_rasterizer_options_validate_their_arguments():
     import pytest
     import vegs_b200.diff_gaussian_rasterization as dgr
     cpu = torch.zeros(4, 1)
     with pytest.raises(ValueError):
-        dgr.set_densification_accumulators(cpu, cpu, torch.zeros(4))     # not CUDA tensors
-    dgr.set_densification_accumulators()                                  # clearing always works
-    dgr.set_fused_grad_accumulation(True)
-    assert dgr._accum_target(torch.zeros(3, requires_grad=True), (3,)) is None   # leaf without .grad yet
-    dgr.set_fused_grad_accumulation(False)
+        dgr.RasterizerOptions(densification_accumulators=(cpu, cpu, torch.zeros(4)))     # not CUDA tensors
+    with pytest.raises(ValueError):
+        dgr.RasterizerOptions(fused_grad_accumulation="sometimes")
+    assert not dgr.RasterizerOptions().any
+    assert dgr.RasterizerOptions(True).fused_grad_accumulation == "add"
+    assert dgr._accum_target(torch.zeros(3, requires_grad=True), (3,), "add") is None   # leaf without .grad yet
+    # extensions are a property of the instance: a plain rasterizer next to an extended one has none
+    z = torch.zeros
+    rs = dgr.GaussianRasterizationSettings(16, 16, 1.0, 1.0, z(3), 1.0, torch.eye(4), torch.eye(4), 3, z(3), False, False)
+    a, b = dgr.GaussianRasterizer(rs, fused_grad_accumulation=True), dgr.GaussianRasterizer(rs)
+    assert a.options.any and not b.options.any
+    assert not hasattr(dgr, "set_fused_grad_accumulation") and not hasattr(dgr, "set_densification_accumulators")
+
+
+def _worker_two_steps(rank, world, port, P, n_views, out):
+    """Two optimisation steps with a persistent FlatGradBuffer and a running DensificationStats:
+    .grad tensors are views of the flat buffer across steps, the per-step statistics are reduced as
+    deltas and added to the running accumulator once (not world-size times)."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    params = _make_params(P)
+    buf = vdist.FlatGradBuffer(params)
+    running = vdist.DensificationStats(P, "cpu")
+    flat_ptr = buf.flat.data_ptr()
+    grads = []
+    for step in range(2):
+        buf.begin_step()
+        kw = buf.rasterizer_kwargs(object, first=True)      # a module without extensions
+        assert kw == {}
+        for v in vdist.shard_views(n_views, rank, world):
+            radii, vg = _fake_view(params, v + 10 * step)
+            buf.step_stats.add_view(vg, radii)
+        assert params["shs"].grad.data_ptr() == buf.grad_views["shs"].data_ptr()
+        buf.allreduce(accumulate_into=running)
+        assert buf.flat.data_ptr() == flat_ptr
+        grads.append({k: v.grad.clone() for k, v in params.items()})
+    # the compatibility path with a reused flat buffer whose slices are already the .grad tensors
+    stats = vdist.DensificationStats(P, "cpu")
+    flat = vdist.allreduce_step(params, stats, flat=None)
+    for t in params.values():
+        t.grad.zero_()
+    _fake_view(params, 99)
+    flat2 = vdist.allreduce_step(params, stats, flat=flat)     # inputs alias `flat`: must not raise
+    assert flat2.data_ptr() == flat.data_ptr()
+    if rank == 0:
+        torch.save(dict(grads=grads, accum=running.xyz_gradient_accum.clone(), denom=running.denom.clone(),
+                        maxr=running.max_radii2D.clone()), out)
+    dist.destroy_process_group()
+
+
+def test_two_steps_with_persistent_buffers(tmp_path):
+    P, n_views = 120, 4
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_worker_two_steps, args=(2, _free_port(), P, n_views, out), nprocs=2, join=True)
+    got = torch.load(out)
+    params = _make_params(P)
+    running = vdist.DensificationStats(P, "cpu")
+    for step in range(2):
+        stats = _run_views(params, [v + 10 * step for v in range(n_views)])
+        for k in params:
+            assert torch.allclose(got["grads"][step][k], params[k].grad, rtol=1e-5, atol=1e-5), (step, k)
+        running.xyz_gradient_accum += stats.xyz_gradient_accum
+        running.denom += stats.denom
+        running.max_radii2D = torch.maximum(running.max_radii2D, stats.max_radii2D)
+    assert torch.allclose(got["accum"], running.xyz_gradient_accum, rtol=1e-6, atol=1e-6)
+    assert torch.equal(got["denom"], running.denom)
+    assert torch.equal(got["maxr"], running.max_radii2D)

@@ -95,45 +95,50 @@ def test_against_oracle_plain_id_lists():
 
 
 def test_fused_grad_accumulation_equals_autograd_accumulation():
-    """Three views accumulated into .grad: with set_fused_grad_accumulation the backward kernel adds
-    into the leaves' .grad itself; the result must equal autograd's separate add (up to the order of
-    the blend stage's floating-point reductions, which differs from run to run)."""
+    """Three views accumulated into .grad: with GaussianRasterizer(..., fused_grad_accumulation=True)
+    the backward kernel adds into the leaves' .grad itself; the result must equal autograd's
+    separate add (up to the order of the blend stage's floating-point reductions, which differs
+    from run to run).  The third mode starts from .grad tensors full of garbage and lets the first
+    view overwrite them ("assign")."""
     import torch
     import vegs_b200.diff_gaussian_rasterization as dgr
     dev = torch.device("cuda")
     scene = util.scene_with_specials(30000)
     cams = [synth.make_camera(v, scale=0.25) for v in range(3)]
 
-    def accumulate(fused):
-        dgr.set_fused_grad_accumulation(fused)
-        try:
-            t = {k: v.to(dev).clone().requires_grad_(True) for k, v in scene.items() if k in
-                 ("means3D", "opacities", "shs", "scales", "rotations")}
-            for i, cam in enumerate(cams):
-                rs = dgr.GaussianRasterizationSettings(
-                    image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
-                    bg=torch.tensor([0.1, 0.2, 0.3], device=dev), scale_modifier=1.0,
-                    viewmatrix=cam.viewmatrix.to(dev), projmatrix=cam.projmatrix.to(dev), sh_degree=3,
-                    campos=cam.campos.to(dev), prefiltered=False, debug=False)
-                means2D = torch.zeros_like(t["means3D"], requires_grad=True)
-                color, depth, quat, scale, alpha, radii = dgr.GaussianRasterizer(rs)(
-                    means3D=t["means3D"], means2D=means2D, opacities=t["opacities"], shs=t["shs"],
-                    scales=t["scales"], rotations=t["rotations"])
-                ((color * (0.5 + i)).sum() + depth.mean() + alpha.sum()).backward()
-                assert means2D.grad is not None
-            return {k: v.grad.detach().cpu().numpy() for k, v in t.items()}
-        finally:
-            dgr.set_fused_grad_accumulation(False)
+    def accumulate(mode):
+        t = {k: v.to(dev).clone().requires_grad_(True) for k, v in scene.items() if k in
+             ("means3D", "opacities", "shs", "scales", "rotations")}
+        if mode == "assign":
+            for v in t.values():
+                v.grad = torch.full_like(v, 1e30)       # stale contents the first view must overwrite
+        for i, cam in enumerate(cams):
+            rs = dgr.GaussianRasterizationSettings(
+                image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+                bg=torch.tensor([0.1, 0.2, 0.3], device=dev), scale_modifier=1.0,
+                viewmatrix=cam.viewmatrix.to(dev), projmatrix=cam.projmatrix.to(dev), sh_degree=3,
+                campos=cam.campos.to(dev), prefiltered=False, debug=False)
+            means2D = torch.zeros_like(t["means3D"], requires_grad=True)
+            fuse = False if mode == "plain" else ("assign" if (mode == "assign" and i == 0) else True)
+            color, depth, quat, scale, alpha, radii = dgr.GaussianRasterizer(rs, fused_grad_accumulation=fuse)(
+                means3D=t["means3D"], means2D=means2D, opacities=t["opacities"], shs=t["shs"],
+                scales=t["scales"], rotations=t["rotations"])
+            ((color * (0.5 + i)).sum() + depth.mean() + alpha.sum()).backward()
+            assert means2D.grad is not None
+        return {k: v.grad.detach().cpu().numpy() for k, v in t.items()}
 
-    plain, fused = accumulate(False), accumulate(True)
+    plain, fused, assigned = accumulate("plain"), accumulate("add"), accumulate("assign")
     for k in plain:
         assert np.abs(plain[k]).max() > 0, k
         util.grad_close(fused[k], plain[k], f"accumulated grad {k}", rtol=1e-5)
+        util.grad_close(assigned[k], plain[k], f"assigned + accumulated grad {k}", rtol=1e-5)
 
 
 def test_fused_densification_statistics_equal_the_separate_passes():
-    """set_densification_accumulators: the backward kernel's own update of xyz_gradient_accum / denom /
-    max_radii2D over three views equals DensificationStats.add_view on the returned tensors."""
+    """GaussianRasterizer(..., densification_accumulators=...): the backward kernel's own update of
+    xyz_gradient_accum / denom / max_radii2D over three views equals DensificationStats.add_view on the
+    returned tensors; a second, plain rasterizer used in between (VEGS's augmented-camera render,
+    train.py:172-193) and one with another Gaussian count (box models) leave the statistics alone."""
     import torch
     import vegs_b200.diff_gaussian_rasterization as dgr
     from vegs_b200 import dist as vdist
@@ -142,24 +147,28 @@ def test_fused_densification_statistics_equal_the_separate_passes():
     P = scene["means3D"].shape[0]
     t = {k: v.to(dev) for k, v in scene.items() if k in ("means3D", "opacities", "shs", "scales", "rotations")}
     fused, plain = vdist.DensificationStats(P, dev), vdist.DensificationStats(P, dev)
-    assert fused.attach(dgr)
-    try:
-        for i in range(3):
-            cam = synth.make_camera(i, scale=0.25)
-            rs = dgr.GaussianRasterizationSettings(
-                image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
-                bg=torch.zeros(3, device=dev), scale_modifier=1.0, viewmatrix=cam.viewmatrix.to(dev),
-                projmatrix=cam.projmatrix.to(dev), sh_degree=3, campos=cam.campos.to(dev),
-                prefiltered=False, debug=False)
-            means2D = torch.zeros_like(t["means3D"], requires_grad=True)
-            color, depth, quat, scale, alpha, radii = dgr.GaussianRasterizer(rs)(
-                means3D=t["means3D"], means2D=means2D, opacities=t["opacities"], shs=t["shs"],
-                scales=t["scales"], rotations=t["rotations"])
-            (color.sum() + depth.mean()).backward()
-            plain.add_view(means2D.grad, radii)
-            fused.add_view(means2D.grad, radii)          # no-op while attached
-    finally:
-        fused.detach(dgr)
+    kw = fused.rasterizer_kwargs(dgr)
+    assert fused.fused and "densification_accumulators" in kw
+    for i in range(3):
+        cam = synth.make_camera(i, scale=0.25)
+        rs = dgr.GaussianRasterizationSettings(
+            image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+            bg=torch.zeros(3, device=dev), scale_modifier=1.0, viewmatrix=cam.viewmatrix.to(dev),
+            projmatrix=cam.projmatrix.to(dev), sh_degree=3, campos=cam.campos.to(dev),
+            prefiltered=False, debug=False)
+        means2D = torch.zeros_like(t["means3D"], requires_grad=True)
+        color, depth, quat, scale, alpha, radii = dgr.GaussianRasterizer(rs, **kw)(
+            means3D=t["means3D"], means2D=means2D, opacities=t["opacities"], shs=t["shs"],
+            scales=t["scales"], rotations=t["rotations"])
+        (color.sum() + depth.mean()).backward()
+        plain.add_view(means2D.grad, radii)
+        fused.add_view(means2D.grad, radii)          # no-op: the kernel did it
+        # a plain instance, and one with fewer Gaussians, in the same iteration: no effect on the statistics
+        for n in (P, P // 3):
+            m2 = torch.zeros((n, 3), device=dev, requires_grad=True)
+            o = dgr.GaussianRasterizer(rs)(means3D=t["means3D"][:n], means2D=m2, opacities=t["opacities"][:n],
+                                           shs=t["shs"][:n], scales=t["scales"][:n], rotations=t["rotations"][:n])
+            o[0].sum().backward()
     assert float(plain.denom.sum()) > 0
     util.assert_bit_equal(fused.denom.cpu().numpy(), plain.denom.cpu().numpy(), "denom")
     util.assert_bit_equal(fused.max_radii2D.cpu().numpy(), plain.max_radii2D.cpu().numpy(), "max_radii2D")

@@ -36,11 +36,15 @@ NVCC_FLAGS = [
   + os.environ.get("VEGS_NVCC_EXTRA", "").split()     # tuning sweeps, e.g. -DVEGS_FWD_SUPER=128
 
 
+class NvccMissing(RuntimeError):
+    """No nvcc on this machine (the GPU box runs the prebuilt library)."""
+
+
 def _nvcc() -> str:
     for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
         if cand and os.path.exists(cand):
             return cand
-    raise RuntimeError("nvcc not found; cannot build libvegs_b200.so")
+    raise NvccMissing("nvcc not found; cannot build libvegs_b200.so")
 
 
 def _stale(target: str, deps: list[str]) -> bool:

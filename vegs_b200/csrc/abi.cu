@@ -44,6 +44,10 @@ void prof_mark(const char* name, cudaStream_t stream) {
     g_prof_events.push_back({name, ev});
 }
 
+// 32-bit depth keys, kRadixBits per pass: the sorted order ends in the second buffer pair iff the
+// number of passes is odd.  Used by both forward stages so they cannot disagree.
+static constexpr bool depth_sort_in_second() { return (((32 + kRadixBits - 1) / kRadixBits) & 1) != 0; }
+
 static int tile_bits(int T) {
     int b = 0;
     while ((1 << b) < T) b++;
@@ -165,6 +169,7 @@ extern "C" int vegs_forward_prepare(const VegsForwardArgs* a, void* stream_) {
                           (uint32_t)a->P, 32, s.hist, s.rowtot, /*write_last_keys=*/false, &second,
                           stream, a->debug != 0);
     if (rc) return rc;
+    if (second != depth_sort_in_second()) { set_error("internal: depth sort pass parity"); return VEGS_EINVAL; }
     const uint32_t* order = second ? s.vals1 : s.vals0;
     rc = launch_tile_count(a->P, order, s.rect, s.chunksum, s.partbase, g.counters, stream,
                            a->debug != 0);
@@ -209,12 +214,12 @@ extern "C" int vegs_forward_render(const VegsForwardArgs* a, int32_t num_rendere
         uint32_t *k0 = bs.tkeys0, *k1 = bs.tkeys1, *v0, *v1;
         if ((passes & 1) == 0) { v0 = b.point_list; v1 = bs.tvals1; }
         else { v0 = bs.tvals1; v1 = b.point_list; }
-        const uint32_t* order = s.vals0;  // 4 depth passes: result is back in the first pair
-        if (!a->num_rendered_host || a->num_rendered_host[0] != num_rendered) {
-            set_error("vegs_forward_render: num_rendered_host must still hold what vegs_forward_prepare wrote");
-            return VEGS_EINVAL;
-        }
-        const uint32_t nparts = (uint32_t)a->num_rendered_host[1];
+        // the depth sort's result buffer, derived exactly as vegs_forward_prepare derives it
+        const uint32_t* order = depth_sort_in_second() ? s.vals1 : s.vals0;
+        // Upper bound of the emission work items (chunk c needs ceil(instances_c / part) CTAs): the
+        // exact count lives on the device (partbase[nchunks]); surplus CTAs exit at once, so the
+        // host never has to read it back.
+        const uint32_t nparts = div_up((uint32_t)a->P, kEmitChunk) + div_up(R, kEmitPartInstances);
         rc = launch_emit(a->P, order, s.rect, s.chunksum, s.partbase, nparts, gx, k0, v0, R, s.pbox, a->W, a->H,
                          stream, debug);
         if (rc) return rc;

@@ -23,7 +23,7 @@ namespace vegs {
 namespace {
 
 constexpr int kEmitThreads = 256;
-constexpr uint32_t kEmitPart = 8192;   // instances emitted by one CTA
+constexpr uint32_t kEmitPart = kEmitPartInstances;   // instances emitted by one CTA
 constexpr int kEmitPerThread = kEmitChunk / kEmitThreads;  // 4
 
 __device__ __forceinline__ uint32_t rect_tiles(uint2 r) {
@@ -149,6 +149,8 @@ emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__
     __shared__ uint32_t s_off[kEmitChunk + 1];
     __shared__ uint32_t s_warp[kEmitThreads / 32];
 
+    // the grid is an upper bound of the work items (abi.cu): surplus CTAs have nothing to do
+    if (blockIdx.x >= partbase[nchunks]) return;
     // which chunk does this part belong to: last c with partbase[c] <= blockIdx.x
     uint32_t clo = 0, chi = nchunks;
     while (chi - clo > 1) {

@@ -27,6 +27,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stddef.h>
+#include <atomic>
 #include "../../include/vegs_b200.h"
 
 namespace vegs {
@@ -55,6 +56,7 @@ constexpr int kRectStride = 2;    // {tile rect, pixel box} per Gaussian, in uin
 constexpr uint32_t kListIdMask = 0x00ffffffu;
 bool list_has_unit_masks(int P);   // abi.cu: P < 2^24 unless disabled through vegs_debug_unit_masks
 constexpr int kEmitChunk = 1024;  // depth-sorted Gaussians per emission block
+constexpr uint32_t kEmitPartInstances = 8192;   // instances emitted by one CTA
 
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 static inline uint32_t div_up(uint64_t a, uint64_t b) { return (uint32_t)((a + b - 1) / b); }
@@ -188,6 +190,16 @@ static inline BinScratchView bin_scratch_view(void* base, int64_t R) {
     v.bytes = (size_t)(cur - reinterpret_cast<char*>(base));
     return v;
 }
+
+// ---------------------------------------------------------------- per-device one-time set-up (host)
+// Opt-in shared-memory sizes and carve-outs are per-device function attributes.  Thread-safe: one
+// atomic bit per device ordinal; two threads that race on the first use both set the (idempotent)
+// attributes, nothing else.
+struct DeviceOnce {
+    std::atomic<uint64_t> bits{0};
+    bool need(int dev) const { return ((bits.load(std::memory_order_acquire) >> (dev & 63)) & 1ull) == 0ull; }
+    void done(int dev) { bits.fetch_or(1ull << (dev & 63), std::memory_order_release); }
+};
 
 // ---------------------------------------------------------------- error handling (host)
 void set_error(const char* fmt, ...);

@@ -292,17 +292,16 @@ int launch_composite_bwd(const VegsBackwardArgs& a, const GeomView& g, const Img
     p.dL_dcolor = a.dL_dout_color; p.dL_ddepth = a.dL_dout_depth; p.dL_dalpha = a.dL_dout_alpha;
     p.acc = acc;
     const int T = p.gx * ((a.H + kTile - 1) / kTile);
-    p.tile_clocks = const_cast<uint32_t*>(im.tile_clocks) + T;
-    p.tile_dbg = const_cast<uint32_t*>(im.tile_dbg);
+    p.tile_clocks = im.tile_clocks + T;
+    p.tile_dbg = im.tile_dbg;
     // opt-in shared memory size is a per-device function attribute
-    static bool configured_dev[64] = {};
+    static DeviceOnce once;
     int dev = 0;
     VEGS_CUDA_OK(cudaGetDevice(&dev));
-    bool& configured = configured_dev[dev & 63];
-    if (!configured) {
+    if (once.need(dev)) {
         VEGS_CUDA_OK(cudaFuncSetAttribute(composite_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)sizeof(BwdSmem)));
-        configured = true;
+        once.done(dev);
     }
     composite_bwd_kernel<<<T * kUnitsPerTile, kSuper, sizeof(BwdSmem), stream>>>(p);
     VEGS_LAUNCH_CHECK("composite_bwd", stream, a.debug);

@@ -69,13 +69,20 @@ __device__ __forceinline__ bool unit_box(const float4 a, int bx0, int by0, int b
 // Which pixels are put to that test is narrowed conservatively first: to the entry's box, and in
 // each pixel row to the interval where the quadratic can reach -(log(255 opacity) + 0.01)
 // (alpha >= 1/255 needs power >= -log(255 opacity)); an elongated Gaussian fills a small part of
-// its box.  The margins (0.01 in power, 0.02 px, 0.05% of the half width) are orders of magnitude
-// above the float error of the interval; a non-finite interval falls back to the whole row.
+// its box.  What has to be bounded is the REFERENCE's float evaluation of the power, whose rounding
+// error grows with the size of the cancelling terms A dx^2, C dy^2, 2 B dx dy (1e5 - 1e6 for a
+// long thin splat centred far outside the tile): the threshold is therefore widened by 0.01 plus
+// 2e-6 (~32 float epsilons) of those terms at the unit's farthest corner.  The remaining margins
+// (0.02 px, 0.05% of the half width) cover the interval arithmetic itself; a non-finite interval
+// falls back to the whole row.
 __device__ __forceinline__ uint32_t entry_hits_fwd(const float4 a, const float4 b, int bx0, int by0, int bx1,
                                                    int by1, float2* mat, int slot, int stride) {
     int x0, x1, y0, y1;
     if (!unit_box(a, bx0, by0, bx1, by1, x0, x1, y0, y1)) return 0u;
-    const float tau = __logf(255.0f * b.w) + 0.01f;
+    const float dxm = fmaxf(fabsf(a.x - (float)bx0), fabsf(a.x - (float)bx1));
+    const float dym = fmaxf(fabsf(a.y - (float)by0), fabsf(a.y - (float)by1));
+    const float mag = fabsf(b.x) * dxm * dxm + fabsf(b.z) * dym * dym + 2.0f * fabsf(b.y) * dxm * dym;
+    const float tau = __logf(255.0f * b.w) + 0.01f + 2e-6f * mag;
     const float bb = b.y * b.y;
     const float det = fmaf(b.x, b.z, -bb) - fmaf(b.y, b.y, -bb);      // compensated A*C - B*B
     const float inv_a = 1.0f / b.x;

@@ -528,16 +528,15 @@ int launch_composite_fwd(const VegsForwardArgs& a, const GeomView& g, const Scra
     p.tile_dbg = im.tile_dbg;
     const int T = p.gx * ((a.H + kTile - 1) / kTile);
     // opt-in shared memory size is a per-device function attribute
-    static bool configured_dev[64] = {};
+    static DeviceOnce once;
     int dev = 0;
     VEGS_CUDA_OK(cudaGetDevice(&dev));
-    bool& configured = configured_dev[dev & 63];
-    if (!configured) {
+    if (once.need(dev)) {
         VEGS_CUDA_OK(cudaFuncSetAttribute(composite_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)sizeof(FwdSmem)));
         VEGS_CUDA_OK(cudaFuncSetAttribute(composite_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)sizeof(FwdSmem)));
-        configured = true;
+        once.done(dev);
     }
     VEGS_CUDA_OK(cudaMemsetAsync(im.tile_clocks, 0, (size_t)2 * T * sizeof(uint32_t), stream));
 #if VEGS_TILE_DEBUG

@@ -300,7 +300,15 @@ extern "C" int vegs_dist2(int32_t P, const float* points, float* out, void* work
 // the device address is looked up once per device with cudaGetSymbolAddress and then passed to the
 // kernels like any other workspace pointer.
 constexpr int32_t kNoAllocMaxPoints = VEGS_DIST2_NOALLOC_MAX_POINTS;
-constexpr size_t kNoAllocScratchBytes = 6u << 20;  // 6 MiB >= vegs_dist2_workspace_bytes(131072)
+constexpr size_t kNoAllocScratchBytes = VEGS_DIST2_NOALLOC_SCRATCH_BYTES;
+// the carve-out of knn_view() for the largest accepted input: 4 sort arrays + histograms + sorted
+// points + three box levels (each region rounded up to 256 B) must fit, plus the alignment slack
+constexpr size_t kNoAllocNeed =
+    256 + (size_t)VEGS_DIST2_NOALLOC_MAX_POINTS * (4 * 4 + 16) +
+    (size_t)vegs::kRadix * 4 * ((VEGS_DIST2_NOALLOC_MAX_POINTS + vegs::kSortTile - 1) / vegs::kSortTile) + vegs::kRadix * 4 +
+    32 * ((size_t)VEGS_DIST2_NOALLOC_MAX_POINTS / 32 + VEGS_DIST2_NOALLOC_MAX_POINTS / 1024 + 16) + 16 * 256;
+static_assert(kNoAllocNeed <= kNoAllocScratchBytes,
+              "VEGS_DIST2_NOALLOC_SCRATCH_BYTES cannot hold the workspace of VEGS_DIST2_NOALLOC_MAX_POINTS points");
 static __device__ __align__(256) unsigned char g_dist2_noalloc_scratch[kNoAllocScratchBytes];
 
 namespace {
@@ -329,7 +337,9 @@ extern "C" int vegs_dist2_noalloc(int32_t P, const float* points, float* out, vo
     }
     void* scratch = nullptr;
     {
-        // Set-up, once per device, with that device current (it is: we just asked which one is).
+        // Set-up, once per device, with that device current (it is: we just asked which one is;
+        // the header requires the current device to be the stream's).  The cached address stays
+        // valid until the process exits or the device is reset.
         std::lock_guard<std::mutex> lk(g_noalloc_mu);
         if (g_noalloc_ptr[dev] == nullptr) {
             void* p = nullptr;

@@ -275,9 +275,16 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_fwd_kernel(const PrePa
                 if (tau < 0.0f) {
                     ex = ey = -1.0f;
                 } else if (cdet > 0.0f) {
-                    const float s2 = 2.0f * tau / cdet;
-                    const float tx = sqrtf(s2 * conic.z) * 1.002f + 0.01f;
-                    const float ty = sqrtf(s2 * conic.x) * 1.002f + 0.01f;
+                    // The reference evaluates the power in float; its rounding error scales with the
+                    // cancelling terms A dx^2, C dy^2, 2 B dx dy, which reach 1e5 - 1e6 at the far end
+                    // of a long thin splat.  Widen tau by 2e-6 (~32 float epsilons) of their size at
+                    // the corner of the first-guess box, twice over because the box grows with tau.
+                    float s2 = 2.0f * tau / cdet;
+                    float tx = sqrtf(s2 * conic.z), ty = sqrtf(s2 * conic.x);
+                    const float mag = conic.x * tx * tx + conic.z * ty * ty + 2.0f * fabsf(conic.y) * tx * ty;
+                    s2 = 2.0f * (tau + 4e-6f * mag) / cdet;
+                    tx = sqrtf(s2 * conic.z) * 1.002f + 0.01f;
+                    ty = sqrtf(s2 * conic.x) * 1.002f + 0.01f;
                     if (isfinite(tx) && isfinite(ty)) { ex = tx; ey = ty; }
                 }
             }

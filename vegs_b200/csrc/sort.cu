@@ -181,14 +181,14 @@ int radix_sort_pairs(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, boo
     const int passes = (nbits + kRadixBits - 1) / kRadixBits;
     {
         // four 43 KB blocks per SM only fit with the shared-memory carve-out at its maximum
-        static bool configured_dev[64] = {};
+        static DeviceOnce once;
         int dev = 0;
         VEGS_CUDA_OK(cudaGetDevice(&dev));
-        if (!configured_dev[dev & 63]) {
+        if (once.need(dev)) {
             VEGS_CUDA_OK(cudaFuncSetAttribute(radix_scatter_kernel<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
             VEGS_CUDA_OK(cudaFuncSetAttribute(radix_scatter_kernel<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
             VEGS_CUDA_OK(cudaFuncSetAttribute(radix_scatter_kernel<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-            configured_dev[dev & 63] = true;
+            once.done(dev);
         }
     }
     uint32_t *kin = k0, *vin = v0, *kout = k1, *vout = v1;

@@ -198,46 +198,60 @@ def export_state(st: _State, radii: torch.Tensor):
 
 
 _ACC_BITS = dict(means3D=1, sh=2, colors=4, opacity=8, scales=16, rotations=32, cov3D=64)   # VEGS_ACC_*
-_fused_grad_accumulation = False
 
 
-def set_fused_grad_accumulation(enabled: bool) -> None:
-    """Opt-in extension (no reference counterpart) for loops that accumulate several views into
-    `.grad` before an optimiser step.  When enabled, the backward pass adds its result straight into
-    the existing `.grad` of every rasterizer input that is a leaf tensor (float32, contiguous, same
-    shape) instead of returning a fresh tensor for autograd to add in a separate pass over the
-    parameters; inputs without a `.grad` yet, and non-leaf inputs, take the normal route.  Hooks
-    registered on those leaves' gradient accumulation do not fire for the fused inputs."""
-    global _fused_grad_accumulation
-    _fused_grad_accumulation = bool(enabled)
+class RasterizerOptions:
+    """Opt-in extensions of ONE GaussianRasterizer instance (no reference counterpart; a plain
+    `GaussianRasterizer(raster_settings)` has none of them and behaves exactly like the reference's
+    module).  They are a property of the rasterizer object, not of the module: a second render in
+    the same iteration through another instance (VEGS's augmented-camera render, train.py:172-193, or
+    a box model with its own Gaussian count, scene/gaussian_model.py:517) is not affected.
+
+    fused_grad_accumulation
+        For loops that accumulate several views into `.grad` before an optimiser step.  The backward
+        pass adds its result straight into the existing `.grad` of every rasterizer input that is a
+        leaf tensor (float32, contiguous, same shape) instead of returning a fresh tensor for
+        autograd to add in a separate pass over the parameters; inputs without a `.grad` yet, and
+        non-leaf inputs, take the normal route.  With the value "assign" the existing `.grad` is
+        overwritten instead of added to (first view of a step whose `.grad` tensors are views of a
+        persistent flat buffer that was not cleared; only valid when this rasterizer call is the
+        leaf's only consumer in that backward pass, because a gradient autograd adds from another
+        path may land before the overwrite).  Hooks registered on those leaves' gradient
+        accumulation do not fire for the fused inputs.
+    densification_accumulators
+        `(xyz_gradient_accum [P,1], denom [P,1], max_radii2D [P])`, VEGS's three densification
+        statistics (scene/gaussian_model.py:154-172; float32, CUDA, contiguous).  The backward pass
+        of this instance updates them itself for the Gaussians its view rendered (radii > 0):
+        `xyz_gradient_accum += ||means2D.grad[:, :2]||`, `denom += 1`,
+        `max_radii2D = max(., radii)` - what train.py:300-301 + add_densification_stats do in
+        separate passes over all Gaussians.
+    """
+    __slots__ = ("fused_grad_accumulation", "densification_accumulators")
+
+    def __init__(self, fused_grad_accumulation=False, densification_accumulators=None):
+        if fused_grad_accumulation not in (False, True, "add", "assign"):
+            raise ValueError("fused_grad_accumulation must be False, True / 'add', or 'assign'")
+        self.fused_grad_accumulation = "add" if fused_grad_accumulation is True else fused_grad_accumulation
+        if densification_accumulators is not None:
+            acc = tuple(densification_accumulators)
+            if len(acc) != 3:
+                raise ValueError("densification accumulators: (xyz_gradient_accum, denom, max_radii2D)")
+            for t in acc:
+                if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+                    raise ValueError("densification accumulators must be contiguous float32 CUDA tensors")
+            if not (acc[0].numel() == acc[1].numel() == acc[2].numel()):
+                raise ValueError("densification accumulators must have one element per Gaussian")
+            densification_accumulators = acc
+        self.densification_accumulators = densification_accumulators
+
+    @property
+    def any(self) -> bool:
+        return bool(self.fused_grad_accumulation) or self.densification_accumulators is not None
 
 
-_densification_accumulators = None
-
-
-def set_densification_accumulators(xyz_gradient_accum=None, denom=None, max_radii2D=None) -> None:
-    """Opt-in extension (no reference counterpart).  Registers the three per-Gaussian statistics
-    buffers of VEGS's densification (`scene/gaussian_model.py:154-172`: `xyz_gradient_accum` [P,1],
-    `denom` [P,1], `max_radii2D` [P]; float32, CUDA, contiguous).  Every following backward pass then
-    updates them itself for the Gaussians its view rendered (radii > 0):
-    `xyz_gradient_accum += ||means2D.grad[:, :2]||`, `denom += 1`, `max_radii2D = max(., radii)` - what
-    `train.py:300-301` + `add_densification_stats` do in separate passes over all Gaussians.
-    Call with no arguments to stop."""
-    global _densification_accumulators
-    if xyz_gradient_accum is None:
-        _densification_accumulators = None
-        return
-    for t in (xyz_gradient_accum, denom, max_radii2D):
-        if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
-            raise ValueError("densification accumulators must be contiguous float32 CUDA tensors")
-    if not (xyz_gradient_accum.numel() == denom.numel() == max_radii2D.numel()):
-        raise ValueError("densification accumulators must have one element per Gaussian")
-    _densification_accumulators = (xyz_gradient_accum, denom, max_radii2D)
-
-
-def _accum_target(t, shape):
-    """`.grad` of leaf `t` if the backward kernel may add into it, else None."""
-    if not _fused_grad_accumulation or t is None or not isinstance(t, torch.Tensor):
+def _accum_target(t, shape, mode):
+    """`.grad` of leaf `t` if the backward kernel may write into it, else None."""
+    if not mode or t is None or not isinstance(t, torch.Tensor):
         return None
     if not (t.is_leaf and t.requires_grad) or t.grad is None:
         return None
@@ -250,7 +264,7 @@ def _accum_target(t, shape):
 def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotations,
                    scale_modifier, cov3Ds_precomp, viewmatrix, projmatrix, tanfovx, tanfovy,
                    grad_color, grad_depth, grad_cov_quat, grad_cov_scale, grad_alpha, sh, campos,
-                   out_alpha, opacities_shape, debug, leaves=None):
+                   out_alpha, opacities_shape, debug, leaves=None, options=None):
     lib = _lib.load()
     device = means3D.device
     P, M = st.P, st.M
@@ -284,6 +298,7 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
 
         # outputs: a fresh tensor, or (fused accumulation) the leaf's existing .grad, added to in place
         leaves = leaves or {}
+        acc_mode = options.fused_grad_accumulation if options is not None else False
         acc_mask = 0
         fused = {}
 
@@ -291,9 +306,10 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
             nonlocal acc_mask
             if not wanted:
                 return None
-            tgt = _accum_target(leaves.get(name), shape) if M <= 16 or name != "sh" else None
+            tgt = _accum_target(leaves.get(name), shape, acc_mode) if M <= 16 or name != "sh" else None
             if tgt is not None:
-                acc_mask |= _ACC_BITS[name]
+                if acc_mode == "add":
+                    acc_mask |= _ACC_BITS[name]     # "assign": the kernel's plain overwrite, into .grad
                 fused[name] = True
                 return tgt
             return torch.empty(shape, **f32)
@@ -335,8 +351,8 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
         b.dL_dscales, b.dL_drotations = _ptr(dscales), _ptr(drots)
         b.dL_dcov3D = _ptr(dcov)
         b.accumulate_mask = acc_mask
-        if _densification_accumulators is not None:
-            sg, sd, sr = _densification_accumulators
+        if options is not None and options.densification_accumulators is not None:
+            sg, sd, sr = options.densification_accumulators
             if sg.numel() != P or sg.device != device:
                 raise RuntimeError("densification accumulators do not match this call (P or device)")
             b.stat_grad_accum, b.stat_denom, b.stat_max_radii = sg.data_ptr(), sd.data_ptr(), sr.data_ptr()
@@ -348,15 +364,17 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                        cov3Ds_precomp, raster_settings):
+                        cov3Ds_precomp, raster_settings, options=None):
+    """Same positional arguments as the reference's function (:21-42); `options` (a
+    RasterizerOptions, default none) carries the opt-in extensions of the calling rasterizer."""
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales,
-                                     rotations, cov3Ds_precomp, raster_settings)
+                                     rotations, cov3Ds_precomp, raster_settings, options)
 
 
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                cov3Ds_precomp, raster_settings):
+                cov3Ds_precomp, raster_settings, options=None):
         rs = raster_settings
         args = (rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier,
                 cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
@@ -380,8 +398,10 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh,
                               alpha)
         # the input objects themselves, to find leaves whose .grad the backward may add into
+        ctx.options = options if (options is not None and options.any) else None
         ctx.leaves = dict(means3D=means3D, sh=sh, colors=colors_precomp, opacity=opacities, scales=scales,
-                          rotations=rotations, cov3D=cov3Ds_precomp) if _fused_grad_accumulation else None
+                          rotations=rotations, cov3D=cov3Ds_precomp) \
+            if (ctx.options is not None and ctx.options.fused_grad_accumulation) else None
         ctx.mark_non_differentiable(radii)
         return color, depth, cov_quat, cov_scale, alpha, radii
 
@@ -397,17 +417,17 @@ class _RasterizeGaussians(torch.autograd.Function):
         if rs.debug:
             cpu_args = cpu_deep_copy_tuple(args[1:])
             try:
-                grads = _backward_impl(*args, leaves=ctx.leaves)
+                grads = _backward_impl(*args, leaves=ctx.leaves, options=ctx.options)
             except Exception as ex:
                 torch.save(cpu_args, "snapshot_bw.dump")
                 print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
                 raise ex
         else:
-            grads = _backward_impl(*args, leaves=ctx.leaves)
+            grads = _backward_impl(*args, leaves=ctx.leaves, options=ctx.options)
         (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales,
          grad_rotations, grad_cov3Ds_precomp) = grads
         return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities,
-                grad_scales, grad_rotations, grad_cov3Ds_precomp, None)
+                grad_scales, grad_rotations, grad_cov3Ds_precomp, None, None)
 
 
 class GaussianRasterizationSettings(NamedTuple):
@@ -426,9 +446,13 @@ class GaussianRasterizationSettings(NamedTuple):
 
 
 class GaussianRasterizer(nn.Module):
-    def __init__(self, raster_settings):
+    def __init__(self, raster_settings, *, fused_grad_accumulation=False, densification_accumulators=None):
+        """`GaussianRasterizer(raster_settings)` is the reference's constructor (:195-198).  The two
+        keyword-only arguments are this package's opt-in extensions for THIS instance; see
+        RasterizerOptions."""
         super().__init__()
         self.raster_settings = raster_settings
+        self.options = RasterizerOptions(fused_grad_accumulation, densification_accumulators)
 
     def markVisible(self, positions):
         """Boolean mask of the points in front of the near plane (view z > 0.2)."""
@@ -474,4 +498,5 @@ class GaussianRasterizer(nn.Module):
             cov3D_precomp = torch.Tensor([])
 
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales,
-                                   rotations, cov3D_precomp, raster_settings)
+                                   rotations, cov3D_precomp, raster_settings,
+                                   self.options if self.options.any else None)

@@ -28,35 +28,39 @@ def shard_views(n_views: int, rank: int, world: int) -> List[int]:
 
 
 class DensificationStats:
-    """xyz_gradient_accum, denom, max_radii2D of scene/gaussian_model.py:154-172."""
+    """xyz_gradient_accum, denom, max_radii2D of scene/gaussian_model.py:154-172.
+
+    The three tensors keep their identity for the lifetime of the object (reductions copy into them
+    in place), so a rasterizer that was handed them through `rasterizer_kwargs` keeps updating the
+    tensors this object reads."""
 
     def __init__(self, P: int, device):
         self.xyz_gradient_accum = torch.zeros((P, 1), device=device)
         self.denom = torch.zeros((P, 1), device=device)
         self.max_radii2D = torch.zeros((P,), device=device)
+        self.fused = False
 
-    def attach(self, rasterizer_module) -> bool:
-        """Let the backward kernel of `rasterizer_module` update these buffers itself
-        (vegs_b200's set_densification_accumulators); False if the module cannot (the reference)."""
-        reg = getattr(rasterizer_module, "set_densification_accumulators", None)
-        self.fused = reg is not None
+    def zero_(self) -> None:
+        self.xyz_gradient_accum.zero_(); self.denom.zero_(); self.max_radii2D.zero_()
+
+    def rasterizer_kwargs(self, rasterizer_module) -> dict:
+        """Keyword arguments for `rasterizer_module.GaussianRasterizer(settings, **kwargs)` that let
+        the backward kernel of that instance update these buffers itself (vegs_b200's per-instance
+        `densification_accumulators`); {} for a module without the extension (the reference), in
+        which case `add_view` does the work.  Sets `self.fused` accordingly."""
+        self.fused = hasattr(rasterizer_module, "RasterizerOptions")
         if self.fused:
-            reg(self.xyz_gradient_accum, self.denom, self.max_radii2D)
-        return self.fused
-
-    def detach(self, rasterizer_module) -> None:
-        if getattr(self, "fused", False):
-            rasterizer_module.set_densification_accumulators()
-            self.fused = False
+            return dict(densification_accumulators=(self.xyz_gradient_accum, self.denom, self.max_radii2D))
+        return {}
 
     def add_view(self, viewspace_grad: torch.Tensor, radii: torch.Tensor) -> None:
         """train.py:300-301 + add_densification_stats for one rendered view (no-op when the
-        backward kernel already did it, see attach)."""
-        if getattr(self, "fused", False):
+        backward kernel already did it, see rasterizer_kwargs).  In place."""
+        if self.fused:
             return
         vis = radii > 0
-        self.max_radii2D = torch.where(vis, torch.maximum(self.max_radii2D, radii.to(self.max_radii2D.dtype)),
-                                       self.max_radii2D)
+        self.max_radii2D.copy_(torch.where(vis, torch.maximum(self.max_radii2D, radii.to(self.max_radii2D.dtype)),
+                                           self.max_radii2D))
         norm = torch.norm(viewspace_grad[:, :2], dim=-1, keepdim=True)
         self.xyz_gradient_accum += torch.where(vis.unsqueeze(1), norm, torch.zeros_like(norm))
         self.denom += vis.unsqueeze(1).to(self.denom.dtype)
@@ -67,38 +71,141 @@ def flat_size(params: Dict[str, torch.Tensor]) -> int:
     return sum(params[k].numel() for k in PARAM_ORDER) + 2 * P
 
 
-def pack(params: Dict[str, torch.Tensor], stats: DensificationStats, out: torch.Tensor = None) -> torch.Tensor:
-    """Gradients of the five parameter tensors + the two additive statistics as one flat buffer."""
-    parts = []
+def _layout(params: Dict[str, torch.Tensor]):
+    """[(name, offset, numel)] of the flat buffer: the five gradients, then the two additive statistics."""
+    P = params["means3D"].shape[0]
+    out, off = [], 0
     for k in PARAM_ORDER:
-        g = params[k].grad
-        parts.append((g if g is not None else torch.zeros_like(params[k])).reshape(-1))
-    parts += [stats.xyz_gradient_accum.reshape(-1), stats.denom.reshape(-1)]
+        out.append((k, off, params[k].numel())); off += params[k].numel()
+    out.append(("xyz_gradient_accum", off, P)); off += P
+    out.append(("denom", off, P)); off += P
+    return out, off
+
+
+def pack(params: Dict[str, torch.Tensor], stats: DensificationStats, out: torch.Tensor = None) -> torch.Tensor:
+    """Gradients of the five parameter tensors + the two additive statistics as one flat buffer.
+    Parts that already ARE the matching slice of `out` (a `.grad` bound by `unpack` /
+    `FlatGradBuffer.bind` and accumulated into in place) are left where they are."""
+    layout, total = _layout(params)
     if out is None:
-        return torch.cat(parts)
-    torch.cat(parts, out=out)
+        out = torch.empty(total, dtype=torch.float32, device=params["means3D"].device)
+    assert out.numel() == total and out.is_contiguous()
+    for name, off, n in layout:
+        if name in params:
+            g = params[name].grad
+        else:
+            g = getattr(stats, name)
+        dst = out[off:off + n]
+        if g is None:
+            dst.zero_()
+        elif g.is_contiguous() and g.data_ptr() == dst.data_ptr():
+            continue
+        else:
+            dst.copy_(g.reshape(-1))
     return out
 
 
 def unpack(flat: torch.Tensor, params: Dict[str, torch.Tensor], stats: DensificationStats) -> None:
-    """Hand the reduced values back as views of the flat buffer (no copy)."""
-    off = 0
-    for k in PARAM_ORDER:
-        n = params[k].numel()
-        params[k].grad = flat[off:off + n].view_as(params[k])
-        off += n
-    P = params["means3D"].shape[0]
-    stats.xyz_gradient_accum = flat[off:off + P].view(P, 1); off += P
-    stats.denom = flat[off:off + P].view(P, 1)
+    """Hand the reduced gradients back as views of the flat buffer (no copy) and copy the reduced
+    statistics into the stats tensors IN PLACE (they keep their identity: a rasterizer instance that
+    was handed them keeps updating the tensors this object reads)."""
+    layout, _ = _layout(params)
+    for name, off, n in layout:
+        if name in params:
+            params[name].grad = flat[off:off + n].view_as(params[name])
+        else:
+            t = getattr(stats, name)
+            src = flat[off:off + n].view_as(t)
+            if t.data_ptr() != src.data_ptr():
+                t.copy_(src)
 
 
 def allreduce_step(params: Dict[str, torch.Tensor], stats: DensificationStats, group=None,
-                   flat: torch.Tensor = None) -> torch.Tensor:
+                   flat: torch.Tensor = None, accumulate_into: DensificationStats = None) -> torch.Tensor:
     """One SUM all-reduce of the flat buffer and one MAX all-reduce of max_radii2D.  Returns the
-    flat buffer (so the caller can reuse it next step)."""
+    flat buffer (so the caller can reuse it next step).
+
+    `stats` must hold THIS STEP's contribution only (fresh or zeroed at the start of the step): the
+    SUM over ranks of a running accumulator would count the earlier steps world-size times.  Pass
+    the running accumulator as `accumulate_into` to have the reduced step added to it."""
     flat = pack(params, stats, flat)
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
         dist.all_reduce(stats.max_radii2D, op=dist.ReduceOp.MAX, group=group)
     unpack(flat, params, stats)
+    if accumulate_into is not None:
+        accumulate_into.xyz_gradient_accum += stats.xyz_gradient_accum
+        accumulate_into.denom += stats.denom
+        torch.maximum(accumulate_into.max_radii2D, stats.max_radii2D, out=accumulate_into.max_radii2D)
     return flat
+
+
+class FlatGradBuffer:
+    """The view-parallel step without a pack copy: ONE persistent fp32 buffer whose slices ARE the
+    parameters' `.grad` tensors and the step's two additive statistics, so the backward kernel's
+    fused accumulation (GaussianRasterizer(..., fused_grad_accumulation=..., densification_accumulators=...))
+    writes straight into what `all_reduce` sends.  Layout = `pack`'s.
+
+        buf = FlatGradBuffer(params)
+        per step:  buf.begin_step()                      # binds .grad, clears the statistics
+                   for i, view in enumerate(my_views):
+                       rast = GaussianRasterizer(settings, **buf.rasterizer_kwargs(module, first=(i == 0)))
+                       ... forward, loss.backward() ...  # view 0 assigns, later views add
+                       buf.step_stats.add_view(means2D.grad, radii)   # no-op when fused
+                   buf.allreduce(accumulate_into=running_stats)
+    """
+
+    def __init__(self, params: Dict[str, torch.Tensor]):
+        layout, total = _layout(params)
+        dev = params["means3D"].device
+        P = params["means3D"].shape[0]
+        self.params = params
+        self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.grad_views = {}
+        self.step_stats = DensificationStats.__new__(DensificationStats)
+        for name, off, n in layout:
+            v = self.flat[off:off + n]
+            if name in params:
+                self.grad_views[name] = v.view_as(params[name])
+            else:
+                setattr(self.step_stats, name, v.view(P, 1))
+        self.step_stats.max_radii2D = torch.zeros((P,), device=dev)
+        self.step_stats.fused = False
+        self._stat_off = layout[-2][1]
+        self._dirty = True        # gradient slices hold stale values until the first view assigns
+
+    def begin_step(self) -> None:
+        """Bind every parameter's `.grad` to its slice and clear the step's statistics.  The gradient
+        slices are NOT cleared here when the first view is rendered with `first=True` (the kernel
+        overwrites them); call `zero_grads()` for a path that only ever adds."""
+        for k, v in self.grad_views.items():
+            self.params[k].grad = v
+        self.flat[self._stat_off:].zero_()
+        self.step_stats.max_radii2D.zero_()
+        self._dirty = True
+
+    def zero_grads(self) -> None:
+        self.flat[:self._stat_off].zero_()
+        self._dirty = False
+
+    def rasterizer_kwargs(self, rasterizer_module, first: bool) -> dict:
+        """Constructor keyword arguments for the rasterizer of one view of the step ({} for a module
+        without the extensions, e.g. the reference: then autograd adds into the bound `.grad` views,
+        which needs `zero_grads()` first)."""
+        kw = self.step_stats.rasterizer_kwargs(rasterizer_module)
+        if self.step_stats.fused:
+            kw["fused_grad_accumulation"] = "assign" if (first and self._dirty) else "add"
+            self._dirty = False
+        elif self._dirty:
+            self.zero_grads()
+        return kw
+
+    def allreduce(self, group=None, accumulate_into: DensificationStats = None) -> None:
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
+            dist.all_reduce(self.step_stats.max_radii2D, op=dist.ReduceOp.MAX, group=group)
+        if accumulate_into is not None:
+            s = self.step_stats
+            accumulate_into.xyz_gradient_accum += s.xyz_gradient_accum
+            accumulate_into.denom += s.denom
+            torch.maximum(accumulate_into.max_radii2D, s.max_radii2D, out=accumulate_into.max_radii2D)
