@@ -1,0 +1,65 @@
+#!/bin/bash
+# Round-2 GPU-box stages.  Usage: gpurun --timeout N -- 'bash scripts/gpu_r2.sh <tag> stage ...'
+# Every stage runs in its own process (a CUDA fault in one must not hide the others) under its own
+# timeout; everything lands under gpurun_out/<tag>_*.
+set -u
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+tag=$1; shift
+S=gpurun_out/${tag}_summary.txt
+: > $S
+run_pytest() {  # name, -k expression, timeout
+  timeout $3 python -m pytest tests -m gpu -q -x -k "$2" -p no:cacheprovider > "gpurun_out/${tag}_pytest_$1.log" 2>&1
+  echo "pytest[$1] rc=$? $(tail -1 gpurun_out/${tag}_pytest_$1.log)" | tee -a $S
+}
+for s in "$@"; do
+  case $s in
+    smoke)
+      timeout 240 python __graft_entry__.py smoke > gpurun_out/${tag}_smoke.log 2>&1; echo "smoke rc=$?" | tee -a $S ;;
+    tests)
+      run_pytest base "not full and not noalloc and not config and not callers and not giant" 600
+      run_pytest noalloc "noalloc" 240 ;;
+    tests_full)
+      run_pytest config2 "config2" 600
+      run_pytest config3 "config3" 900
+      run_pytest config5 "config5" 900
+      run_pytest config4 "config4" 300
+      run_pytest callers "callers or giant" 600 ;;
+    tests_all)   # what the driver runs
+      timeout 2400 python -m pytest tests -m gpu -q -x -p no:cacheprovider > gpurun_out/${tag}_pytest_all.log 2>&1
+      echo "pytest[all] rc=$? $(tail -1 gpurun_out/${tag}_pytest_all.log)" | tee -a $S ;;
+    bench)
+      timeout 900 python bench.py --steps ${STEPS:-10} --warmup 3 > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?" | tee -a $S ;;
+    bench_ref)
+      timeout 900 python bench.py --impl reference --steps ${STEPS:-10} --warmup 3 > gpurun_out/${tag}_bench_ref.json 2> gpurun_out/${tag}_bench_ref.err; echo "bench_ref rc=$?" | tee -a $S
+      # proof that the reference process never maps the repo's library
+      grep -c libvegs_b200 gpurun_out/${tag}_bench_ref.err >> $S ;;
+    bench_quick)
+      timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench_quick rc=$?" | tee -a $S ;;
+    configs)
+      timeout 1200 python scripts/bench_configs.py > gpurun_out/${tag}_configs.json 2> gpurun_out/${tag}_configs.err; echo "configs rc=$?" | tee -a $S ;;
+    ncu_launches)
+      CMD="python bench.py --P 6000000 --views 2 --steps 1 --warmup 3 --no-cpu-baseline --no-fused-leg"
+      timeout 600 $CMD > gpurun_out/${tag}_ncu_plain.log 2>&1 &&
+      timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 300 -c 400 --csv --log-file gpurun_out/${tag}_launches.csv $CMD > gpurun_out/${tag}_ncu_launches.log 2>&1
+      echo "ncu launches rc=$?" | tee -a $S
+      python scripts/ncu_launch_table.py gpurun_out/${tag}_launches.csv gpurun_out/${tag}_ncu_launches.md "ncu launch list ($tag): \`ncu --metrics gpu__time_duration.sum --clock-control none -s 300 -c 400 $CMD\`" > /dev/null 2>&1 ;;
+    ncu_launches_ref)
+      CMD="python bench.py --impl reference --P 6000000 --views 2 --steps 1 --warmup 3"
+      timeout 600 $CMD > gpurun_out/${tag}_ncu_plain_ref.log 2>&1 &&
+      timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 200 -c 400 --csv --log-file gpurun_out/${tag}_launches_ref.csv $CMD > gpurun_out/${tag}_ncu_launches_ref.log 2>&1
+      echo "ncu launches ref rc=$?" | tee -a $S
+      python scripts/ncu_launch_table.py gpurun_out/${tag}_launches_ref.csv gpurun_out/${tag}_ncu_launches_ref.md "ncu launch list of the REFERENCE's CUDA extension ($tag): \`ncu --metrics gpu__time_duration.sum --clock-control none -s 200 -c 400 $CMD\`" > /dev/null 2>&1 ;;
+    ncu_all)
+      # one --set full capture of every kernel of the second pass of scripts/profile_all.py
+      CMD="python scripts/profile_all.py"
+      timeout 600 $CMD > gpurun_out/${tag}_profile_all.log 2>&1 &&
+      timeout 1500 ncu --set full --clock-control none -k regex:vegs -s ${NCU_SKIP:-48} -c ${NCU_COUNT:-48} -f -o gpurun_out/${tag}_prof_all $CMD > gpurun_out/${tag}_ncu_all.log 2>&1
+      echo "ncu all rc=$?" | tee -a $S
+      python scripts/ncu_table.py gpurun_out/${tag}_prof_all.ncu-rep gpurun_out/${tag}_ncu_all.md "ncu --set full --clock-control none, every kernel of one pass over the 6 M scene ($tag): \`$CMD\`" > /dev/null 2>&1
+      ls -la gpurun_out/${tag}_prof_all.ncu-rep >> $S
+      # keep the merge under the 64 MiB limit
+      if [ $(stat -c %s gpurun_out/${tag}_prof_all.ncu-rep 2>/dev/null || echo 0) -gt 40000000 ]; then rm -f gpurun_out/${tag}_prof_all.ncu-rep; fi ;;
+  esac
+done
+cat $S
