@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define VEGS_ABI_VERSION 3
+#define VEGS_ABI_VERSION 4
 
 enum {
     VEGS_OK = 0,
@@ -86,7 +86,19 @@ typedef struct VegsForwardArgs {
      * [0] = num_rendered, [1] = number of emission work items (informational).  The library never
      * reads them back: num_rendered travels through the argument of vegs_forward_render. */
     int32_t* num_rendered_host;
+    /* Fused activations and fused concatenation (no reference counterpart; the reference's caller
+     * applies them in separate passes over all Gaussians, scene/gaussian_model.py:100-120).
+     * activations: VEGS_ACT_* bits - the matching input array holds the RAW parameter and the
+     * kernel applies sigmoid (opacities), exp (scales), x / max(|x|, 1e-12) (rotations) itself.
+     * shs_rest: when not NULL, `shs` is f_dc [P,1,3] and shs_rest is f_rest [P,M-1,3]; the kernel
+     * reads them as the concatenated [P,M,3] row.  Both default to 0 / NULL = the reference's inputs. */
+    uint32_t activations;
+    const float* shs_rest;
 } VegsForwardArgs;
+
+#define VEGS_ACT_OPACITY_SIGMOID 1u
+#define VEGS_ACT_SCALE_EXP       2u
+#define VEGS_ACT_ROT_NORMALIZE   4u
 
 /*
  * Backward arguments.  Replaces the 28 positional arguments of `_C.rasterize_gaussians_backward`
@@ -148,6 +160,15 @@ typedef struct VegsBackwardArgs {
     float* stat_grad_accum;
     float* stat_denom;
     float* stat_max_radii;
+    /* Backward of the fused activations / concatenation of the matching forward (see
+     * VegsForwardArgs).  With a VEGS_ACT_* bit set the matching input is the RAW parameter and the
+     * returned gradient is with respect to it; `opacities` (raw, [P]) is only read for
+     * VEGS_ACT_OPACITY_SIGMOID.  With shs_rest given, dL_dsh receives the f_dc part [P,1,3] and
+     * dL_dsh_rest the f_rest part [P,M-1,3] (VEGS_ACC_SH applies to both). */
+    uint32_t activations;
+    const float* opacities;
+    const float* shs_rest;
+    float* dL_dsh_rest;
 } VegsBackwardArgs;
 
 #define VEGS_ACC_MEANS3D   1u

@@ -176,6 +176,92 @@ def test_fused_densification_statistics_equal_the_separate_passes():
                     "xyz_gradient_accum", rtol=1e-6)
 
 
+def _raw_model_run(scene, cams, raw: bool, fused=False, deg=3):
+    """Two views accumulated from VEGS's raw parameters: through the model's getters + the drop-in
+    forward (raw=False), or through forward_raw with the activations fused into the kernels."""
+    import vegs_b200.diff_gaussian_rasterization as dgr
+    import vegs_caller as vc
+    dev = torch.device("cuda")
+    pc = vc.StubGaussianModel(scene, sh_degree=deg)
+    outs = []
+    for i, cam in enumerate(cams):
+        rs = dgr.GaussianRasterizationSettings(
+            image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+            bg=torch.tensor([0.2, 0.1, 0.4], device=dev), scale_modifier=1.0, viewmatrix=cam.viewmatrix.to(dev),
+            projmatrix=cam.projmatrix.to(dev), sh_degree=deg, campos=cam.campos.to(dev), prefiltered=False, debug=False)
+        rast = dgr.GaussianRasterizer(rs, fused_grad_accumulation=bool(fused and i > 0))
+        m2 = torch.zeros_like(pc.get_xyz, requires_grad=True)
+        if raw:
+            out = rast.forward_raw(pc._xyz, m2, pc._opacity, pc._features_dc, pc._features_rest, pc._scaling,
+                                   pc._rotation)
+        else:
+            out = rast(means3D=pc.get_xyz, means2D=m2, opacities=pc.get_opacity, shs=pc.get_features,
+                       scales=pc.get_scaling, rotations=pc.get_rotation)
+        cot = util.np_cotangents(cam.W, cam.H, seed=20 + i)
+        loss = sum((o * torch.from_numpy(cot[k]).to(dev)).sum()
+                   for o, k in zip(out[:5], ("color", "depth", "cov_quat", "cov_scale", "alpha")))
+        loss.backward()
+        outs.append([o.detach().cpu().numpy() for o in out] + [m2.grad.cpu().numpy()])
+    return {k: v.grad.cpu().numpy() for k, v in pc.leaves().items()}, outs
+
+
+@pytest.mark.parametrize("P,deg", [(60000, 3), (5003, 2)])
+def test_forward_raw_equals_activations_plus_dropin(P, deg):
+    """forward_raw (sigmoid / exp / normalize / cat and their Jacobians inside the per-Gaussian
+    kernels) against torch's own activation kernels + autograd around the drop-in forward
+    (scene/gaussian_model.py:100-120).  The activations are recomputed with the same float
+    operations, but torch's norm reduction may round differently in the last bit, which can move a
+    radius or a 1/255 decision at isolated Gaussians: radii and images allow a few outliers."""
+    scene = util.scene_with_specials(P)
+    cams = [synth.make_camera(k, scale=0.25) for k in range(2)]
+    g_ref, o_ref = _raw_model_run(scene, cams, raw=False, deg=deg)
+    g_raw, o_raw = _raw_model_run(scene, cams, raw=True, deg=deg)
+    g_fused, _ = _raw_model_run(scene, cams, raw=True, fused=True, deg=deg)
+    for a, b in zip(o_raw, o_ref):
+        assert (a[5] != b[5]).mean() < 1e-4, "radii"
+        for k in range(5):
+            d = np.abs(a[k] - b[k])
+            assert (d > 1e-5).mean() < 1e-4 and np.median(d) <= 1e-6, (k, float(d.max()))
+        util.grad_close(a[6], b[6], "viewspace gradient", rtol=2e-4)
+    for k in g_ref:
+        assert np.abs(g_ref[k]).max() > 0, k
+        util.grad_close(g_raw[k], g_ref[k], f"raw-parameter grad {k}", rtol=2e-4)
+        util.grad_close(g_fused[k], g_raw[k], f"raw-parameter grad {k}, fused accumulation", rtol=1e-5)
+
+
+def test_bulk_copy_paths_equal_the_load_paths():
+    """The asynchronous bulk-copy staging of the per-Gaussian kernels (bulk.cuh) and the 16-byte-load
+    fallback must give bit-identical results: strided / offset views force the fallback (unaligned
+    bases), a Gaussian count that is not a multiple of 32 exercises the partial last warp."""
+    import vegs_b200.diff_gaussian_rasterization as dgr
+    dev = torch.device("cuda")
+    scene = util.scene_with_specials(40001)
+    cam = synth.make_camera(1, scale=0.25)
+    cot = util.np_cotangents(cam.W, cam.H)
+    a = util.run_ours(scene, cam, cot=cot, want_state=False)
+    # the same data at addresses that are only 4-byte aligned
+    P = scene["means3D"].shape[0]
+    shifted = {}
+    for k, v in scene.items():
+        flat = torch.zeros(v.numel() + 1, device=dev)
+        flat[1:] = v.to(dev).reshape(-1)
+        shifted[k] = flat[1:].view(v.shape).requires_grad_(True)
+        assert shifted[k].data_ptr() % 16 != 0
+    rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, torch.zeros(3, device=dev), 1.0,
+                                           cam.viewmatrix.to(dev), cam.projmatrix.to(dev), 3, cam.campos.to(dev),
+                                           False, False)
+    m2 = torch.zeros((P, 3), device=dev, requires_grad=True)
+    out = dgr.GaussianRasterizer(rs)(means3D=shifted["means3D"], means2D=m2, opacities=shifted["opacities"],
+                                     shs=shifted["shs"], scales=shifted["scales"], rotations=shifted["rotations"])
+    c = {k: torch.from_numpy(v).to(dev) for k, v in cot.items()}
+    (sum((o * c[k]).sum() for o, k in zip(out[:5], ("color", "depth", "cov_quat", "cov_scale", "alpha")))).backward()
+    for k, o in zip(("color", "depth", "cov_quat", "cov_scale", "alpha", "radii"), out):
+        assert np.array_equal(o.detach().cpu().numpy(), a[k]), k
+    pairs = dict(means3D="means3D", sh="shs", opacities="opacities", scales="scales", rotations="rotations")
+    for gk, tk in pairs.items():
+        util.grad_close(shifted[tk].grad.cpu().numpy(), a["grads"][gk], f"grad {gk} (fallback vs bulk)", rtol=1e-5)
+
+
 def test_modes_colors_precomp_and_cov3d_precomp_against_oracle():
     scene = util.scene_with_specials(4000)
     cam = synth.make_camera(0, scale=0.125)

@@ -28,6 +28,7 @@ class VegsForwardArgs(C.Structure):
         ("geom", C.c_void_p), ("img", C.c_void_p), ("binning", C.c_void_p),
         ("scratch", C.c_void_p), ("bin_scratch", C.c_void_p),
         ("num_rendered_host", C.c_void_p),
+        ("activations", C.c_uint32), ("shs_rest", C.c_void_p),
     ]
 
 
@@ -52,6 +53,8 @@ class VegsBackwardArgs(C.Structure):
         ("dL_drotations", C.c_void_p), ("dL_dcov3D", C.c_void_p),
         ("accumulate_mask", C.c_uint32),
         ("stat_grad_accum", C.c_void_p), ("stat_denom", C.c_void_p), ("stat_max_radii", C.c_void_p),
+        ("activations", C.c_uint32), ("opacities", C.c_void_p), ("shs_rest", C.c_void_p),
+        ("dL_dsh_rest", C.c_void_p),
     ]
 
 
@@ -99,7 +102,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if a declared symbol is not exported
         fn.restype = res
         fn.argtypes = args
-    if lib.vegs_abi_version() != 3:
+    if lib.vegs_abi_version() != 4:
         raise ImportError("libvegs_b200.so ABI version mismatch; rebuild it")
     _lib = lib
     return lib

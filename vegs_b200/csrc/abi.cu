@@ -6,6 +6,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -83,6 +84,10 @@ extern "C" void vegs_profile_enable(int32_t on) { g_prof_on.store(on != 0); }
 static std::atomic<bool> g_unit_masks{true};
 extern "C" void vegs_debug_unit_masks(int32_t on) { g_unit_masks.store(on != 0); }
 namespace vegs {
+bool sh_bulk_disabled() {
+    static const bool off = [] { const char* e = getenv("VEGS_SH_BULK"); return e != nullptr && e[0] == '0'; }();
+    return off;
+}
 bool list_has_unit_masks(int P) { return g_unit_masks.load() && P <= (int)kListIdMask; }
 }
 

@@ -54,6 +54,7 @@ constexpr int kRectStride = 2;    // {tile rect, pixel box} per Gaussian, in uin
 // the tile's compositing units the Gaussian's conservative box reaches (written by the emission
 // kernel), so a unit rejects an entry from the list word alone.
 constexpr uint32_t kListIdMask = 0x00ffffffu;
+bool sh_bulk_disabled();             // abi.cu: VEGS_SH_BULK=0 in the environment selects the 16-byte-load paths (A/B measurements)
 bool list_has_unit_masks(int P);   // abi.cu: P < 2^24 unless disabled through vegs_debug_unit_masks
 constexpr int kEmitChunk = 1024;  // depth-sorted Gaussians per emission block
 constexpr uint32_t kEmitPartInstances = 8192;   // instances emitted by one CTA

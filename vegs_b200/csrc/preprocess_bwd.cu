@@ -7,200 +7,207 @@
 // What differs from the reference:
 //   * one kernel instead of two, and no zero-fill passes: every element of every returned gradient
 //     tensor is written exactly once here (zeros for Gaussians with radii == 0);
-//   * the blend-stage gradients arrive as one packed 48-byte record per Gaussian (three 16-byte
-//     loads) instead of five separate arrays;
-//   * SH coefficients are read and dL/dSH written warp-cooperatively with coalesced 16-byte
-//     accesses through padded shared memory (the reference does 48 strided scalar loads and 48
-//     strided scalar stores per thread);
+//   * every warp works on its own 32 consecutive Gaussians and moves their data with asynchronous
+//     bulk copies (bulk.cuh, the 1-D form of TMA) tracked by mbarriers: the contiguous input blocks
+//     (means, scales, rotations, radii, the packed 48-byte blend-stage accumulators) by a handful
+//     of copies issued by one lane, the 192-byte SH row of every visible Gaussian by one copy per
+//     row; on the way out the warp's gradient blocks are staged in shared memory and leave as bulk
+//     stores - or, for fused gradient accumulation, as bulk REDUCTIONS (cp.reduce.async.bulk
+//     .add.f32) that do the read-modify-write in L2, so the old .grad never travels to the SM;
+//   * the SH backward runs in a streaming per-coefficient form (sh_bwd.cuh), four coefficients =
+//     three 16-byte shared-memory accesses at a time;
 //   * the 3D covariance is recomputed from scale/rotation instead of being stored by the forward
-//     and re-read (saves 48 B per Gaussian of traffic).
+//     and re-read (saves 48 B per Gaussian of traffic);
+//   * optionally the Jacobians of the caller's activations (sigmoid / exp / normalize, split
+//     f_dc / f_rest) are applied here (VegsBackwardArgs.activations, no reference counterpart).
 // The gradient formulas are the reference's; dL/dscale and dL/drot do not receive the quaternion /
-// scale-map cotangents and the quaternion gradient has no normalisation Jacobian
-// (backward.cu:340-341).
+// scale-map cotangents unless the opt-in live-map gradient is requested and the
+// quaternion gradient has no normalisation Jacobian of its own (backward.cu:340-341).
 // Roofline: HBM.  Algorithmic bytes per Gaussian: reads 4 (radius) for all, +12+28+48+1+12*M for
 // visible; writes 12+12+4+12+16+12*M (+12 colours, +24 cov3D when requested) for all.
 #include "common.cuh"
 #include "gsmath.cuh"
+#include "bulk.cuh"
+#include "pwide.cuh"
+#include "sh_bwd.cuh"
 
 namespace vegs {
 
 namespace {
 
-constexpr int kPbThreads = 128;
-constexpr int kPbWarps = kPbThreads / 32;
-constexpr int kMaxStageCoeffs = 16;
-constexpr int kShStrideMax = 3 * kMaxStageCoeffs + 1;
-
 struct PbParams {
     int P, D, M, W, H;
     const float* means;
     const int* radii;
-    const float* shs;
+    const float* shs;            // [P,M,3], or f_dc when shs_rest is given
+    const float* shs_rest;
     const uint8_t* clamped;
     const float* scales;
     const float* rots;
+    const float* opac;           // raw opacities, only read when VEGS_ACT_OPACITY_SIGMOID
     const float* cov3D_precomp;
     float mod, tan_fovx, tan_fovy, focal_x, focal_y;
     const float* view;
     const float* proj;
     const float* campos;
     const float4* acc;
+    const float4* map_acc;       // [2P] live quaternion / scale-map gradients (opt-in) or NULL
     float* dL_dmeans3D;
     float* dL_dmeans2D;
     float* dL_dsh;
+    float* dL_dsh_rest;
     float* dL_dcolors;
     float* dL_dopacity;
     float* dL_dscales;
     float* dL_drots;
     float* dL_dcov3D;
     bool shs_vec_ok, dsh_vec_ok, rots_vec_ok;
+    bool in_bulk_ok;             // means, scales, rotations, radii, acc 16-byte aligned
+    bool out_bulk_ok;            // the dense outputs that are present are 16-byte aligned
     uint32_t accum;      // VEGS_ACC_* bits: those outputs receive old + gradient
+    uint32_t act;        // VEGS_ACT_* bits
     float *stat_grad, *stat_denom, *stat_maxr;   // fused densification statistics, or NULL
 };
 
-__device__ __forceinline__ float4 ldg_stream4(const float4* p) {
-    float4 v;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
-                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                 : "l"(p));
-    return v;
-}
+// Dense output staging of one warp (overlays the input blocks once they are in registers).
+constexpr int kOutMeans3D = 0, kOutMeans2D = 96, kOutScales = 192, kOutRots = 288, kOutOpac = 416, kOutFloats = 448;
 
-// SH backward for one Gaussian.  `row` holds its coefficients [k][rgb] on entry (first
-// (deg+1)^2 valid) and receives dL/dSH (all M coefficients; unused ones zero) on exit.
-// Returns dL/d(mean) through the view direction.  Reference: backward.cu:20-139.
-__device__ __forceinline__ float3 sh_backward(float* row, int deg, int M, float dox, float doy,
-                                              float doz, const float dRGB[3]) {
-    const float len = sqrtf(dox * dox + doy * doy + doz * doz);
-    const float x = dox / len, y = doy / len, z = doz / len;
-    float ddx[3] = {0.f, 0.f, 0.f}, ddy[3] = {0.f, 0.f, 0.f}, ddz[3] = {0.f, 0.f, 0.f};
+struct __align__(16) BwdWarpStage {
+    float sh[kShWarpFloats];              // SH rows in, dL/dSH rows out
+    float io[736];                        // inputs: means 96 | scales 96 | rots 128 | opac 32 | acc 384; then outputs
+    int radii[32];
+};
+constexpr int kIoAcc = kInWarpFloats;    // 352: the 32 x 12 accumulator floats follow the four input blocks
 
-    auto put = [&](int k, float w) {
+// One group of four SH coefficients of one lane's row: load, backward, store.
+//   kShBulkRows  row = the lane's 52-float-stride row, three 16-byte accesses
+//   kShSplit     dc = coefficient 0, row[3k + ch] = coefficient k >= 1 (row = rest - 3), scalar accesses
+//   kShLdg       row[3k + ch], dc = row, scalar accesses
+template <int kSh, int G>
+__device__ __forceinline__ void sh_bwd_row_group(ShBwdState& s, float* row, float* dc, int M, bool zero_only) {
+    if (4 * G >= M) return;
+    float g[12];
+    if (kSh == kShBulkRows) {
+        float4* r4 = reinterpret_cast<float4*>(row) + 3 * G;
+        if (!zero_only) {
+            const float4 a = r4[0], b = r4[1], c = r4[2];
+            g[0] = a.x; g[1] = a.y; g[2] = a.z; g[3] = a.w; g[4] = b.x; g[5] = b.y; g[6] = b.z; g[7] = b.w;
+            g[8] = c.x; g[9] = c.y; g[10] = c.z; g[11] = c.w;
+            sh_bwd_group<G>(s, g);
+        } else {
 #pragma unroll
-        for (int ch = 0; ch < 3; ch++) row[3 * k + ch] = w * dRGB[ch];
-    };
-    put(0, kSH_C0);
-    int used = 1;
-    if (deg > 0) {
-        float sh1[3], sh2[3], sh3[3];
-#pragma unroll
-        for (int ch = 0; ch < 3; ch++) { sh1[ch] = row[3 + ch]; sh2[ch] = row[6 + ch]; sh3[ch] = row[9 + ch]; }
-        put(1, -kSH_C1 * y);
-        put(2, kSH_C1 * z);
-        put(3, -kSH_C1 * x);
-#pragma unroll
-        for (int ch = 0; ch < 3; ch++) {
-            ddx[ch] = -kSH_C1 * sh3[ch];
-            ddy[ch] = -kSH_C1 * sh1[ch];
-            ddz[ch] = kSH_C1 * sh2[ch];
+            for (int i = 0; i < 12; i++) g[i] = 0.f;
         }
-        used = 4;
-        if (deg > 1) {
-            const float xx = x * x, yy = y * y, zz = z * z;
-            const float xy = x * y, yz = y * z, xz = x * z;
-            float s4[3], s5[3], s6[3], s7[3], s8[3];
+        r4[0] = make_float4(g[0], g[1], g[2], g[3]);
+        r4[1] = make_float4(g[4], g[5], g[6], g[7]);
+        r4[2] = make_float4(g[8], g[9], g[10], g[11]);
+    } else {
 #pragma unroll
-            for (int ch = 0; ch < 3; ch++) {
-                s4[ch] = row[12 + ch]; s5[ch] = row[15 + ch]; s6[ch] = row[18 + ch];
-                s7[ch] = row[21 + ch]; s8[ch] = row[24 + ch];
-            }
-            put(4, kSH_C2[0] * xy);
-            put(5, kSH_C2[1] * yz);
-            put(6, kSH_C2[2] * (2.f * zz - xx - yy));
-            put(7, kSH_C2[3] * xz);
-            put(8, kSH_C2[4] * (xx - yy));
+        for (int j = 0; j < 4; j++) {
+            const int k = 4 * G + j;
+            float* ptr = (k == 0) ? dc : row + 3 * k;
 #pragma unroll
-            for (int ch = 0; ch < 3; ch++) {
-                ddx[ch] += kSH_C2[0] * y * s4[ch] + kSH_C2[2] * 2.f * -x * s6[ch] +
-                           kSH_C2[3] * z * s7[ch] + kSH_C2[4] * 2.f * x * s8[ch];
-                ddy[ch] += kSH_C2[0] * x * s4[ch] + kSH_C2[1] * z * s5[ch] +
-                           kSH_C2[2] * 2.f * -y * s6[ch] + kSH_C2[4] * 2.f * -y * s8[ch];
-                ddz[ch] += kSH_C2[1] * y * s5[ch] + kSH_C2[2] * 2.f * 2.f * z * s6[ch] +
-                           kSH_C2[3] * x * s7[ch];
-            }
-            used = 9;
-            if (deg > 2) {
-                float s9[3], s10[3], s11[3], s12[3], s13[3], s14[3], s15[3];
+            for (int ch = 0; ch < 3; ch++) g[3 * j + ch] = (!zero_only && k < M) ? ptr[ch] : 0.f;
+        }
+        if (!zero_only) sh_bwd_group<G>(s, g);
 #pragma unroll
-                for (int ch = 0; ch < 3; ch++) {
-                    s9[ch] = row[27 + ch]; s10[ch] = row[30 + ch]; s11[ch] = row[33 + ch];
-                    s12[ch] = row[36 + ch]; s13[ch] = row[39 + ch]; s14[ch] = row[42 + ch];
-                    s15[ch] = row[45 + ch];
-                }
-                put(9, kSH_C3[0] * y * (3.f * xx - yy));
-                put(10, kSH_C3[1] * xy * z);
-                put(11, kSH_C3[2] * y * (4.f * zz - xx - yy));
-                put(12, kSH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy));
-                put(13, kSH_C3[4] * x * (4.f * zz - xx - yy));
-                put(14, kSH_C3[5] * z * (xx - yy));
-                put(15, kSH_C3[6] * x * (xx - 3.f * yy));
+        for (int j = 0; j < 4; j++) {
+            const int k = 4 * G + j;
+            if (k < M) {
+                float* ptr = (k == 0) ? dc : row + 3 * k;
 #pragma unroll
-                for (int ch = 0; ch < 3; ch++) {
-                    ddx[ch] += kSH_C3[0] * s9[ch] * 3.f * 2.f * xy + kSH_C3[1] * s10[ch] * yz +
-                               kSH_C3[2] * s11[ch] * -2.f * xy + kSH_C3[3] * s12[ch] * -3.f * 2.f * xz +
-                               kSH_C3[4] * s13[ch] * (-3.f * xx + 4.f * zz - yy) +
-                               kSH_C3[5] * s14[ch] * 2.f * xz + kSH_C3[6] * s15[ch] * 3.f * (xx - yy);
-                    ddy[ch] += kSH_C3[0] * s9[ch] * 3.f * (xx - yy) + kSH_C3[1] * s10[ch] * xz +
-                               kSH_C3[2] * s11[ch] * (-3.f * yy + 4.f * zz - xx) +
-                               kSH_C3[3] * s12[ch] * -3.f * 2.f * yz + kSH_C3[4] * s13[ch] * -2.f * xy +
-                               kSH_C3[5] * s14[ch] * -2.f * yz + kSH_C3[6] * s15[ch] * -3.f * 2.f * xy;
-                    ddz[ch] += kSH_C3[1] * s10[ch] * xy + kSH_C3[2] * s11[ch] * 4.f * 2.f * yz +
-                               kSH_C3[3] * s12[ch] * 3.f * (2.f * zz - xx - yy) +
-                               kSH_C3[4] * s13[ch] * 4.f * 2.f * xz + kSH_C3[5] * s14[ch] * (xx - yy);
-                }
-                used = 16;
+                for (int ch = 0; ch < 3; ch++) ptr[ch] = g[3 * j + ch];
             }
         }
     }
-    for (int k = 3 * used; k < 3 * M; k++) row[k] = 0.0f;
-
-    const float dLx = ddx[0] * dRGB[0] + ddx[1] * dRGB[1] + ddx[2] * dRGB[2];
-    const float dLy = ddy[0] * dRGB[0] + ddy[1] * dRGB[1] + ddy[2] * dRGB[2];
-    const float dLz = ddz[0] * dRGB[0] + ddz[1] * dRGB[1] + ddz[2] * dRGB[2];
-    // dnormvdv (auxiliary.h:107-117)
-    const float sum2 = dox * dox + doy * doy + doz * doz;
-    const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
-    float3 r;
-    r.x = ((+sum2 - dox * dox) * dLx - doy * dox * dLy - doz * dox * dLz) * invsum32;
-    r.y = (-dox * doy * dLx + (sum2 - doy * doy) * dLy - doz * doy * dLz) * invsum32;
-    r.z = (-dox * doz * dLx - doy * doz * dLy + (sum2 - doz * doz) * dLz) * invsum32;
-    return r;
 }
 
-// kM: SH coefficients per Gaussian when known at compile time (1, 4, 9, 16), 0 = read p.M.  The
-// staging loops divide element indices by the row length; with a constant that is a multiply.
-template <int kM>
-__global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbParams p) {
+// kM: SH coefficients per Gaussian when known at compile time (16), 0 = read p.M.
+// kSh: how the SH rows travel (pwide.cuh).
+template <int kM, int kSh>
+__global__ void __launch_bounds__(kPwThreads, 5) preprocess_bwd_kernel(const PbParams p) {
     const int M = kM ? kM : p.M;
-    __shared__ float s_sh[kPbWarps][32 * kShStrideMax];
+    __shared__ BwdWarpStage s_stage[kPwWarps];
+    __shared__ __align__(8) uint64_t s_bar[kPwWarps][2];     // [0] inputs, [1] SH rows
     __shared__ Camera cam;
     load_camera(cam, p.view, p.proj, p.campos);
 
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    const int idx = blockIdx.x * kPbThreads + threadIdx.x;
+    const int idx = blockIdx.x * kPwThreads + threadIdx.x;
     const int warp_base = idx - lane;
     const bool in_range = idx < p.P;
-    // Every per-Gaussian input is requested before the visibility test (nine in ten Gaussians are
-    // visible): the loads overlap instead of queueing behind the radius.
-    float in_m[3] = {0.f, 0.f, 0.f}, in_s[3] = {0.f, 0.f, 0.f};
-    float4 in_q = make_float4(1.f, 0.f, 0.f, 0.f);
+    const bool full = warp_base + 32 <= p.P;
+    BwdWarpStage& st = s_stage[warp];
+    uint64_t* bar_in = &s_bar[warp][0];
+    uint64_t* bar_sh = &s_bar[warp][1];
+    const bool have_sr = p.cov3D_precomp == nullptr;
+    const bool in_bulk = full && p.in_bulk_ok;
+    const bool out_bulk = full && p.out_bulk_ok;
+    const bool use_sh = p.shs != nullptr && p.dL_dsh != nullptr;
+    const bool staged_sh = use_sh && M <= kMaxStageCoeffs;
+    const bool sh_block_bulk = staged_sh && kSh == kShSplit && full && p.shs_vec_ok;   // whole-warp blocks in
+    const bool act_op = (p.act & VEGS_ACT_OPACITY_SIGMOID) != 0u;
+
+    if (lane == 0) {
+        mbar_init(bar_in, 1);
+        mbar_init(bar_sh, kSh == kShBulkRows ? 32 : 1);
+        mbar_init_fence();
+    }
+    __syncwarp();
+    if (lane == 0) {
+        if (in_bulk) {
+            issue_input_copies(st.io, bar_in, p.means, have_sr ? p.scales : nullptr, have_sr ? p.rots : nullptr,
+                               act_op ? p.opac : nullptr, warp_base, 128u + 1536u);
+            bulk_g2s(st.radii, p.radii + warp_base, 128u, bar_in);
+            bulk_g2s(st.io + kIoAcc, p.acc + 3 * (size_t)warp_base, 1536u, bar_in);
+        }
+        if (sh_block_bulk) {
+            const uint32_t rest_bytes = 32u * 12u * (uint32_t)(M - 1);
+            mbar_arrive_expect_tx(bar_sh, 384u + rest_bytes);
+            bulk_g2s(st.sh + 32 * 3 * (M - 1), p.shs + 3 * (size_t)warp_base, 384u, bar_sh);
+            if (rest_bytes) bulk_g2s(st.sh, p.shs_rest + (size_t)warp_base * 3 * (M - 1), rest_bytes, bar_sh);
+        }
+    }
+
+    // ---- inputs
+    LaneInputs li = LaneInputs{0.f, 0.f, 0.f, 0.f, 0.f, 0.f, make_float4(1.f, 0.f, 0.f, 0.f), 0.f};
     float4 in_a0 = make_float4(0.f, 0.f, 0.f, 0.f), in_a1 = in_a0, in_a2 = in_a0;
     int in_radius = 0;
-    if (in_range) {
+    if (in_bulk) {
+        mbar_wait(bar_in, 0);
+        li = read_inputs_smem(st.io, lane, have_sr, act_op);
+        in_radius = st.radii[lane];
+        const float4* a4 = reinterpret_cast<const float4*>(st.io + kIoAcc) + 3 * lane;
+        in_a0 = a4[0]; in_a1 = a4[1]; in_a2 = a4[2];
+    } else if (in_range) {
+        li = read_inputs_global(p.means, have_sr ? p.scales : nullptr, p.rots, act_op ? p.opac : nullptr, idx,
+                                p.rots_vec_ok);
         in_radius = p.radii[idx];
-#pragma unroll
-        for (int k = 0; k < 3; k++) in_m[k] = p.means[3 * (size_t)idx + k];
         in_a0 = p.acc[3 * (size_t)idx + 0];
         in_a1 = p.acc[3 * (size_t)idx + 1];
         in_a2 = p.acc[3 * (size_t)idx + 2];
-        if (p.cov3D_precomp == nullptr) {
-#pragma unroll
-            for (int k = 0; k < 3; k++) in_s[k] = p.scales[3 * (size_t)idx + k];
-            in_q = load_quat(p.rots, idx, p.rots_vec_ok);
-        }
     }
     const bool visible = in_range && in_radius > 0;
+    // the SH row of every visible Gaussian is requested now and arrives underneath the arithmetic
+    if (kSh == kShBulkRows && staged_sh) {
+        if (visible) {
+            const uint32_t row_bytes = 12u * (uint32_t)M;
+            mbar_arrive_expect_tx(bar_sh, row_bytes);
+            bulk_g2s(st.sh + lane * kShRowStride, p.shs + (size_t)idx * 3 * M, row_bytes, bar_sh);
+        } else {
+            mbar_arrive(bar_sh);
+        }
+    }
+
+    // activated scale / rotation (what the forward rasterised) and what their Jacobians need
+    float sx = li.sx, sy = li.sy, sz = li.sz;
+    float4 q = li.q;
+    float q_denom = 1.0f;
+    if (have_sr) {
+        if (p.act & VEGS_ACT_SCALE_EXP) { sx = expf(sx); sy = expf(sy); sz = expf(sz); }
+        if (p.act & VEGS_ACT_ROT_NORMALIZE) q = act_normalize(q, q_denom);
+    }
 
     float dmean[3] = {0.f, 0.f, 0.f};
     float dm2d[2] = {0.f, 0.f};
@@ -212,7 +219,7 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
     float mx = 0.f, my = 0.f, mz = 0.f;
 
     if (visible) {
-        mx = in_m[0]; my = in_m[1]; mz = in_m[2];
+        mx = li.mx; my = li.my; mz = li.mz;
         const float4 a0 = in_a0;  // dmean2D.xy, dconic.xx, dconic.xy
         const float4 a1 = in_a1;  // dconic.yy, dopacity, dcol.r, dcol.g
         const float4 a2 = in_a2;  // dcol.b, ddepth
@@ -222,16 +229,12 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
         dcol[0] = a1.z; dcol[1] = a1.w; dcol[2] = a2.x;
         const float ddepth = a2.y;
 
-        // ---- 3D covariance (recomputed) and scale/rotation
+        // ---- 3D covariance (recomputed) from the activated scale / rotation
         float c3[6];
-        float sx = 0.f, sy = 0.f, sz = 0.f;
-        float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
         if (p.cov3D_precomp != nullptr) {
 #pragma unroll
             for (int k = 0; k < 6; k++) c3[k] = p.cov3D_precomp[6 * (size_t)idx + k];
         } else {
-            sx = in_s[0]; sy = in_s[1]; sz = in_s[2];
-            q = in_q;
             cov3d_from_scale_rot(sx, sy, sz, p.mod, q.x, q.y, q.z, q.w, c3);
         }
 
@@ -354,10 +357,10 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
         }
     }
 
-    // ---- SH backward (row staged in shared memory, coalesced both ways)
-    if (p.shs != nullptr && p.dL_dsh != nullptr) {
-        const int rowlen = 3 * M;
-        const unsigned vis = __ballot_sync(0xffffffffu, visible);
+    // ---- SH backward: dL/dSH rows built in the staging rows, dL/dmean through the view direction
+    const bool acc_sh = (p.accum & VEGS_ACC_SH) != 0u;
+    bool dsh_done = !use_sh;
+    if (use_sh) {
         float dRGB[3] = {0.f, 0.f, 0.f};
         if (visible) {
             const uint32_t cb = p.clamped[idx];
@@ -366,46 +369,74 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
             dRGB[2] = (cb & 4u) ? 0.f : dcol[2];
         }
         const float dox = mx - cam.campos[0], doy = my - cam.campos[1], doz = mz - cam.campos[2];
-        if (M <= kMaxStageCoeffs) {
-            const int stride = rowlen | 1;
-            float* srow = s_sh[warp];
-            float* myrow = srow + lane * stride;
-            const bool full = (warp_base + 32 <= p.P);
-            const int nvec = 8 * rowlen;
-            if (vis != 0u) {
-                if (full && p.shs_vec_ok) {
-                    const float4* src =
-                        reinterpret_cast<const float4*>(p.shs + (size_t)warp_base * rowlen);
-                    for (int f = lane; f < nvec; f += 32) {
-                        const int e0 = 4 * f;
-                        const int r0 = e0 / rowlen;
-                        const int r1 = (e0 + 3) / rowlen;
-                        if (((vis >> r0) | (vis >> r1)) & 1u) {
-                            const float4 v4 = ldg_stream4(src + f);
-                            const float vv[4] = {v4.x, v4.y, v4.z, v4.w};
-#pragma unroll
-                            for (int k = 0; k < 4; k++) {
-                                const int e = e0 + k;
-                                const int r = e / rowlen;
-                                srow[r * stride + (e - r * rowlen)] = vv[k];
-                            }
-                        }
+        if (staged_sh) {
+            const int rowlen = 3 * M;
+            float *row, *dc;
+            if (kSh == kShBulkRows) {
+                row = st.sh + lane * kShRowStride; dc = row;
+                mbar_wait(bar_sh, 0);
+            } else if (kSh == kShSplit) {
+                const int rs = 3 * (M - 1);
+                dc = st.sh + 32 * rs + 3 * lane;
+                row = st.sh + lane * rs - 3;
+                if (sh_block_bulk) {
+                    mbar_wait(bar_sh, 0);
+                } else {
+                    if (visible) {
+                        for (int k = 0; k < 3; k++) dc[k] = p.shs[3 * (size_t)idx + k];
+                        const float* src = p.shs_rest + (size_t)idx * rs;
+                        for (int k = 0; k < rs; k++) row[3 + k] = src[k];
                     }
-                } else if (visible) {
-                    const float* src = p.shs + (size_t)idx * rowlen;
-                    for (int k = 0; k < rowlen; k++) myrow[k] = src[k];
+                    __syncwarp();
                 }
-            }
-            __syncwarp();
-            if (visible) {
-                const float3 dm = sh_backward(myrow, p.D, M, dox, doy, doz, dRGB);
-                dmean[0] += dm.x; dmean[1] += dm.y; dmean[2] += dm.z;
             } else {
-                for (int k = 0; k < rowlen; k++) myrow[k] = 0.0f;
+                row = st.sh + lane * (rowlen | 1); dc = row;
+                const unsigned vis = __ballot_sync(0xffffffffu, visible);
+                if (vis != 0u) stage_sh_ldg(st.sh, p.shs, rowlen, warp_base, p.P, vis, visible, idx, lane, p.shs_vec_ok, rowlen);
+                __syncwarp();
             }
-            __syncwarp();
-            const bool acc_sh = (p.accum & VEGS_ACC_SH) != 0u;
-            if (full && p.dsh_vec_ok) {
+            ShBwdState sb = sh_bwd_begin(p.D, visible ? dox : 1.f, doy, doz, dRGB);
+            const bool zero_only = !visible;       // rows of culled Gaussians: zeros (ignored when accumulating)
+            sh_bwd_row_group<kSh, 0>(sb, row, dc, M, zero_only);
+            sh_bwd_row_group<kSh, 1>(sb, row, dc, M, zero_only);
+            sh_bwd_row_group<kSh, 2>(sb, row, dc, M, zero_only);
+            sh_bwd_row_group<kSh, 3>(sb, row, dc, M, zero_only);
+            if (visible) {
+                const float3 dm = sh_bwd_end(sb, dox, doy, doz);
+                dmean[0] += dm.x; dmean[1] += dm.y; dmean[2] += dm.z;
+            }
+            // ---- dL/dSH rows to global memory
+            if (kSh == kShBulkRows && p.dsh_vec_ok) {
+                // one bulk store (or L2 reduction, when accumulating) per row, issued by the row's lane
+                fence_smem_to_async_proxy();
+                if (in_range && (visible || !acc_sh)) {
+                    float* dst = p.dL_dsh + (size_t)idx * rowlen;
+                    if (acc_sh) bulk_s2g_add_f32(dst, row, 12u * (uint32_t)M);
+                    else bulk_s2g(dst, row, 12u * (uint32_t)M);
+                }
+                dsh_done = true;
+            } else if (kSh == kShSplit && full && p.dsh_vec_ok) {
+                // the warp's two dense blocks leave as they came
+                fence_smem_to_async_proxy();
+                __syncwarp();
+                if (lane == 0) {
+                    const int rs = 3 * (M - 1);
+                    float* d0 = p.dL_dsh + 3 * (size_t)warp_base;
+                    float* d1 = p.dL_dsh_rest + (size_t)warp_base * rs;
+                    if (acc_sh) {
+                        bulk_s2g_add_f32(d0, st.sh + 32 * rs, 384u);
+                        if (rs) bulk_s2g_add_f32(d1, st.sh, 32u * 4u * (uint32_t)rs);
+                    } else {
+                        bulk_s2g(d0, st.sh + 32 * rs, 384u);
+                        if (rs) bulk_s2g(d1, st.sh, 32u * 4u * (uint32_t)rs);
+                    }
+                }
+                dsh_done = true;
+            } else if (kSh == kShLdg && full && p.dsh_vec_ok) {
+                __syncwarp();
+                const unsigned vis = __ballot_sync(0xffffffffu, visible);
+                const int stride = rowlen | 1;
+                const int nvec = 8 * rowlen;
                 float4* dst = reinterpret_cast<float4*>(p.dL_dsh + (size_t)warp_base * rowlen);
                 for (int f = lane; f < nvec; f += 32) {
                     float vv[4];
@@ -413,7 +444,7 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
                     for (int k = 0; k < 4; k++) {
                         const int e = 4 * f + k;
                         const int r = e / rowlen;
-                        vv[k] = srow[r * stride + (e - r * rowlen)];
+                        vv[k] = st.sh[r * stride + (e - r * rowlen)];
                     }
                     if (acc_sh) {
                         // rows of culled Gaussians add nothing: leave chunks that only touch them alone
@@ -424,26 +455,88 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
                     }
                     dst[f] = make_float4(vv[0], vv[1], vv[2], vv[3]);
                 }
-            } else if (in_range && (!acc_sh || visible)) {
-                float* dst = p.dL_dsh + (size_t)idx * rowlen;
-                for (int k = 0; k < rowlen; k++) dst[k] = acc_sh ? dst[k] + myrow[k] : myrow[k];
+                dsh_done = true;
+            }
+            if (!dsh_done && in_range && (!acc_sh || visible)) {
+                // partial warp / unaligned output: the lane writes its own row
+                if (kSh == kShSplit) {
+                    float* d0 = p.dL_dsh + 3 * (size_t)idx;
+                    float* d1 = p.dL_dsh_rest + (size_t)idx * 3 * (M - 1);
+                    for (int k = 0; k < 3; k++) d0[k] = acc_sh ? d0[k] + dc[k] : dc[k];
+                    for (int k = 0; k < 3 * (M - 1); k++) d1[k] = acc_sh ? d1[k] + row[3 + k] : row[3 + k];
+                } else {
+                    float* dst = p.dL_dsh + (size_t)idx * rowlen;
+                    for (int k = 0; k < rowlen; k++) dst[k] = acc_sh ? dst[k] + row[k] : row[k];
+                }
             }
         } else if (in_range) {
-            // M > 16: no staging; work in the output row directly
+            // M > 16: no staging; work in a local copy of the first 16 coefficients
             // (accumulation is refused for M > 16 by the launcher)
-            float* dst = p.dL_dsh + (size_t)idx * rowlen;
+            float* dst = p.dL_dsh + (size_t)idx * 3 * M;
             if (visible) {
-                const float* src = p.shs + (size_t)idx * rowlen;
-                for (int k = 0; k < 48; k++) dst[k] = src[k];
-                const float3 dm = sh_backward(dst, p.D, M, dox, doy, doz, dRGB);
+                const float* src = p.shs + (size_t)idx * 3 * M;
+                float loc[48];
+                for (int k = 0; k < 48; k++) loc[k] = src[k];
+                ShBwdState sb = sh_bwd_begin(p.D, dox, doy, doz, dRGB);
+                sh_bwd_group<0>(sb, loc); sh_bwd_group<1>(sb, loc + 12);
+                sh_bwd_group<2>(sb, loc + 24); sh_bwd_group<3>(sb, loc + 36);
+                const float3 dm = sh_bwd_end(sb, dox, doy, doz);
                 dmean[0] += dm.x; dmean[1] += dm.y; dmean[2] += dm.z;
+                for (int k = 0; k < 48; k++) dst[k] = loc[k];
+                for (int k = 48; k < 3 * M; k++) dst[k] = 0.0f;
             } else {
-                for (int k = 0; k < rowlen; k++) dst[k] = 0.0f;
+                for (int k = 0; k < 3 * M; k++) dst[k] = 0.0f;
+            }
+        }
+    }
+
+    // ---- Jacobians of the fused activations (scene/gaussian_model.py:100-120 applied by the caller otherwise)
+    float dm2_norm = 0.f;
+    if (visible) {
+        dm2_norm = sqrtf(dm2d[0] * dm2d[0] + dm2d[1] * dm2d[1]);
+        if (act_op) { const float o = act_sigmoid(li.op); dopac *= o * (1.0f - o); }
+        if (have_sr) {
+            if (p.act & VEGS_ACT_SCALE_EXP) { dscale[0] *= sx; dscale[1] *= sy; dscale[2] *= sz; }
+            if (p.act & VEGS_ACT_ROT_NORMALIZE) {
+                // n = q_raw / max(|q_raw|, eps):  dL/dq_raw = (g - n <n, g>) / max(|q_raw|, eps)
+                const float ng = q.x * drot[0] + q.y * drot[1] + q.z * drot[2] + q.w * drot[3];
+                const float inv = 1.0f / q_denom;
+                drot[0] = (drot[0] - q.x * ng) * inv; drot[1] = (drot[1] - q.y * ng) * inv;
+                drot[2] = (drot[2] - q.z * ng) * inv; drot[3] = (drot[3] - q.w * ng) * inv;
             }
         }
     }
 
     // ---- dense outputs: overwritten, or added to (visible rows only) where accumulation is requested
+    if (out_bulk) {
+        // the warp's blocks are staged in shared memory (over the input blocks, which every lane has
+        // in registers by now) and leave as one bulk store / reduction each; culled rows hold zeros,
+        // which is what an overwrite must write and what an addition may add
+        __syncwarp();
+        float* o = st.io;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            o[kOutMeans3D + 3 * lane + k] = dmean[k];
+            o[kOutMeans2D + 3 * lane + k] = (k < 2) ? dm2d[k] : 0.0f;
+            o[kOutScales + 3 * lane + k] = dscale[k];
+        }
+        *reinterpret_cast<float4*>(&o[kOutRots + 4 * lane]) = make_float4(drot[0], drot[1], drot[2], drot[3]);
+        o[kOutOpac + lane] = dopac;
+        fence_smem_to_async_proxy();
+        __syncwarp();
+        if (lane == 0) {
+            auto put_block = [&](float* dst, int off, uint32_t bytes, uint32_t bit) {
+                if (dst == nullptr) return;
+                if (p.accum & bit) bulk_s2g_add_f32(dst, o + off, bytes);
+                else bulk_s2g(dst, o + off, bytes);
+            };
+            put_block(p.dL_dmeans3D ? p.dL_dmeans3D + 3 * (size_t)warp_base : nullptr, kOutMeans3D, 384u, VEGS_ACC_MEANS3D);
+            put_block(p.dL_dmeans2D ? p.dL_dmeans2D + 3 * (size_t)warp_base : nullptr, kOutMeans2D, 384u, 0u);
+            put_block(p.dL_dopacity ? p.dL_dopacity + (size_t)warp_base : nullptr, kOutOpac, 128u, VEGS_ACC_OPACITY);
+            put_block(p.dL_dscales ? p.dL_dscales + 3 * (size_t)warp_base : nullptr, kOutScales, 384u, VEGS_ACC_SCALES);
+            put_block(p.dL_drots ? p.dL_drots + 4 * (size_t)warp_base : nullptr, kOutRots, 512u, VEGS_ACC_ROTATIONS);
+        }
+    }
     if (in_range) {
         const size_t i3 = 3 * (size_t)idx;
         auto put = [&](float* dst, int n, const float* v, uint32_t bit) {
@@ -452,22 +545,28 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PbPara
             if (acc && !visible) return;
             for (int k = 0; k < n; k++) dst[k] = acc ? dst[k] + v[k] : v[k];
         };
-        const float dm2[3] = {dm2d[0], dm2d[1], 0.0f};
-        put(p.dL_dmeans3D ? p.dL_dmeans3D + i3 : nullptr, 3, dmean, VEGS_ACC_MEANS3D);
-        put(p.dL_dmeans2D ? p.dL_dmeans2D + i3 : nullptr, 3, dm2, 0u);
+        if (!out_bulk) {
+            const float dm2[3] = {dm2d[0], dm2d[1], 0.0f};
+            put(p.dL_dmeans3D ? p.dL_dmeans3D + i3 : nullptr, 3, dmean, VEGS_ACC_MEANS3D);
+            put(p.dL_dmeans2D ? p.dL_dmeans2D + i3 : nullptr, 3, dm2, 0u);
+            put(p.dL_dopacity ? p.dL_dopacity + idx : nullptr, 1, &dopac, VEGS_ACC_OPACITY);
+            put(p.dL_dscales ? p.dL_dscales + i3 : nullptr, 3, dscale, VEGS_ACC_SCALES);
+            put(p.dL_drots ? p.dL_drots + 4 * (size_t)idx : nullptr, 4, drot, VEGS_ACC_ROTATIONS);
+        }
+        // the two rarely used outputs (colors_precomp / cov3D_precomp modes) are written directly
         put(p.dL_dcolors ? p.dL_dcolors + i3 : nullptr, 3, dcol, VEGS_ACC_COLORS);
-        put(p.dL_dopacity ? p.dL_dopacity + idx : nullptr, 1, &dopac, VEGS_ACC_OPACITY);
-        put(p.dL_dscales ? p.dL_dscales + i3 : nullptr, 3, dscale, VEGS_ACC_SCALES);
-        put(p.dL_drots ? p.dL_drots + 4 * (size_t)idx : nullptr, 4, drot, VEGS_ACC_ROTATIONS);
         put(p.dL_dcov3D ? p.dL_dcov3D + 6 * (size_t)idx : nullptr, 6, dcov, VEGS_ACC_COV3D);
         // densification statistics of the reference's training loop (scene/gaussian_model.py:411-413,
         // train.py:300-301), for the Gaussians this view rendered
         if (p.stat_grad != nullptr && visible) {
-            p.stat_grad[idx] += sqrtf(dm2d[0] * dm2d[0] + dm2d[1] * dm2d[1]);
+            p.stat_grad[idx] += dm2_norm;
             p.stat_denom[idx] += 1.0f;
             p.stat_maxr[idx] = fmaxf(p.stat_maxr[idx], (float)in_radius);
         }
     }
+    // the shared-memory sources of this thread's bulk stores must stay intact until they were read
+    bulk_commit();
+    bulk_wait_read_all();
 }
 
 }  // namespace
@@ -476,20 +575,29 @@ int launch_preprocess_bwd(const VegsBackwardArgs& a, const GeomView& g, const fl
                           cudaStream_t stream) {
     PbParams p;
     p.P = a.P; p.D = a.D; p.M = a.M; p.W = a.W; p.H = a.H;
-    p.means = a.means3D; p.radii = a.radii; p.shs = a.shs; p.clamped = g.clamped;
-    p.scales = a.scales; p.rots = a.rotations; p.cov3D_precomp = a.cov3D_precomp;
+    p.means = a.means3D; p.radii = a.radii; p.shs = a.shs; p.shs_rest = a.shs_rest; p.clamped = g.clamped;
+    p.scales = a.scales; p.rots = a.rotations; p.opac = a.opacities; p.cov3D_precomp = a.cov3D_precomp;
     p.mod = a.scale_modifier; p.tan_fovx = a.tan_fovx; p.tan_fovy = a.tan_fovy;
     p.focal_y = a.H / (2.0f * a.tan_fovy);
     p.focal_x = a.W / (2.0f * a.tan_fovx);
     p.view = a.viewmatrix; p.proj = a.projmatrix; p.campos = a.campos;
     p.acc = acc;
-    p.dL_dmeans3D = a.dL_dmeans3D; p.dL_dmeans2D = a.dL_dmeans2D; p.dL_dsh = a.dL_dsh;
+    p.map_acc = nullptr;
+    p.dL_dmeans3D = a.dL_dmeans3D; p.dL_dmeans2D = a.dL_dmeans2D; p.dL_dsh = a.dL_dsh; p.dL_dsh_rest = a.dL_dsh_rest;
     p.dL_dcolors = a.dL_dcolors; p.dL_dopacity = a.dL_dopacity; p.dL_dscales = a.dL_dscales;
     p.dL_drots = a.dL_drotations; p.dL_dcov3D = a.dL_dcov3D;
-    p.shs_vec_ok = a.shs != nullptr && (reinterpret_cast<uintptr_t>(a.shs) & 15u) == 0;
-    p.dsh_vec_ok = a.dL_dsh != nullptr && (reinterpret_cast<uintptr_t>(a.dL_dsh) & 15u) == 0;
-    p.rots_vec_ok = a.rotations != nullptr && (reinterpret_cast<uintptr_t>(a.rotations) & 15u) == 0;
+    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };   // NULL counts as aligned
+    p.shs_vec_ok = a.shs != nullptr && al16(a.shs) && al16(a.shs_rest);
+    p.dsh_vec_ok = a.dL_dsh != nullptr && al16(a.dL_dsh) && al16(a.dL_dsh_rest);
+    p.rots_vec_ok = a.rotations != nullptr && al16(a.rotations);
+    p.act = a.activations;
     p.accum = a.accumulate_mask;
+    const bool bulk_off = sh_bulk_disabled();
+    p.in_bulk_ok = !bulk_off && al16(a.means3D) && al16(a.radii) && al16(acc) &&
+                   (a.cov3D_precomp != nullptr || (al16(a.scales) && al16(a.rotations))) &&
+                   (!(a.activations & VEGS_ACT_OPACITY_SIGMOID) || al16(a.opacities));
+    p.out_bulk_ok = !bulk_off && al16(a.dL_dmeans3D) && al16(a.dL_dmeans2D) && al16(a.dL_dopacity) &&
+                    al16(a.dL_dscales) && al16(a.dL_drotations);
     p.stat_grad = a.stat_grad_accum; p.stat_denom = a.stat_denom; p.stat_maxr = a.stat_max_radii;
     if ((p.stat_grad != nullptr) != (p.stat_denom != nullptr) || (p.stat_grad != nullptr) != (p.stat_maxr != nullptr)) {
         set_error("vegs_backward: stat_grad_accum, stat_denom and stat_max_radii go together");
@@ -499,14 +607,31 @@ int launch_preprocess_bwd(const VegsBackwardArgs& a, const GeomView& g, const fl
         set_error("vegs_backward: VEGS_ACC_SH needs M <= %d", kMaxStageCoeffs);
         return VEGS_EINVAL;
     }
-    const int blocks = (a.P + kPbThreads - 1) / kPbThreads;
-    switch (a.M) {
-        case 16: preprocess_bwd_kernel<16><<<blocks, kPbThreads, 0, stream>>>(p); break;
-        case 9:  preprocess_bwd_kernel<9><<<blocks, kPbThreads, 0, stream>>>(p); break;
-        case 4:  preprocess_bwd_kernel<4><<<blocks, kPbThreads, 0, stream>>>(p); break;
-        case 1:  preprocess_bwd_kernel<1><<<blocks, kPbThreads, 0, stream>>>(p); break;
-        default: preprocess_bwd_kernel<0><<<blocks, kPbThreads, 0, stream>>>(p); break;
+    if ((a.activations & VEGS_ACT_OPACITY_SIGMOID) && a.opacities == nullptr) {
+        set_error("vegs_backward: VEGS_ACT_OPACITY_SIGMOID needs the raw opacities");
+        return VEGS_EINVAL;
     }
+    if (a.shs_rest != nullptr && (a.shs == nullptr || a.dL_dsh_rest == nullptr || a.M < 1 || a.M > kMaxStageCoeffs)) {
+        set_error("vegs_backward: shs_rest needs shs (= f_dc), dL_dsh_rest and 1 <= M <= %d", kMaxStageCoeffs);
+        return VEGS_EINVAL;
+    }
+    int mode = kShLdg;
+    if (a.shs_rest != nullptr) mode = kShSplit;
+    else if (a.shs != nullptr && a.dL_dsh != nullptr && a.M <= kMaxStageCoeffs && (12 * a.M) % 16 == 0 &&
+             p.shs_vec_ok && !bulk_off)
+        mode = kShBulkRows;
+    const int blocks = (a.P + kPwThreads - 1) / kPwThreads;
+#define VEGS_PB_LAUNCH(KM, MODE) preprocess_bwd_kernel<KM, MODE><<<blocks, kPwThreads, 0, stream>>>(p)
+    if (a.M == 16) {
+        if (mode == kShBulkRows) VEGS_PB_LAUNCH(16, kShBulkRows);
+        else if (mode == kShSplit) VEGS_PB_LAUNCH(16, kShSplit);
+        else VEGS_PB_LAUNCH(16, kShLdg);
+    } else {
+        if (mode == kShBulkRows) VEGS_PB_LAUNCH(0, kShBulkRows);
+        else if (mode == kShSplit) VEGS_PB_LAUNCH(0, kShSplit);
+        else VEGS_PB_LAUNCH(0, kShLdg);
+    }
+#undef VEGS_PB_LAUNCH
     VEGS_LAUNCH_CHECK("preprocess_bwd", stream, a.debug);
     return VEGS_OK;
 }

@@ -68,7 +68,8 @@ class _State:
 
 def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier,
                   cov3Ds_precomp, viewmatrix, projmatrix, tanfovx, tanfovy, image_height,
-                  image_width, sh, degree, campos, prefiltered, debug, keep_scratch=False):
+                  image_width, sh, degree, campos, prefiltered, debug, keep_scratch=False,
+                  activations=0, sh_rest=None):
     lib = _lib.load()
     if means3D.dim() != 2 or means3D.shape[1] != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
@@ -82,6 +83,8 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
     st = _State()
     st.P, st.D, st.W, st.H, st.R = P, int(degree), W, H, 0
     st.M = int(sh.shape[1]) if (sh is not None and sh.numel() != 0) else 0
+    if sh_rest is not None:
+        st.M += int(sh_rest.shape[1])      # sh is f_dc [P,1,3], sh_rest is f_rest [P,M-1,3]
     st.geom = st.img = st.binning = st.scratch = st.bin_scratch = None
     st.args = None
 
@@ -96,6 +99,7 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
         means3D = _dev_f32(means3D, device, "means3D")
         opacities = _dev_f32(opacities, device, "opacities")
         sh = _dev_f32(sh, device, "shs")
+        sh_rest = _dev_f32(sh_rest, device, "features_rest")
         colors_precomp = _dev_f32(colors_precomp, device, "colors_precomp")
         scales = _dev_f32(scales, device, "scales")
         rotations = _dev_f32(rotations, device, "rotations")
@@ -139,6 +143,8 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
         a.out_alpha, a.radii = out_alpha.data_ptr(), radii.data_ptr()
         a.geom, a.img, a.scratch = st.geom.data_ptr(), st.img.data_ptr(), st.scratch.data_ptr()
         a.num_rendered_host = word.data_ptr()
+        a.activations = int(activations)
+        a.shs_rest = _ptr(sh_rest)
 
         sp = C.c_void_p(stream.cuda_stream)
         _lib.check(lib.vegs_forward_prepare(C.byref(a), sp), "vegs_forward_prepare")
@@ -153,7 +159,7 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
         if keep_scratch:
             st.args = a
             # keep the inputs alive for as long as the args struct may be used
-            st.args._keep = (bg, means3D, sh, colors_precomp, opacities, scales, rotations,
+            st.args._keep = (bg, means3D, sh, sh_rest, colors_precomp, opacities, scales, rotations,
                              cov3Ds_precomp, viewmatrix, projmatrix, campos, out_color, out_depth,
                              out_quat, out_scale, out_alpha, radii)
         else:
@@ -197,7 +203,7 @@ def export_state(st: _State, radii: torch.Tensor):
     return out
 
 
-_ACC_BITS = dict(means3D=1, sh=2, colors=4, opacity=8, scales=16, rotations=32, cov3D=64)   # VEGS_ACC_*
+_ACC_BITS = dict(means3D=1, sh=2, sh_rest=2, colors=4, opacity=8, scales=16, rotations=32, cov3D=64)   # VEGS_ACC_*
 
 
 class RasterizerOptions:
@@ -264,7 +270,8 @@ def _accum_target(t, shape, mode):
 def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotations,
                    scale_modifier, cov3Ds_precomp, viewmatrix, projmatrix, tanfovx, tanfovy,
                    grad_color, grad_depth, grad_cov_quat, grad_cov_scale, grad_alpha, sh, campos,
-                   out_alpha, opacities_shape, debug, leaves=None, options=None):
+                   out_alpha, opacities_shape, debug, leaves=None, options=None, activations=0,
+                   opacities_raw=None, sh_rest=None):
     lib = _lib.load()
     device = means3D.device
     P, M = st.P, st.M
@@ -291,10 +298,14 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
         campos = _dev_f32(campos, device, "campos")
         means3D = _dev_f32(means3D, device, "means3D")
         sh = _dev_f32(sh, device, "shs")
+        sh_rest = _dev_f32(sh_rest, device, "features_rest")
+        opacities_raw = _dev_f32(opacities_raw, device, "opacities")
         colors_precomp = _dev_f32(colors_precomp, device, "colors_precomp")
         scales = _dev_f32(scales, device, "scales")
         rotations = _dev_f32(rotations, device, "rotations")
         cov3Ds_precomp = _dev_f32(cov3Ds_precomp, device, "cov3D_precomp")
+        split = sh_rest is not None
+        M_dc = 1 if split else M          # rows of the tensor `sh` points at
 
         # outputs: a fresh tensor, or (fused accumulation) the leaf's existing .grad, added to in place
         leaves = leaves or {}
@@ -306,7 +317,7 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
             nonlocal acc_mask
             if not wanted:
                 return None
-            tgt = _accum_target(leaves.get(name), shape, acc_mode) if M <= 16 or name != "sh" else None
+            tgt = _accum_target(leaves.get(name), shape, acc_mode) if M <= 16 or name not in ("sh", "sh_rest") else None
             if tgt is not None:
                 if acc_mode == "add":
                     acc_mask |= _ACC_BITS[name]     # "assign": the kernel's plain overwrite, into .grad
@@ -317,7 +328,11 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
         dmeans3D = out("means3D", (P, 3))
         dmeans2D = torch.empty((P, 3), **f32)
         dopac = out("opacity", tuple(opacities_shape))
-        dsh = out("sh", (P, M, 3), have_sh)
+        if split and (_accum_target(leaves.get("sh"), (P, 1, 3), acc_mode) is None
+                      or _accum_target(leaves.get("sh_rest"), (P, M - 1, 3), acc_mode) is None):
+            leaves = {k: v for k, v in leaves.items() if k not in ("sh", "sh_rest")}   # VEGS_ACC_SH covers both
+        dsh = out("sh", (P, M_dc, 3), have_sh)
+        dsh_rest = out("sh_rest", (P, M - 1, 3), split)
         dcolors = out("colors", (P, 3), not have_sh)
         dscales = out("scales", (P, 3), have_sr)
         drots = out("rotations", (P, 4), have_sr)
@@ -351,6 +366,10 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
         b.dL_dscales, b.dL_drotations = _ptr(dscales), _ptr(drots)
         b.dL_dcov3D = _ptr(dcov)
         b.accumulate_mask = acc_mask
+        b.activations = int(activations)
+        b.opacities = _ptr(opacities_raw)
+        b.shs_rest = _ptr(sh_rest)
+        b.dL_dsh_rest = _ptr(dsh_rest)
         if options is not None and options.densification_accumulators is not None:
             sg, sd, sr = options.densification_accumulators
             if sg.numel() != P or sg.device != device:
@@ -359,8 +378,9 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
         _lib.check(lib.vegs_backward(C.byref(b), C.c_void_p(stream.cuda_stream)), "vegs_backward")
     # inputs whose .grad already received the result get no gradient from autograd
     nf = lambda name, t: None if name in fused else t
-    return (nf("means3D", dmeans3D), dmeans2D, nf("sh", dsh), nf("colors", dcolors), nf("opacity", dopac),
-            nf("scales", dscales), nf("rotations", drots), nf("cov3D", dcov))
+    res = (nf("means3D", dmeans3D), dmeans2D, nf("sh", dsh), nf("colors", dcolors), nf("opacity", dopac),
+           nf("scales", dscales), nf("rotations", drots), nf("cov3D", dcov))
+    return res + (nf("sh_rest", dsh_rest),) if split else res
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
@@ -430,6 +450,52 @@ class _RasterizeGaussians(torch.autograd.Function):
                 grad_scales, grad_rotations, grad_cov3Ds_precomp, None, None)
 
 
+ACT_OPACITY_SIGMOID, ACT_SCALE_EXP, ACT_ROT_NORMALIZE = 1, 2, 4       # VEGS_ACT_* (include/vegs_b200.h)
+_ACT_ALL = ACT_OPACITY_SIGMOID | ACT_SCALE_EXP | ACT_ROT_NORMALIZE
+
+
+class _RasterizeGaussiansRaw(torch.autograd.Function):
+    """GaussianRasterizer.forward_raw: the rasterizer on VEGS's RAW parameters.  No reference
+    counterpart: it stands for `render()`'s getter calls + the rasterizer call
+    (gaussian_renderer/__init__.py:55-82 with scene/gaussian_model.py:100-120), with
+    sigmoid / exp / normalize / cat and their backward folded into the two per-Gaussian kernels."""
+
+    @staticmethod
+    def forward(ctx, xyz, means2D, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw,
+                raster_settings, options=None):
+        rs = raster_settings
+        empty = torch.Tensor([])
+        color, depth, cov_quat, cov_scale, alpha, radii, st = _forward_impl(
+            rs.bg, xyz, empty, opacity_raw, scaling_raw, rotation_raw, rs.scale_modifier, empty, rs.viewmatrix,
+            rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, features_dc, rs.sh_degree,
+            rs.campos, rs.prefiltered, rs.debug, activations=_ACT_ALL, sh_rest=features_rest)
+        ctx.raster_settings = rs
+        ctx.state = st
+        ctx.opacities_shape = tuple(opacity_raw.shape)
+        ctx.save_for_backward(xyz, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw, radii, alpha)
+        ctx.options = options if (options is not None and options.any) else None
+        ctx.leaves = dict(means3D=xyz, sh=features_dc, sh_rest=features_rest, opacity=opacity_raw,
+                          scales=scaling_raw, rotations=rotation_raw) \
+            if (ctx.options is not None and ctx.options.fused_grad_accumulation) else None
+        ctx.mark_non_differentiable(radii)
+        return color, depth, cov_quat, cov_scale, alpha, radii
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_out_depth, grad_out_cov_quat, grad_out_cov_scale, grad_out_alpha, _):
+        rs = ctx.raster_settings
+        xyz, f_dc, f_rest, opacity_raw, scaling_raw, rotation_raw, radii, alpha = ctx.saved_tensors
+        empty = torch.Tensor([])
+        g = _backward_impl(ctx.state, rs.bg, xyz, radii, empty, scaling_raw, rotation_raw, rs.scale_modifier, empty,
+                           rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color, grad_out_depth,
+                           grad_out_cov_quat, grad_out_cov_scale, grad_out_alpha, f_dc, rs.campos, alpha,
+                           ctx.opacities_shape, rs.debug, leaves=ctx.leaves, options=ctx.options,
+                           activations=_ACT_ALL, opacities_raw=opacity_raw, sh_rest=f_rest)
+        if len(g) == 8:                      # no higher-order coefficients: features_rest was empty
+            g = g + (torch.zeros_like(f_rest),)
+        g_xyz, g_m2d, g_dc, _gc, g_op, g_sc, g_rot, _gcov, g_rest = g
+        return g_xyz, g_m2d, g_dc, g_rest, g_op, g_sc, g_rot, None, None
+
+
 class GaussianRasterizationSettings(NamedTuple):
     image_height: int
     image_width: int
@@ -474,6 +540,21 @@ class GaussianRasterizer(nn.Module):
                                                visible.data_ptr(), C.c_void_p(stream.cuda_stream))
                     _lib.check(rc, "vegs_mark_visible")
         return visible
+
+    def forward_raw(self, xyz, means2D, opacity_raw, features_dc, features_rest, scaling_raw, rotation_raw):
+        """Opt-in extension (no reference counterpart): rasterise from VEGS's RAW parameters
+        `_xyz [P,3], _opacity [P,1], _features_dc [P,1,3], _features_rest [P,M-1,3], _scaling [P,3],
+        _rotation [P,4]`.  Equivalent to
+            forward(xyz, means2D, sigmoid(opacity_raw), shs=cat((features_dc, features_rest), 1),
+                    scales=exp(scaling_raw), rotations=normalize(rotation_raw))
+        (scene/gaussian_model.py:100-120) with the four activation passes and their backward passes
+        fused into the per-Gaussian kernels.  Same six return values; gradients arrive at the raw
+        parameters."""
+        if not (features_dc.dim() == 3 and features_dc.shape[1] == 1 and features_rest.dim() == 3):
+            raise Exception('features_dc must be [P,1,3] and features_rest [P,M-1,3]')
+        return _RasterizeGaussiansRaw.apply(xyz, means2D, features_dc, features_rest, opacity_raw, scaling_raw,
+                                            rotation_raw, self.raster_settings,
+                                            self.options if self.options.any else None)
 
     def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None,
                 rotations=None, cov3D_precomp=None):

@@ -67,18 +67,20 @@ class DensificationStats:
 
 
 def flat_size(params: Dict[str, torch.Tensor]) -> int:
-    P = params["means3D"].shape[0]
-    return sum(params[k].numel() for k in PARAM_ORDER) + 2 * P
+    return _layout(params)[1]
 
 
 def _layout(params: Dict[str, torch.Tensor]):
-    """[(name, offset, numel)] of the flat buffer: the five gradients, then the two additive statistics."""
+    """[(name, offset, numel)] of the flat buffer: the five gradients, then the two additive
+    statistics.  Every segment starts on a multiple of four floats, so that each `.grad` view is
+    16-byte aligned (what the backward kernel's bulk stores / reductions need) whatever P is."""
     P = params["means3D"].shape[0]
     out, off = [], 0
+    al = lambda n: (n + 3) // 4 * 4
     for k in PARAM_ORDER:
-        out.append((k, off, params[k].numel())); off += params[k].numel()
-    out.append(("xyz_gradient_accum", off, P)); off += P
-    out.append(("denom", off, P)); off += P
+        out.append((k, off, params[k].numel())); off = al(off + params[k].numel())
+    out.append(("xyz_gradient_accum", off, P)); off = al(off + P)
+    out.append(("denom", off, P)); off = al(off + P)
     return out, off
 
 
@@ -90,6 +92,12 @@ def pack(params: Dict[str, torch.Tensor], stats: DensificationStats, out: torch.
     if out is None:
         out = torch.empty(total, dtype=torch.float32, device=params["means3D"].device)
     assert out.numel() == total and out.is_contiguous()
+    if total != sum(n for _, _, n in layout):
+        # alignment padding (at most three words after a segment) must reduce as zeros
+        ends = [off for _, off, _ in layout[1:]] + [total]
+        for (_, off, n), nxt in zip(layout, ends):
+            if off + n < nxt:
+                out[off + n:nxt].zero_()
     for name, off, n in layout:
         if name in params:
             g = params[name].grad
