@@ -257,6 +257,37 @@ int vegs_dist2(int32_t P, const float* points, float* out, void* workspace, size
 int vegs_dist2_noalloc(int32_t P, const float* points, float* out, void* stream);
 
 /*
+ * Optimiser step over the view-parallel step's buffers in one pass (no counterpart inside the
+ * reference's extensions; it replaces the caller's torch.optim.Adam step, zero_grad and the folding
+ * of the step's densification statistics: scene/gaussian_model.py:154-172,411-413,
+ * train.py:300-301,319-320).  Up to VEGS_ADAM_MAX_SEGMENTS contiguous float segments per call:
+ *   kind 0  Adam:  exp_avg += (1-b1)(g - exp_avg);  exp_avg_sq = b2 exp_avg_sq + (1-b2) g g;
+ *                  param -= (lr / (1-b1^step)) * exp_avg / (sqrt(exp_avg_sq) / sqrt(1-b2^step) + eps)
+ *                  (torch.optim.Adam without weight decay / amsgrad; `step` counts from 1)
+ *   kind 1  param += grad      (running statistic += this step's reduced value)
+ *   kind 2  param  = max(param, grad)
+ * With zero_grad != 0 every `grad` element is set to zero after it was read.
+ */
+#define VEGS_ADAM_MAX_SEGMENTS 12
+typedef struct VegsAdamSegment {
+    float* param;
+    float* grad;
+    float* exp_avg;       /* kind 0 only */
+    float* exp_avg_sq;    /* kind 0 only */
+    int64_t count;        /* elements */
+    float lr;             /* kind 0 only */
+    int32_t kind;
+} VegsAdamSegment;
+typedef struct VegsAdamArgs {
+    VegsAdamSegment segments[VEGS_ADAM_MAX_SEGMENTS];
+    int32_t num_segments;
+    int32_t step;         /* t of the bias corrections, >= 1 */
+    float beta1, beta2, eps;
+    int32_t zero_grad;
+} VegsAdamArgs;
+int vegs_adam_step(const VegsAdamArgs* args, void* stream);
+
+/*
  * Test / parity support: re-express the binning state in the reference's format
  * (cuda_rasterizer/rasterizer_impl.cu:70-111,116-138): point_list_keys[R] = (tile << 32) | depth
  * bits, point_list[R], ranges[T] (uint2), tiles_touched[P], depths[P], means2D[P,2].  Any output

@@ -262,6 +262,103 @@ def test_bulk_copy_paths_equal_the_load_paths():
         util.grad_close(shifted[tk].grad.cpu().numpy(), a["grads"][gk], f"grad {gk} (fallback vs bulk)", rtol=1e-5)
 
 
+def test_fused_adam_matches_torch_adam_step_for_step():
+    """vegs_adam_step (vegs_b200.optim.FusedAdam) against torch.optim.Adam with VEGS's six parameter
+    groups, learning rates and eps = 1e-15 (scene/gaussian_model.py:154-172), five steps with a
+    changing xyz learning rate; plus the statistic folding and the in-pass gradient clear."""
+    from vegs_b200.optim import FusedAdam
+    dev = torch.device("cuda")
+    P = 5003                                    # odd: the 4-element groups have tails
+    shapes = dict(xyz=(P, 3), f_dc=(P, 1, 3), f_rest=(P, 15, 3), opacity=(P, 1), scaling=(P, 3), rotation=(P, 4))
+    lrs = dict(xyz=1.6e-4, f_dc=2.5e-3, f_rest=2.5e-3 / 20, opacity=0.05, scaling=5e-3, rotation=1e-3)
+    g = torch.Generator().manual_seed(0)
+    init = {k: torch.randn(*s, generator=g) for k, s in shapes.items()}
+
+    def make(cls):
+        ps = {k: torch.nn.Parameter(v.to(dev).clone()) for k, v in init.items()}
+        return ps, cls([{"params": [ps[k]], "lr": lrs[k], "name": k} for k in shapes], lr=0.0, eps=1e-15)
+
+    pa, oa = make(torch.optim.Adam)
+    pb, ob = make(FusedAdam)
+    run_add, run_max = torch.zeros(P, 1, device=dev), torch.zeros(P, device=dev)
+    ref_add, ref_max = torch.zeros(P, 1, device=dev), torch.zeros(P, device=dev)
+    for step in range(5):
+        grads = {k: (torch.randn(*s, generator=g) * (10.0 ** (step - 2))).to(dev) for k, s in shapes.items()}
+        grads["f_rest"][::2] = 0.0              # rows without a gradient this step: moments still decay
+        for o in (oa, ob):
+            o.param_groups[0]["lr"] = lrs["xyz"] * (0.9 ** step)
+        for k in shapes:
+            pa[k].grad = grads[k].clone(); pb[k].grad = grads[k].clone()
+        sv_add, sv_max = torch.rand(P, 1, device=dev), torch.rand(P, device=dev) * 30
+        oa.step()
+        ref_add += sv_add; ref_max = torch.maximum(ref_max, sv_max)
+        ob.step(zero_grad=True, stat_updates=[(run_add, sv_add, "add"), (run_max, sv_max, "max")])
+        for k in shapes:
+            assert torch.allclose(pb[k], pa[k], rtol=1e-5, atol=1e-7), (step, k, float((pb[k] - pa[k]).abs().max()))
+            sa, sb = oa.state[pa[k]], ob.state[pb[k]]
+            assert torch.allclose(sb["exp_avg"], sa["exp_avg"], rtol=1e-5, atol=1e-12), (step, k)
+            assert torch.allclose(sb["exp_avg_sq"], sa["exp_avg_sq"], rtol=1e-5, atol=1e-20), (step, k)
+            assert float(pb[k].grad.abs().max()) == 0.0, "zero_grad clears the gradient in the same pass"
+        assert torch.equal(run_add, ref_add) and torch.equal(run_max, ref_max)
+        assert float(sv_add.abs().max()) == 0.0
+
+
+def test_view_parallel_trainer_single_gpu():
+    """The view-parallel driver (vegs_b200/parallel_train.py) end to end on one GPU: SplatModel with
+    FusedAdam, views rendered through forward_raw with the fused accumulation into the flat buffer,
+    a densification inside the run; and the first step's parameters against the same step done the
+    reference's way (getters + drop-in forward, autograd accumulation, torch.optim.Adam)."""
+    import vegs_b200.diff_gaussian_rasterization as dgr
+    from vegs_b200.optim import FusedAdam
+    from vegs_b200.parallel_train import ViewParallelTrainer
+    from vegs_b200.splat_model import SplatModel, TrainingArgs
+    dev = torch.device("cuda")
+    scene = synth.make_scene(30000, seed=2)
+    cams = [synth.make_camera(k, scale=0.25, device=dev) for k in range(4)]
+    gen = torch.Generator().manual_seed(1)
+    gts = [torch.rand(3, c.H, c.W, generator=gen).to(dev) for c in cams]
+    args = TrainingArgs(densify_from_iter=1, densification_interval=2, densify_until_iter=10, opacity_reset_interval=1000,
+                        densify_grad_threshold=1e-7)
+    bg = torch.zeros(3, device=dev)
+
+    def settings(cam):
+        return dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, bg, 1.0, cam.viewmatrix,
+                                                 cam.projmatrix, 3, cam.campos, False, False)
+
+    def render_raw(model, ci, kw):
+        m2 = torch.zeros_like(model._xyz, requires_grad=True)
+        out = dgr.GaussianRasterizer(settings(cams[ci]), **kw).forward_raw(
+            model._xyz, m2, model._opacity, model._features_dc, model._features_rest, model._scaling, model._rotation)
+        return (out[0] - gts[ci]).abs().mean() + 0.01 * out[3].abs().mean(), m2, out[5]
+
+    def render_plain(model, ci, kw):
+        m2 = torch.zeros_like(model._xyz, requires_grad=True)
+        out = dgr.GaussianRasterizer(settings(cams[ci]))(
+            means3D=model.get_xyz, means2D=m2, opacities=model.get_opacity, shs=model.get_features,
+            scales=model.get_scaling, rotations=model.get_rotation)
+        return (out[0] - gts[ci]).abs().mean() + 0.01 * out[3].abs().mean(), m2, out[5]
+
+    fused = SplatModel(scene, device=dev); fused.training_setup(args, FusedAdam)
+    plain = SplatModel(scene, device=dev); plain.training_setup(args)
+    tf = ViewParallelTrainer(fused, list(range(4)), render_raw, args, views_per_step=4, rasterizer_module=dgr,
+                             cameras_extent=50.0, seed=5)
+    tp = ViewParallelTrainer(plain, list(range(4)), render_plain, args, views_per_step=4, cameras_extent=50.0, seed=5)
+    a, b = tf.step(), tp.step()
+    assert a["views"] == b["views"] and abs(a["loss"] - b["loss"]) < 1e-4
+    for k, v in fused.parameters().items():
+        w = plain.parameters()[k]
+        # Adam's first step moves every element by ~lr * sign(g): compare the moves
+        assert torch.allclose(v, w, rtol=1e-4, atol=1e-5), (k, float((v - w).abs().max()))
+    util.grad_close(fused.xyz_gradient_accum.cpu().numpy(), plain.xyz_gradient_accum.cpu().numpy(), "accum", rtol=2e-4)
+    assert torch.equal(fused.denom, plain.denom) and torch.equal(fused.max_radii2D, plain.max_radii2D)
+    P0 = fused.num_points
+    tf.run(3)
+    assert any("densified_to" in l for l in tf.log) and fused.num_points != P0
+    assert all(np.isfinite(l["loss"]) for l in tf.log)
+    for v in fused.parameters().values():
+        assert torch.isfinite(v).all()
+
+
 def test_modes_colors_precomp_and_cov3d_precomp_against_oracle():
     scene = util.scene_with_specials(4000)
     cam = synth.make_camera(0, scale=0.125)

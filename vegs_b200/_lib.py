@@ -58,6 +58,19 @@ class VegsBackwardArgs(C.Structure):
     ]
 
 
+ADAM_MAX_SEGMENTS = 12
+
+
+class VegsAdamSegment(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("count", C.c_int64), ("lr", C.c_float), ("kind", C.c_int32)]
+
+
+class VegsAdamArgs(C.Structure):
+    _fields_ = [("segments", VegsAdamSegment * ADAM_MAX_SEGMENTS), ("num_segments", C.c_int32), ("step", C.c_int32),
+                ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("zero_grad", C.c_int32)]
+
+
 # name -> (restype, argtypes); the list doubles as the symbol inventory checked by the tests
 SIGNATURES = {
     "vegs_abi_version": (C.c_int, []),
@@ -77,6 +90,7 @@ SIGNATURES = {
     "vegs_dist2": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
                              C.c_void_p]),
     "vegs_dist2_noalloc": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "vegs_adam_step": (C.c_int, [C.POINTER(VegsAdamArgs), C.c_void_p]),
     "vegs_export_state": (C.c_int, [C.POINTER(VegsForwardArgs), C.c_int32] + [C.c_void_p] * 10),
     "vegs_export_tile_clocks": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "vegs_kernel_launch_count": (C.c_uint64, []),

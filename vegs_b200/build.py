@@ -26,6 +26,7 @@ SOURCES = [
     "preprocess_bwd.cu",
     "export.cu",
     "knn.cu",
+    "adam.cu",
 ]
 
 NVCC_FLAGS = [

@@ -40,6 +40,13 @@ class DensificationStats:
         self.max_radii2D = torch.zeros((P,), device=device)
         self.fused = False
 
+    @classmethod
+    def wrap(cls, xyz_gradient_accum, denom, max_radii2D) -> "DensificationStats":
+        """A view of three existing tensors (e.g. a GaussianModel's running statistics)."""
+        s = cls.__new__(cls)
+        s.xyz_gradient_accum, s.denom, s.max_radii2D, s.fused = xyz_gradient_accum, denom, max_radii2D, False
+        return s
+
     def zero_(self) -> None:
         self.xyz_gradient_accum.zero_(); self.denom.zero_(); self.max_radii2D.zero_()
 
@@ -70,14 +77,20 @@ def flat_size(params: Dict[str, torch.Tensor]) -> int:
     return _layout(params)[1]
 
 
-def _layout(params: Dict[str, torch.Tensor]):
+def _order(params: Dict[str, torch.Tensor], order=None):
+    if order is not None:
+        return tuple(order)
+    return PARAM_ORDER if all(k in params for k in PARAM_ORDER) and len(params) == len(PARAM_ORDER) else tuple(params.keys())
+
+
+def _layout(params: Dict[str, torch.Tensor], order=None):
     """[(name, offset, numel)] of the flat buffer: the five gradients, then the two additive
     statistics.  Every segment starts on a multiple of four floats, so that each `.grad` view is
     16-byte aligned (what the backward kernel's bulk stores / reductions need) whatever P is."""
     P = params["means3D"].shape[0]
     out, off = [], 0
     al = lambda n: (n + 3) // 4 * 4
-    for k in PARAM_ORDER:
+    for k in _order(params, order):
         out.append((k, off, params[k].numel())); off = al(off + params[k].numel())
     out.append(("xyz_gradient_accum", off, P)); off = al(off + P)
     out.append(("denom", off, P)); off = al(off + P)
@@ -163,8 +176,10 @@ class FlatGradBuffer:
                    buf.allreduce(accumulate_into=running_stats)
     """
 
-    def __init__(self, params: Dict[str, torch.Tensor]):
-        layout, total = _layout(params)
+    def __init__(self, params: Dict[str, torch.Tensor], order=None):
+        """`params`: name -> leaf tensor; must contain "means3D" (its first dimension is the Gaussian
+        count).  `order` fixes the segment order (default: PARAM_ORDER, else the dict's order)."""
+        layout, total = _layout(params, order)
         dev = params["means3D"].device
         P = params["means3D"].shape[0]
         self.params = params
