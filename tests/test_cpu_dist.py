@@ -54,8 +54,15 @@ def _worker(rank, world, port, P, n_views, out):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     params = _make_params(P)
     stats = _run_views(params, vdist.shard_views(n_views, rank, world))
+    # the per-tensor route (NCCL's default) on a copy of the same step must give the same result
+    params2 = _make_params(P)
+    stats2 = _run_views(params2, vdist.shard_views(n_views, rank, world))
+    assert vdist.allreduce_step(params2, stats2, per_tensor=True) is None
     flat = vdist.allreduce_step(params, stats)
     assert flat.numel() == vdist.flat_size(params)
+    for k in params:
+        assert torch.allclose(params[k].grad, params2[k].grad, rtol=1e-6, atol=1e-6), k
+    assert torch.equal(stats.denom, stats2.denom) and torch.equal(stats.max_radii2D, stats2.max_radii2D)
     if rank == 0:
         torch.save(dict(grads={k: v.grad.clone() for k, v in params.items()},
                         accum=stats.xyz_gradient_accum.clone(), denom=stats.denom.clone(),
