@@ -169,6 +169,17 @@ typedef struct VegsBackwardArgs {
     const float* opacities;
     const float* shs_rest;
     float* dL_dsh_rest;
+    /* Opt-in LIVE gradient of the covariance maps (no reference counterpart: the reference computes
+     * such terms and then overwrites them, SURVEY.md Q1, so by default - 0 - they are ignored here
+     * too).  With live_map_gradients != 0 the cotangents dL_dout_cov_scale / dL_dout_cov_quat reach
+     * dL_dscales / dL_drotations with the blending weights w = alpha * T held constant:
+     *   dL_dscales[j]    += sum_pix w_j(pix) * dL_dout_cov_scale[:, pix]          (exact for fixed weights)
+     *   dL_drotations[j] += sum_pix w_j(pix) * P_pix dL_dout_cov_quat[:, pix]     (first order in w: the
+     *       slerp mix(identity, q_j, w) ~ identity + w (q_j - identity); P_pix projects onto the
+     *       tangent space of the normalised output quaternion, out_cov_quat of the forward, required)
+     * No term flows through the weights themselves (they do not feed dL/dalpha). */
+    int32_t live_map_gradients;
+    const float* out_cov_quat;    /* [4,H,W] from the forward; only read when live_map_gradients != 0 */
 } VegsBackwardArgs;
 
 #define VEGS_ACC_MEANS3D   1u
@@ -286,6 +297,20 @@ typedef struct VegsAdamArgs {
     int32_t zero_grad;
 } VegsAdamArgs;
 int vegs_adam_step(const VegsAdamArgs* args, void* stream);
+
+/*
+ * Normal-guidance loss on the covariance maps, value and both gradients in one pass (no
+ * counterpart inside the reference's extensions; it replaces the Python loss of
+ * loss/normal_guidance.py:3-23):
+ *   loss = w_rot * mean|Rot(q)^T n_w| + w_scale * mean|scale * (Rot(q)^T n_w)|,  n_w = R_cam2world n_cam,
+ * the rotation detached in the second term as the reference does.  cov_quat [4,H,W] (w,x,y,z planes),
+ * cov_scale [3,H,W], normal_cam [3,H,W] are device arrays; R_cam2world_host points at 9 HOST floats
+ * (row-major); loss is one device float; d_cov_quat [4,H,W] / d_cov_scale [3,H,W] receive
+ * dloss/dmap and may be NULL.  The reference uses w_rot = 0.8, w_scale = 0.2.
+ */
+int vegs_normal_guidance(int32_t W, int32_t H, const float* cov_quat, const float* cov_scale,
+                         const float* normal_cam, const float* R_cam2world_host, float w_rot, float w_scale,
+                         float* loss, float* d_cov_quat, float* d_cov_scale, void* stream);
 
 /*
  * Test / parity support: re-express the binning state in the reference's format

@@ -361,6 +361,95 @@ def test_view_parallel_trainer_single_gpu():
         assert torch.isfinite(v).all()
 
 
+def test_normal_guidance_loss_kernel_matches_the_reference_loss():
+    """vegs_b200.losses.loss_normal_guidance (one fused kernel: value + both gradient maps) against
+    the reference's Python loss restated in tests/vegs_caller.py (loss/normal_guidance.py:3-23) with
+    torch autograd, on maps rendered from a scene and on random maps with un-normalised quaternions."""
+    import vegs_caller as vc
+    from types import SimpleNamespace
+    from vegs_b200.losses import loss_normal_guidance
+    dev = torch.device("cuda")
+    g = torch.Generator().manual_seed(8)
+    H, W = 94, 352
+    R = np.array([[0.0, 0.0, 1.0], [-1.0, 0.0, 0.0], [0.0, -1.0, 0.0]]) @ synth.rot_x(7.0)
+    normal = torch.nn.functional.normalize(torch.randn(3, H, W, generator=g), dim=0).to(dev)
+    cam = SimpleNamespace(original_normal=normal, R=R)
+    scene = util.scene_with_specials(20000)
+    rendered = util.run_ours(scene, synth.make_camera(0, scale=0.25), want_state=False)
+    cases = [(torch.from_numpy(rendered["cov_quat"]), torch.from_numpy(rendered["cov_scale"])),
+             (torch.randn(4, H, W, generator=g) * 1.5, torch.randn(3, H, W, generator=g))]
+    for q0, s0 in cases:
+        qa, sa = q0.to(dev).clone().requires_grad_(True), s0.to(dev).clone().requires_grad_(True)
+        qb, sb = q0.to(dev).clone().requires_grad_(True), s0.to(dev).clone().requires_grad_(True)
+        la = vc.loss_normal_guidance(cam, qa, sa)
+        lb = loss_normal_guidance(cam, qb, sb)
+        assert abs(float(la) - float(lb)) <= 1e-6 * max(1.0, abs(float(la)))
+        (la * 3.0).backward(); (lb * 3.0).backward()
+        util.grad_close(qb.grad.cpu().numpy(), qa.grad.cpu().numpy(), "dloss/dcov_quat", rtol=1e-5)
+        util.grad_close(sb.grad.cpu().numpy(), sa.grad.cpu().numpy(), "dloss/dcov_scale", rtol=1e-5)
+        rel = ((qb.grad - qa.grad).abs() / qa.grad.abs().clamp_min(1e-9))[qa.grad.abs() > 1e-3 * qa.grad.abs().max()]
+        assert float(rel.median()) < 1e-5
+
+
+def test_live_map_gradients_are_the_weighted_map_cotangents():
+    """Opt-in live gradient of the covariance maps (RasterizerOptions.live_map_gradients).  The extra
+    terms are sum_pix w_j(pix) * cotangent(pix) with the rasterizer's own blending weights
+    w = alpha * T, and the colour image rendered from colors_precomp = v (background 0) is
+    sum_j w_j v_j with the very same weights, so for any per-Gaussian probe v:
+        sum_j <extra dL/dscale_j, v_j> = sum_pix <dL/dscale_map(pix), image_v(pix)>
+    and likewise for the rotations with the cotangent projected onto the tangent space of the
+    output quaternion.  Without the flag the map cotangents change nothing (the reference's
+    behaviour)."""
+    import vegs_b200.diff_gaussian_rasterization as dgr
+    dev = torch.device("cuda")
+    scene = util.scene_with_specials(30000)
+    cam = synth.make_camera(0, scale=0.25, device=dev)
+    P = scene["means3D"].shape[0]
+    rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, torch.zeros(3, device=dev), 1.0,
+                                           cam.viewmatrix, cam.projmatrix, 3, cam.campos, False, False)
+    gen = torch.Generator().manual_seed(4)
+    cs = torch.randn(3, cam.H, cam.W, generator=gen).to(dev)
+    cq = torch.randn(4, cam.H, cam.W, generator=gen).to(dev)
+
+    def grads(live, with_maps):
+        t = {k: v.to(dev).clone().requires_grad_(True) for k, v in scene.items()}
+        m2 = torch.zeros((P, 3), device=dev, requires_grad=True)
+        out = dgr.GaussianRasterizer(rs, live_map_gradients=live)(
+            means3D=t["means3D"], means2D=m2, opacities=t["opacities"], shs=t["shs"], scales=t["scales"],
+            rotations=t["rotations"])
+        loss = out[0].sum() * 0.5 + out[1].mean()
+        if with_maps:
+            loss = loss + (out[3] * cs).sum() + (out[2] * cq).sum()
+        loss.backward()
+        return {k: v.grad.detach() for k, v in t.items()}, [o.detach() for o in out]
+
+    base, _ = grads(False, False)
+    dead, outs = grads(False, True)
+    live, _ = grads(True, True)
+    for k in base:      # default: the map cotangents do not reach any gradient
+        util.grad_close(dead[k].cpu().numpy(), base[k].cpu().numpy(), f"default, {k}", rtol=1e-5)
+    for k in ("means3D", "shs", "opacities"):
+        util.grad_close(live[k].cpu().numpy(), base[k].cpu().numpy(), f"live, {k} unchanged", rtol=1e-5)
+    ds = (live["scales"] - base["scales"]).double()
+    dq = (live["rotations"] - base["rotations"]).double()
+    assert float(ds.abs().max()) > 0 and float(dq.abs().max()) > 0
+    n = outs[2].double()                                   # normalised output quaternion map
+    cq_t = cq.double() - n * (n * cq.double()).sum(0, keepdim=True)
+    for trial in range(3):
+        v = torch.rand(P, 4, generator=gen).to(dev)        # non-negative probes: colours are clamped nowhere
+        imgs = []
+        for cols in (v[:, :3], v[:, 1:]):
+            o = dgr.GaussianRasterizer(rs)(means3D=scene["means3D"].to(dev), means2D=torch.zeros((P, 3), device=dev),
+                                           opacities=scene["opacities"].to(dev), colors_precomp=cols.contiguous(),
+                                           scales=scene["scales"].to(dev), rotations=scene["rotations"].to(dev))
+            imgs.append(o[0].double())
+        img4 = torch.cat([imgs[0], imgs[1][2:3]], 0)       # sum_j w_j v_j for the four probe components
+        lhs_s = float((ds * v[:, :3].double()).sum()); rhs_s = float((cs.double() * img4[:3]).sum())
+        lhs_q = float((dq * v.double()).sum()); rhs_q = float((cq_t * img4).sum())
+        assert abs(lhs_s - rhs_s) <= 2e-4 * max(abs(rhs_s), 1.0), (lhs_s, rhs_s)
+        assert abs(lhs_q - rhs_q) <= 2e-4 * max(abs(rhs_q), 1.0), (lhs_q, rhs_q)
+
+
 def test_modes_colors_precomp_and_cov3d_precomp_against_oracle():
     scene = util.scene_with_specials(4000)
     cam = synth.make_camera(0, scale=0.125)

@@ -27,6 +27,7 @@ SOURCES = [
     "export.cu",
     "knn.cu",
     "adam.cu",
+    "normal_guidance.cu",
 ]
 
 NVCC_FLAGS = [

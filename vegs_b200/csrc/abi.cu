@@ -132,7 +132,8 @@ extern "C" size_t vegs_bin_scratch_bytes(int64_t R, int32_t W, int32_t H) {
     return bin_scratch_view(nullptr, R).bytes + 256;
 }
 extern "C" size_t vegs_bwd_scratch_bytes(int32_t P) {
-    return align_up((size_t)(P > 0 ? P : 1) * 48) + 256;
+    // 48 B per Gaussian of blend-stage accumulators + 32 B for the opt-in live map gradients
+    return align_up((size_t)(P > 0 ? P : 1) * 48) + align_up((size_t)(P > 0 ? P : 1) * 32) + 256;
 }
 
 static inline void* aligned(const void* p) {
@@ -266,11 +267,20 @@ extern "C" int vegs_backward(const VegsBackwardArgs* a, void* stream_) {
     prof_mark("__start", stream);
     VEGS_CUDA_OK(cudaMemsetAsync(acc, 0, (size_t)a->P * 48, stream));
     prof_mark("memset_bwd_acc", stream);
+    float4* map_acc = nullptr;
+    if (a->live_map_gradients) {
+        if (!a->out_cov_quat || a->cov3D_precomp) {
+            set_error("vegs_backward: live_map_gradients needs out_cov_quat and the scale / rotation inputs");
+            return VEGS_EINVAL;
+        }
+        map_acc = reinterpret_cast<float4*>(reinterpret_cast<char*>(acc) + align_up((size_t)a->P * 48));
+        VEGS_CUDA_OK(cudaMemsetAsync(map_acc, 0, (size_t)a->P * 32, stream));
+    }
     if (a->R > 0) {
-        rc = launch_composite_bwd(*a, g, im, b, acc, stream);
+        rc = launch_composite_bwd(*a, g, im, b, acc, map_acc, stream);
         if (rc) return rc;
     }
-    return launch_preprocess_bwd(*a, g, acc, stream);
+    return launch_preprocess_bwd(*a, g, acc, map_acc, stream);
 }
 
 extern "C" int vegs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,

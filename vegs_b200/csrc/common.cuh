@@ -268,11 +268,11 @@ int launch_composite_fwd(const VegsForwardArgs& a, const GeomView& g, const Scra
 
 // composite_bwd.cu
 int launch_composite_bwd(const VegsBackwardArgs& a, const GeomView& g, const ImgView& im,
-                         const BinView& b, float4* acc, cudaStream_t stream);
+                         const BinView& b, float4* acc, float4* map_acc, cudaStream_t stream);
 
 // preprocess_bwd.cu
 int launch_preprocess_bwd(const VegsBackwardArgs& a, const GeomView& g, const float4* acc,
-                          cudaStream_t stream);
+                          const float4* map_acc, cudaStream_t stream);
 
 // export.cu
 int launch_export(const VegsForwardArgs& a, const GeomView& g, const ScratchView& s,

@@ -61,6 +61,10 @@ struct BwdParams {
     const float* out_alpha;
     const float *dL_dcolor, *dL_ddepth, *dL_dalpha;
     float4* acc;
+    // opt-in live map gradients: cotangents of the scale / quaternion maps, the forward's
+    // normalised quaternion map, and the per-Gaussian accumulator [2P] (scale xyz | quaternion)
+    const float *dL_dscale_map, *dL_dquat_map, *out_quat;
+    float4* map_acc;
     uint32_t* tile_clocks;
     uint32_t* tile_dbg;
 };
@@ -69,6 +73,8 @@ struct BwdSmem {
     float2 M[32 * kSuper];          // [pixel][slot]: (alpha, v) after S0, (alpha*T, dL/dalpha) after S2
     float4 pix[32];                 // per pixel: dL/dcolor rgb, dL/ddepth
     float pixa[32];                 // per pixel: dL/dalpha map
+    float4 pixs[32];                // per pixel: dL/dscale map (live map gradients only)
+    float4 pixq[32];                // per pixel: dL/dquaternion map, projected onto the output's tangent space
     float agg[kWarps][3][32];       // [segment][prod 1/(1-alpha), a, b][pixel]: A_out = a + b * A_in
 };
 
@@ -121,6 +127,20 @@ __global__ void __launch_bounds__(kSuper, 3) composite_bwd_kernel(const BwdParam
     if (warp == 0) {
         sm.pix[lane] = make_float4(dpix0, dpix1, dpix2, dpix_depth);
         sm.pixa[lane] = dpix_alpha;
+        if (p.map_acc != nullptr) {
+            float4 ds = make_float4(0.f, 0.f, 0.f, 0.f), dq = ds;
+            if (inside) {
+                if (p.dL_dscale_map) ds = make_float4(p.dL_dscale_map[pid], p.dL_dscale_map[npix + pid], p.dL_dscale_map[2 * npix + pid], 0.f);
+                if (p.dL_dquat_map) {
+                    const float4 g = make_float4(p.dL_dquat_map[pid], p.dL_dquat_map[npix + pid], p.dL_dquat_map[2 * npix + pid], p.dL_dquat_map[3 * npix + pid]);
+                    const float4 n = make_float4(p.out_quat[pid], p.out_quat[npix + pid], p.out_quat[2 * npix + pid], p.out_quat[3 * npix + pid]);
+                    const float ng = n.x * g.x + n.y * g.y + n.z * g.z + n.w * g.w;
+                    dq = make_float4(g.x - n.x * ng, g.y - n.y * ng, g.z - n.z * ng, g.w - n.w * ng);
+                }
+            }
+            sm.pixs[lane] = ds;
+            sm.pixq[lane] = dq;
+        }
     }
     __syncthreads();
     const float bg_term = -T_final * (p.bg[0] * dpix0 + p.bg[1] * dpix1 + p.bg[2] * dpix2);
@@ -229,6 +249,8 @@ __global__ void __launch_bounds__(kSuper, 3) composite_bwd_kernel(const BwdParam
                 const float4 a = a_cur, bb = b_cur;
                 float g_mx = 0.f, g_my = 0.f, g_cxx = 0.f, g_cxy = 0.f, g_cyy = 0.f, g_op = 0.f;
                 float g_c0 = 0.f, g_c1 = 0.f, g_c2 = 0.f, g_dep = 0.f;
+                float g_s0 = 0.f, g_s1 = 0.f, g_s2 = 0.f, g_q0 = 0.f, g_q1 = 0.f, g_q2 = 0.f, g_q3 = 0.f;
+                const bool live = p.map_acc != nullptr;
                 bool any = false;
                 uint32_t bits = h;
                 while (bits != 0u) {
@@ -255,12 +277,22 @@ __global__ void __launch_bounds__(kSuper, 3) composite_bwd_kernel(const BwdParam
                     g_cxy += -0.5f * gdx * dy * dL_dG;
                     g_cyy += -0.5f * gdy * dy * dL_dG;
                     g_op += G * dL_dalpha;
+                    if (live) {
+                        const float4 ds = sm.pixs[q], dq = sm.pixq[q];
+                        g_s0 += wgt * ds.x; g_s1 += wgt * ds.y; g_s2 += wgt * ds.z;
+                        g_q0 += wgt * dq.x; g_q1 += wgt * dq.y; g_q2 += wgt * dq.z; g_q3 += wgt * dq.w;
+                    }
                 }
                 if (any) {
                     float4* dst = p.acc + 3 * (size_t)ent.x;
                     red_add_v4(dst + 0, g_mx, g_my, g_cxx, g_cxy);
                     red_add_v4(dst + 1, g_cyy, g_op, g_c0, g_c1);
                     red_add_v4(dst + 2, g_c2, g_dep, 0.0f, 0.0f);
+                    if (live) {
+                        float4* md = p.map_acc + 2 * (size_t)ent.x;
+                        red_add_v4(md + 0, g_s0, g_s1, g_s2, 0.0f);
+                        red_add_v4(md + 1, g_q0, g_q1, g_q2, g_q3);
+                    }
                 }
             }
         }
@@ -278,7 +310,7 @@ __global__ void __launch_bounds__(kSuper, 3) composite_bwd_kernel(const BwdParam
 }  // namespace
 
 int launch_composite_bwd(const VegsBackwardArgs& a, const GeomView& g, const ImgView& im,
-                         const BinView& b, float4* acc, cudaStream_t stream) {
+                         const BinView& b, float4* acc, float4* map_acc, cudaStream_t stream) {
     BwdParams p;
     p.ranges = im.ranges;
     p.hitlist = b.hitlist;
@@ -291,6 +323,8 @@ int launch_composite_bwd(const VegsBackwardArgs& a, const GeomView& g, const Img
     p.last_hit = im.last_hit;
     p.dL_dcolor = a.dL_dout_color; p.dL_ddepth = a.dL_dout_depth; p.dL_dalpha = a.dL_dout_alpha;
     p.acc = acc;
+    p.map_acc = map_acc;
+    p.dL_dscale_map = a.dL_dout_cov_scale; p.dL_dquat_map = a.dL_dout_cov_quat; p.out_quat = a.out_cov_quat;
     const int T = p.gx * ((a.H + kTile - 1) / kTile);
     p.tile_clocks = im.tile_clocks + T;
     p.tile_dbg = im.tile_dbg;

@@ -490,6 +490,14 @@ __global__ void __launch_bounds__(kPwThreads, 5) preprocess_bwd_kernel(const PbP
         }
     }
 
+    // ---- opt-in live gradient of the covariance maps (composite_bwd.cu), with respect to the
+    // activated scale / rotation like the terms above
+    if (p.map_acc != nullptr && visible && have_sr) {
+        const float4 ms = p.map_acc[2 * (size_t)idx], mq = p.map_acc[2 * (size_t)idx + 1];
+        dscale[0] += ms.x; dscale[1] += ms.y; dscale[2] += ms.z;
+        drot[0] += mq.x; drot[1] += mq.y; drot[2] += mq.z; drot[3] += mq.w;
+    }
+
     // ---- Jacobians of the fused activations (scene/gaussian_model.py:100-120 applied by the caller otherwise)
     float dm2_norm = 0.f;
     if (visible) {
@@ -572,7 +580,7 @@ __global__ void __launch_bounds__(kPwThreads, 5) preprocess_bwd_kernel(const PbP
 }  // namespace
 
 int launch_preprocess_bwd(const VegsBackwardArgs& a, const GeomView& g, const float4* acc,
-                          cudaStream_t stream) {
+                          const float4* map_acc, cudaStream_t stream) {
     PbParams p;
     p.P = a.P; p.D = a.D; p.M = a.M; p.W = a.W; p.H = a.H;
     p.means = a.means3D; p.radii = a.radii; p.shs = a.shs; p.shs_rest = a.shs_rest; p.clamped = g.clamped;
@@ -582,7 +590,7 @@ int launch_preprocess_bwd(const VegsBackwardArgs& a, const GeomView& g, const fl
     p.focal_x = a.W / (2.0f * a.tan_fovx);
     p.view = a.viewmatrix; p.proj = a.projmatrix; p.campos = a.campos;
     p.acc = acc;
-    p.map_acc = nullptr;
+    p.map_acc = map_acc;
     p.dL_dmeans3D = a.dL_dmeans3D; p.dL_dmeans2D = a.dL_dmeans2D; p.dL_dsh = a.dL_dsh; p.dL_dsh_rest = a.dL_dsh_rest;
     p.dL_dcolors = a.dL_dcolors; p.dL_dopacity = a.dL_dopacity; p.dL_dscales = a.dL_dscales;
     p.dL_drots = a.dL_drotations; p.dL_dcov3D = a.dL_dcov3D;

@@ -231,10 +231,18 @@ class RasterizerOptions:
         `xyz_gradient_accum += ||means2D.grad[:, :2]||`, `denom += 1`,
         `max_radii2D = max(., radii)` - what train.py:300-301 + add_densification_stats do in
         separate passes over all Gaussians.
+    live_map_gradients
+        CHANGES RESULTS, never default.  The reference computes a gradient of the covariance maps
+        (cov_quat, cov_scale) towards the Gaussians' rotations and scales and then overwrites it
+        (SURVEY.md Q1), so `loss_normal_guidance` trains nothing there; by default this package
+        reproduces that.  With this flag the cotangents of the two maps do reach `scales` and
+        `rotations`, with the blending weights held constant (see VegsBackwardArgs in
+        include/vegs_b200.h for the exact definition).
     """
-    __slots__ = ("fused_grad_accumulation", "densification_accumulators")
+    __slots__ = ("fused_grad_accumulation", "densification_accumulators", "live_map_gradients")
 
-    def __init__(self, fused_grad_accumulation=False, densification_accumulators=None):
+    def __init__(self, fused_grad_accumulation=False, densification_accumulators=None, live_map_gradients=False):
+        self.live_map_gradients = bool(live_map_gradients)
         if fused_grad_accumulation not in (False, True, "add", "assign"):
             raise ValueError("fused_grad_accumulation must be False, True / 'add', or 'assign'")
         self.fused_grad_accumulation = "add" if fused_grad_accumulation is True else fused_grad_accumulation
@@ -252,7 +260,8 @@ class RasterizerOptions:
 
     @property
     def any(self) -> bool:
-        return bool(self.fused_grad_accumulation) or self.densification_accumulators is not None
+        return bool(self.fused_grad_accumulation) or self.densification_accumulators is not None \
+            or self.live_map_gradients
 
 
 def _accum_target(t, shape, mode):
@@ -271,7 +280,7 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
                    scale_modifier, cov3Ds_precomp, viewmatrix, projmatrix, tanfovx, tanfovy,
                    grad_color, grad_depth, grad_cov_quat, grad_cov_scale, grad_alpha, sh, campos,
                    out_alpha, opacities_shape, debug, leaves=None, options=None, activations=0,
-                   opacities_raw=None, sh_rest=None):
+                   opacities_raw=None, sh_rest=None, out_cov_quat=None):
     lib = _lib.load()
     device = means3D.device
     P, M = st.P, st.M
@@ -370,6 +379,11 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
         b.opacities = _ptr(opacities_raw)
         b.shs_rest = _ptr(sh_rest)
         b.dL_dsh_rest = _ptr(dsh_rest)
+        if options is not None and options.live_map_gradients:
+            if out_cov_quat is None or not have_sr:
+                raise RuntimeError("live_map_gradients needs the scale / rotation inputs")
+            b.live_map_gradients = 1
+            b.out_cov_quat = out_cov_quat.data_ptr()
         if options is not None and options.densification_accumulators is not None:
             sg, sd, sr = options.densification_accumulators
             if sg.numel() != P or sg.device != device:
@@ -419,6 +433,7 @@ class _RasterizeGaussians(torch.autograd.Function):
                               alpha)
         # the input objects themselves, to find leaves whose .grad the backward may add into
         ctx.options = options if (options is not None and options.any) else None
+        ctx.cov_quat = cov_quat.detach() if (ctx.options is not None and ctx.options.live_map_gradients) else None
         ctx.leaves = dict(means3D=means3D, sh=sh, colors=colors_precomp, opacity=opacities, scales=scales,
                           rotations=rotations, cov3D=cov3Ds_precomp) \
             if (ctx.options is not None and ctx.options.fused_grad_accumulation) else None
@@ -437,13 +452,13 @@ class _RasterizeGaussians(torch.autograd.Function):
         if rs.debug:
             cpu_args = cpu_deep_copy_tuple(args[1:])
             try:
-                grads = _backward_impl(*args, leaves=ctx.leaves, options=ctx.options)
+                grads = _backward_impl(*args, leaves=ctx.leaves, options=ctx.options, out_cov_quat=ctx.cov_quat)
             except Exception as ex:
                 torch.save(cpu_args, "snapshot_bw.dump")
                 print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
                 raise ex
         else:
-            grads = _backward_impl(*args, leaves=ctx.leaves, options=ctx.options)
+            grads = _backward_impl(*args, leaves=ctx.leaves, options=ctx.options, out_cov_quat=ctx.cov_quat)
         (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales,
          grad_rotations, grad_cov3Ds_precomp) = grads
         return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities,
@@ -474,6 +489,7 @@ class _RasterizeGaussiansRaw(torch.autograd.Function):
         ctx.opacities_shape = tuple(opacity_raw.shape)
         ctx.save_for_backward(xyz, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw, radii, alpha)
         ctx.options = options if (options is not None and options.any) else None
+        ctx.cov_quat = cov_quat.detach() if (ctx.options is not None and ctx.options.live_map_gradients) else None
         ctx.leaves = dict(means3D=xyz, sh=features_dc, sh_rest=features_rest, opacity=opacity_raw,
                           scales=scaling_raw, rotations=rotation_raw) \
             if (ctx.options is not None and ctx.options.fused_grad_accumulation) else None
@@ -489,7 +505,7 @@ class _RasterizeGaussiansRaw(torch.autograd.Function):
                            rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color, grad_out_depth,
                            grad_out_cov_quat, grad_out_cov_scale, grad_out_alpha, f_dc, rs.campos, alpha,
                            ctx.opacities_shape, rs.debug, leaves=ctx.leaves, options=ctx.options,
-                           activations=_ACT_ALL, opacities_raw=opacity_raw, sh_rest=f_rest)
+                           activations=_ACT_ALL, opacities_raw=opacity_raw, sh_rest=f_rest, out_cov_quat=ctx.cov_quat)
         if len(g) == 8:                      # no higher-order coefficients: features_rest was empty
             g = g + (torch.zeros_like(f_rest),)
         g_xyz, g_m2d, g_dc, _gc, g_op, g_sc, g_rot, _gcov, g_rest = g
@@ -512,13 +528,14 @@ class GaussianRasterizationSettings(NamedTuple):
 
 
 class GaussianRasterizer(nn.Module):
-    def __init__(self, raster_settings, *, fused_grad_accumulation=False, densification_accumulators=None):
+    def __init__(self, raster_settings, *, fused_grad_accumulation=False, densification_accumulators=None,
+                 live_map_gradients=False):
         """`GaussianRasterizer(raster_settings)` is the reference's constructor (:195-198).  The two
         keyword-only arguments are this package's opt-in extensions for THIS instance; see
         RasterizerOptions."""
         super().__init__()
         self.raster_settings = raster_settings
-        self.options = RasterizerOptions(fused_grad_accumulation, densification_accumulators)
+        self.options = RasterizerOptions(fused_grad_accumulation, densification_accumulators, live_map_gradients)
 
     def markVisible(self, positions):
         """Boolean mask of the points in front of the near plane (view z > 0.2)."""
