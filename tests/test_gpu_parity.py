@@ -231,8 +231,10 @@ def test_forward_raw_equals_activations_plus_dropin(P, deg):
 
 def test_bulk_copy_paths_equal_the_load_paths():
     """The asynchronous bulk-copy staging of the per-Gaussian kernels (bulk.cuh) and the 16-byte-load
-    fallback must give bit-identical results: strided / offset views force the fallback (unaligned
-    bases), a Gaussian count that is not a multiple of 32 exercises the partial last warp."""
+    fallback must agree: offset views force the fallback (unaligned bases), a Gaussian count that
+    is not a multiple of 32 exercises the partial last warp.  Geometry (radii, depth, alpha) is
+    bit-identical; the SH colour is evaluated from registers on one path and from shared memory on
+    the other, where the compiler may contract a multiply-add differently: last-bit differences."""
     import vegs_b200.diff_gaussian_rasterization as dgr
     dev = torch.device("cuda")
     scene = util.scene_with_specials(40001)
@@ -256,7 +258,10 @@ def test_bulk_copy_paths_equal_the_load_paths():
     c = {k: torch.from_numpy(v).to(dev) for k, v in cot.items()}
     (sum((o * c[k]).sum() for o, k in zip(out[:5], ("color", "depth", "cov_quat", "cov_scale", "alpha")))).backward()
     for k, o in zip(("color", "depth", "cov_quat", "cov_scale", "alpha", "radii"), out):
-        assert np.array_equal(o.detach().cpu().numpy(), a[k]), k
+        if k == "color":
+            assert np.abs(o.detach().cpu().numpy() - a[k]).max() <= 1e-6, k
+        else:
+            assert np.array_equal(o.detach().cpu().numpy(), a[k]), k
     pairs = dict(means3D="means3D", sh="shs", opacities="opacities", scales="scales", rotations="rotations")
     for gk, tk in pairs.items():
         util.grad_close(shifted[tk].grad.cpu().numpy(), a["grads"][gk], f"grad {gk} (fallback vs bulk)", rtol=1e-5)
