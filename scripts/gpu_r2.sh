@@ -47,6 +47,18 @@ for s in "$@"; do
       echo "scale $N rc=$?" | tee -a $S
       timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29518 bench.py --impl reference --gpus $N --steps 4 --warmup 3 > gpurun_out/${tag}_scale_${N}_ref.json 2> gpurun_out/${tag}_scale_${N}_ref.err
       echo "scale ref $N rc=$?" | tee -a $S ;;
+    sweep)      # working-set size of the compositing kernels: VEGS_SWEEP="F:B F:B ..." (threads = candidates per set)
+      for fb in ${VEGS_SWEEP:-512:256 256:512 512:512}; do
+        F=${fb%%:*}; B=${fb##*:}
+        touch vegs_b200/csrc/composite_fwd.cu vegs_b200/csrc/composite_bwd.cu
+        VEGS_NVCC_EXTRA="-DVEGS_FWD_SUPER=$F -DVEGS_BWD_SUPER=$B" python vegs_b200/build.py > gpurun_out/${tag}_sweep_build_${F}_${B}.log 2>&1
+        timeout 600 python bench.py --steps 6 --warmup 3 --no-cpu-baseline --no-fused-leg > gpurun_out/${tag}_sweep_${F}_${B}.json 2> gpurun_out/${tag}_sweep_${F}_${B}.err
+        echo "sweep $F:$B rc=$? $(python -c "import json;d=json.load(open('gpurun_out/${tag}_sweep_${F}_${B}.json'));print(round(d['value'],1), {k: round(v['ms_per_view'],3) for k,v in d['kernels'].items()})" 2>&1 | tail -1)" | tee -a $S
+        timeout 900 python -m pytest tests -m gpu -q -x -k "against_oracle or golden or config3 or config5" -p no:cacheprovider > gpurun_out/${tag}_sweep_pytest_${F}_${B}.log 2>&1
+        echo "sweep pytest $F:$B rc=$? $(tail -1 gpurun_out/${tag}_sweep_pytest_${F}_${B}.log)" | tee -a $S
+      done
+      touch vegs_b200/csrc/composite_fwd.cu vegs_b200/csrc/composite_bwd.cu
+      python vegs_b200/build.py > gpurun_out/${tag}_sweep_build_default.log 2>&1 ;;
     bench_quick)
       timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench_quick rc=$?" | tee -a $S ;;
     configs)

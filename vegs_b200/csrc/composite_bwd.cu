@@ -47,7 +47,11 @@ __device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float
                  : "memory");
 }
 
-constexpr int kSuper = 256;                 // entries per working set = threads per CTA
+#ifndef VEGS_BWD_SUPER
+#define VEGS_BWD_SUPER 256
+#endif
+constexpr int kSuper = VEGS_BWD_SUPER;      // entries per working set = threads per CTA
+constexpr int kMinCtas = kSuper <= 256 ? 3 : 1;
 constexpr int kWarps = kSuper / 32;
 
 struct BwdParams {
@@ -78,6 +82,8 @@ struct BwdSmem {
     float agg[kWarps][3][32];       // [segment][prod 1/(1-alpha), a, b][pixel]: A_out = a + b * A_in
 };
 
+static_assert(sizeof(BwdSmem) <= 227 * 1024, "backward working set does not fit the 227 KB of shared memory per CTA");
+
 #if VEGS_TILE_DEBUG
 #define PHASE_INIT long long ph_t = clock64(), ph_acc[4] = {0, 0, 0, 0}
 #define PHASE_MARK(k) { long long now_; asm volatile("mov.u64 %0, %%clock64;" : "=l"(now_) :: "memory"); ph_acc[k] += now_ - ph_t; ph_t = now_; }
@@ -86,7 +92,7 @@ struct BwdSmem {
 #define PHASE_MARK(k)
 #endif
 
-__global__ void __launch_bounds__(kSuper, 3) composite_bwd_kernel(const BwdParams p) {
+__global__ void __launch_bounds__(kSuper, kMinCtas) composite_bwd_kernel(const BwdParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
 

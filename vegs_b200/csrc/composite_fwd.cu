@@ -53,7 +53,7 @@ namespace {
 #endif
 constexpr int kSuper = VEGS_FWD_SUPER;      // candidates per working set = threads per CTA
 constexpr int kWarps = kSuper / 32;
-constexpr int kMinCtas = kSuper == 256 ? 2 : 4;
+constexpr int kMinCtas = kSuper > 256 ? 1 : (kSuper == 256 ? 2 : 4);
 constexpr int kScanSub = 2;                 // list entries per thread and scan step
 constexpr int kScanStep = kScanSub * kSuper;
 constexpr int kRow = kSuper + 1;             // row stride of the pixel x slot matrix
@@ -87,6 +87,8 @@ struct FwdSmem {
     uint32_t scan_cnt[2][kScanSub * kWarps];   // survivors per (sub-step, warp) of a scan step (double-buffered)
     int all_done;
 };
+
+static_assert(sizeof(FwdSmem) <= 227 * 1024, "forward working set does not fit the 227 KB of shared memory per CTA");
 
 // sin and cos of x in [0, pi] (w * theta of the slerp: w in [0, 1], theta = acos(.)), ~1 ulp: one
 // Cody-Waite reduction to [-pi/4, pi/4] shared by both, Cephes single-precision polynomials.  The
