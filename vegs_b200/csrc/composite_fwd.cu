@@ -27,7 +27,8 @@
 //       saturation point (T(1-alpha) < 1e-4 stops the pixel, that Gaussian is not blended),
 //       n_contrib, plus the depth sum — branch-free rounds of four hits over dense arrays
 //   S3  pixel-parallel per 32-candidate segment (8 warps, lane = pixel): colour and scale sums and
-//       the slerp quaternion product of the segment's hits with the T values from S2
+//       the slerp quaternion product of the segment's hits, from the (1 - alpha, T) pairs S2 left
+//       in the matrix (no second exp per hit)
 //   S4  warps 0 and 1 fold the eight segment partials into the pixel state, in list order
 // so the expensive work (exp, sin, cos, quaternion product per contribution) is spread over 8
 // warps per pixel block and 64 warps per tile, the fixed costs of a working set are paid per 256
@@ -77,8 +78,8 @@ struct FwdParams {
 struct FwdSmem {
     float2 M[32 * kRow + 4];        // [pixel][slot], rows padded by one entry so that lanes reading the same
                                     // column of their own rows spread over the banks: (1 - alpha, depth * alpha)
-                                    // after S0; S2 replaces the first word by T, the transmittance before the hit
-    float4 A[kSuper], B[kSuper], C[kSuper], D[kSuper], E[kSuper];   // records of candidates with a hit
+                                    // after S0; S2 replaces the second word by T, the transmittance before the hit
+    float4 C[kSuper], D[kSuper], E[kSuper];   // blend records of candidates with a hit (colour, scale, rotation)
     uint2 ring[kRing];              // candidates in list order: (Gaussian id, ordinal in the tile's list)
     uint32_t bits[kWarps][32];      // [segment][pixel]: hits of the pixel inside the segment
     uint32_t stop_at[32];           // first (segment * 32 + hit index) the pixel does not blend (kSuper = none)
@@ -137,7 +138,6 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
     // lane = pixel (used by S2..S4)
     const int px = bx0 + (lane & 7), py = by0 + (lane >> 3);
     const bool inside = px < p.W && py < p.H;
-    const float pixfx = (float)px, pixfy = (float)py;
 
     const uint2 range = p.ranges[tile];
     const int n = (int)(range.y - range.x);
@@ -263,8 +263,6 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
             const float4 c_rec = ldg_f4(p.recC + (size_t)kGeomRecStride * id), d_rec = ldg_f4(p.recD + (size_t)kScratchRecStride * id), e_rec = ldg_f4(p.recE + (size_t)kScratchRecStride * id);
             h = entry_hits_fwd(a_cur, b_cur, bx0, by0, bx1, by1, sm.M, tid, kRow);
             if (h != 0u) {
-                sm.A[tid] = a_cur;
-                sm.B[tid] = b_cur;
                 sm.C[tid] = c_rec;
                 sm.D[tid] = d_rec;
                 sm.E[tid] = e_rec;
@@ -345,7 +343,9 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
                             const float test_T = __fmul_rn(T, active ? m[k].x : 1.0f);   // T * (1 - alpha)
                             // T(1 - alpha) < 1e-4: not blended, the pixel is finished (forward.cu:382-386)
                             const bool sat = active && test_T < 0.0001f;
-                            if (active && !sat) row[j].x = T;                // transmittance in front of this hit
+                            // transmittance in front of this hit, in the word whose depth * alpha
+                            // has just been consumed: S3 reads (1 - alpha, T) and needs no exp
+                            if (active && !sat) row[j].y = T;
                             // depth is accumulated here, in the reference's running order, so it
                             // stays bit-identical: depth values are ~1e2, re-associating that sum
                             // per segment already costs more than the 1e-5 tolerance
@@ -385,12 +385,11 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
                 const int t = warp * 32 + __ffs(bits) - 1;
                 bits &= bits - 1;
                 if ((uint32_t)(warp * 32 + j) >= stop) break;
-                const float4 a = sm.A[t];    // x, y, half2(ex, ey), depth
-                const float4 bb = sm.B[t];   // conic.a, conic.b, conic.c, opacity
-                float dx, dy;
-                const float power = pair_power(a, bb, pixfx, pixfy, dx, dy);
-                const float alpha = fminf(0.99f, __fmul_rn(bb.w, expf(power)));
-                const float Tb = sm.M[lane * kRow + warp * 32 + j].x;
+                // alpha from the stored 1 - alpha (exact to half an ulp of 1: 3e-8, far inside the 1e-5
+                // tolerance of the colour / scale / quaternion maps), T from the sequential pass
+                const float2 mt = sm.M[lane * kRow + warp * 32 + j];
+                const float alpha = __fsub_rn(1.0f, mt.x);
+                const float Tb = mt.y;
                 j++;
                 const float4 c = sm.C[t];    // r, g, b, 1 / sin(theta)
                 const float4 d = sm.D[t];    // scale xyz, rot.r
