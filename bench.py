@@ -224,7 +224,7 @@ def kernel_groups(prof):
     """Per-view milliseconds of each stage group from the library's event profile."""
     groups = {"preprocess_fwd": ["preprocess_fwd"],
               "binning": ["radix_hist", "radix_rowscan", "radix_scatter", "tile_count", "tile_spine", "emit",
-                          "tile_ranges", "memset_ranges", "num_rendered_d2h"],
+                          "tile_ranges", "tile_order", "memset_ranges", "memset_sort", "num_rendered_d2h"],
               "composite_fwd": ["composite_fwd"],
               "composite_bwd": ["composite_bwd", "memset_bwd_acc"],
               "preprocess_bwd": ["preprocess_bwd"]}

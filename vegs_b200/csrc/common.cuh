@@ -41,6 +41,14 @@ constexpr int kSortItemsPerThread = 16;
 constexpr int kSortTile = kSortThreads * kSortItemsPerThread;  // 4096 items per block
 constexpr int kRadixBits = 8;
 constexpr int kRadix = 1 << kRadixBits;
+constexpr int kSortMaxPasses = 4;           // 32-bit keys
+// Words of the sort's `hist` scratch for n items: per pass one 256-word status row per 4096-item
+// block (decoupled look-back; the three-kernel fallback uses the first pass's part as its block
+// histograms), then the global digit histograms of all passes and the dynamic block counters.
+static inline size_t sort_hist_words(size_t n) {
+    const size_t nblocks = (n + (size_t)kSortTile - 1) / (size_t)kSortTile;
+    return (size_t)kRadix * nblocks * kSortMaxPasses + (size_t)kSortMaxPasses * kRadix + 64;
+}
 
 // ---------------------------------------------------------------- emission configuration
 constexpr int kUnitsPerTile = 8;  // compositing units (8x4 pixel blocks) per 16x16 tile
@@ -146,7 +154,7 @@ static inline ScratchView scratch_view(void* base, int P) {
     v.keys1 = carve<uint32_t>(cur, n);
     v.vals0 = carve<uint32_t>(cur, n);
     v.vals1 = carve<uint32_t>(cur, n);
-    v.hist = carve<uint32_t>(cur, (size_t)kRadix * div_up(n, kSortTile));
+    v.hist = carve<uint32_t>(cur, sort_hist_words(n));
     v.rowtot = carve<uint32_t>(cur, kRadix);
     v.chunksum = carve<uint32_t>(cur, (size_t)div_up(n, kEmitChunk) + 1);
     v.partbase = carve<uint32_t>(cur, (size_t)div_up(n, kEmitChunk) + 1);
@@ -186,7 +194,7 @@ static inline BinScratchView bin_scratch_view(void* base, int64_t R) {
     v.tkeys0 = carve<uint32_t>(cur, n);
     v.tkeys1 = carve<uint32_t>(cur, n);
     v.tvals1 = carve<uint32_t>(cur, n);
-    v.hist = carve<uint32_t>(cur, (size_t)kRadix * div_up(n, kSortTile));
+    v.hist = carve<uint32_t>(cur, sort_hist_words(n));
     v.rowtot = carve<uint32_t>(cur, kRadix);
     v.bytes = (size_t)(cur - reinterpret_cast<char*>(base));
     return v;

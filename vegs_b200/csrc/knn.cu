@@ -50,7 +50,7 @@ KnnView knn_view(void* base, int P) {
     v.codes1 = carve<uint32_t>(cur, n);
     v.idx0 = carve<uint32_t>(cur, n);
     v.idx1 = carve<uint32_t>(cur, n);
-    v.hist = carve<uint32_t>(cur, (size_t)kRadix * div_up(n, kSortTile));
+    v.hist = carve<uint32_t>(cur, sort_hist_words(n));
     v.rowtot = carve<uint32_t>(cur, kRadix);
     v.pts = carve<float4>(cur, n);
     v.box1 = carve<float4>(cur, 2 * n1);
@@ -305,7 +305,8 @@ constexpr size_t kNoAllocScratchBytes = VEGS_DIST2_NOALLOC_SCRATCH_BYTES;
 // points + three box levels (each region rounded up to 256 B) must fit, plus the alignment slack
 constexpr size_t kNoAllocNeed =
     256 + (size_t)VEGS_DIST2_NOALLOC_MAX_POINTS * (4 * 4 + 16) +
-    (size_t)vegs::kRadix * 4 * ((VEGS_DIST2_NOALLOC_MAX_POINTS + vegs::kSortTile - 1) / vegs::kSortTile) + vegs::kRadix * 4 +
+    4 * (size_t)vegs::kRadix * vegs::kSortMaxPasses * ((VEGS_DIST2_NOALLOC_MAX_POINTS + vegs::kSortTile - 1) / vegs::kSortTile) +
+    4 * ((size_t)vegs::kSortMaxPasses * vegs::kRadix + 64) + vegs::kRadix * 4 +
     32 * ((size_t)VEGS_DIST2_NOALLOC_MAX_POINTS / 32 + VEGS_DIST2_NOALLOC_MAX_POINTS / 1024 + 16) + 16 * 256;
 static_assert(kNoAllocNeed <= kNoAllocScratchBytes,
               "VEGS_DIST2_NOALLOC_SCRATCH_BYTES cannot hold the workspace of VEGS_DIST2_NOALLOC_MAX_POINTS points");

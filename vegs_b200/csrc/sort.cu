@@ -8,12 +8,23 @@
 //   2. emit tile instances in that order and sort them by tile id only (ceil(log2 T / 8) passes
 //      over R items of 8 bytes instead of 6 passes over R items of 12 bytes).
 //
-// One pass = three kernels:
+// A sort = one histogram launch + one launch per pass ("onesweep" structure):
+//   radix_hist_all global digit histograms of ALL passes in one read of the keys
+//   radix_scatter  (one per pass) stable in-block ranking (warp ballots + per-warp counters),
+//                  staging of the block's 4096 items in digit order in shared memory, coalesced
+//                  scatter.  Where the block's items start inside each digit's output range - the
+//                  number of items with that digit in all EARLIER blocks - is found by a decoupled
+//                  look-back: blocks take their index from an atomic counter (so every block only
+//                  waits for blocks that are already running), publish their 256 digit counts
+//                  (flag "aggregate"), walk back over their predecessors' published words until
+//                  they meet an "inclusive" one, and publish their own inclusive prefix.  Value
+//                  and flag share one 32-bit word, so no fence is needed.
+// Fallback (VEGS_SORT_LOOKBACK=0, kept for A/B): three kernels per pass -
 //   radix_hist     per-block digit histogram, stored digit-major  hist[d * nblocks + b]
 //   radix_rowscan  one block per digit: exclusive scan of its row + row total
-//   radix_scatter  stable in-block ranking (warp ballots + per-warp counters), staging of the
-//                  block's 4096 items in digit order in shared memory, coalesced scatter
-// Roofline: HBM; algorithmic bytes per item per pass: 4 (hist) + 8 (read) + 8 (write).
+//   radix_scatter  as above with the offsets read from the scanned histogram.
+// Roofline: HBM; algorithmic bytes per item per pass: 8 (read) + 8 (write), + 4 once per sort.
+#include <cstdlib>
 #include "common.cuh"
 
 namespace vegs {
@@ -36,6 +47,25 @@ radix_hist_kernel(const uint32_t* __restrict__ keys, uint32_t n, int shift,
     __syncthreads();
     hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = s_hist[threadIdx.x];
 }
+
+// Global digit histograms of every pass of a sort in one read of the keys: ghist[pass * 256 + d].
+__global__ void __launch_bounds__(kSortThreads)
+radix_hist_all_kernel(const uint32_t* __restrict__ keys, uint32_t n, int passes, uint32_t* __restrict__ ghist) {
+    __shared__ uint32_t s_hist[kSortMaxPasses * kRadix];
+    for (int i = threadIdx.x; i < kSortMaxPasses * kRadix; i += kSortThreads) s_hist[i] = 0;
+    __syncthreads();
+    for (uint32_t i = blockIdx.x * (uint32_t)kSortThreads + threadIdx.x; i < n; i += gridDim.x * (uint32_t)kSortThreads) {
+        const uint32_t k = keys[i];
+#pragma unroll
+        for (int p = 0; p < kSortMaxPasses; p++)
+            if (p < passes) atomicAdd(&s_hist[p * kRadix + ((k >> (p * kRadixBits)) & (kRadix - 1))], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < passes * kRadix; i += kSortThreads)
+        if (s_hist[i] != 0u) atomicAdd(&ghist[i], s_hist[i]);
+}
+
+constexpr uint32_t kFlagAggregate = 1u << 30, kFlagInclusive = 2u << 30, kStatusValue = (1u << 30) - 1u;
 
 // Exclusive scan of 256 values held one per thread (blockDim.x == 256).
 __device__ __forceinline__ uint32_t block_exclusive_scan_256(uint32_t v, uint32_t* s_warp,
@@ -78,12 +108,15 @@ radix_rowscan_kernel(uint32_t* __restrict__ hist, uint32_t nblocks,
     if (threadIdx.x == 0) rowtot[blockIdx.x] = carry;
 }
 
-template <bool kImplicitVals, bool kWriteKeys>
+// kLookback: offsets by decoupled look-back (hist = this pass's status rows [nblocks][256], rowtot =
+// this pass's global digit histogram, counter = its dynamic block counter; all zero at launch);
+// otherwise from the scanned block histograms (hist digit-major, rowtot = digit totals).
+template <bool kImplicitVals, bool kWriteKeys, bool kLookback>
 __global__ void __launch_bounds__(kSortThreads, 4)
 radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                      uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint32_t n,
-                     int shift, const uint32_t* __restrict__ hist,
-                     const uint32_t* __restrict__ rowtot, uint32_t nblocks) {
+                     int shift, uint32_t* hist, const uint32_t* __restrict__ rowtot, uint32_t nblocks,
+                     uint32_t* counter) {
     constexpr int kWarps = kSortThreads / 32;
     constexpr int kWarpItems = kSortTile / kWarps;  // 512 consecutive items per warp
     __shared__ uint32_t s_keys[kSortTile];
@@ -94,11 +127,17 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
     __shared__ uint32_t s_warp[kWarps];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t base = blockIdx.x * (uint32_t)kSortTile;
-    const uint32_t count = min((uint32_t)kSortTile, n - base);
-
+    // look-back needs every predecessor to be running already: blocks number themselves in the
+    // order in which they start
+    if (kLookback) {
+        if (tid == 0) s_warp[0] = atomicAdd(counter, 1u);
+    }
     for (int i = tid; i < kWarps * kRadix; i += kSortThreads) (&s_whist[0][0])[i] = 0;
     __syncthreads();
+    const uint32_t bid = kLookback ? s_warp[0] : blockIdx.x;
+    const uint32_t base = bid * (uint32_t)kSortTile;
+    const uint32_t count = min((uint32_t)kSortTile, n - base);
+    __syncthreads();          // s_warp is reused by the scans below
 
     // ---- phase 1: rank every item inside (warp, digit), in item order
     uint32_t key[kSortItemsPerThread];
@@ -143,7 +182,29 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
         const uint32_t dbase = block_exclusive_scan_256(run, s_warp, nullptr);
         const uint32_t gdigit = block_exclusive_scan_256(rowtot[d], s_warp, nullptr);
         s_dbase[d] = dbase;
-        s_gbase[d] = gdigit + hist[(size_t)d * nblocks + blockIdx.x] - dbase;
+        uint32_t before;      // items with digit d in the blocks in front of this one
+        if (kLookback) {
+            volatile uint32_t* st = hist;
+            before = 0;
+            if (bid == 0) {
+                st[d] = kFlagInclusive | run;
+            } else {
+                st[(size_t)bid * kRadix + d] = kFlagAggregate | run;
+                uint32_t j = bid - 1;
+                for (;;) {
+                    const uint32_t v = st[(size_t)j * kRadix + d];
+                    const uint32_t flag = v & ~kStatusValue;
+                    if (flag == 0u) continue;                 // not published yet: look again
+                    before += v & kStatusValue;
+                    if (flag == kFlagInclusive) break;
+                    j--;                                      // block 0 always publishes "inclusive"
+                }
+                st[(size_t)bid * kRadix + d] = kFlagInclusive | (before + run);
+            }
+        } else {
+            before = hist[(size_t)d * nblocks + bid];
+        }
+        s_gbase[d] = gdigit + before - dbase;
     }
     __syncthreads();
 
@@ -172,6 +233,23 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
 
 }  // namespace
 
+static bool sort_lookback_enabled() {
+    static const bool on = [] { const char* e = getenv("VEGS_SORT_LOOKBACK"); return !(e != nullptr && e[0] == '0'); }();
+    return on;
+}
+
+template <bool kLookback>
+static void launch_scatter(bool first_implicit, bool write_keys, uint32_t nblocks, cudaStream_t stream,
+                           const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, uint32_t n,
+                           int shift, uint32_t* hist, const uint32_t* rowtot, uint32_t* counter) {
+    if (first_implicit)
+        radix_scatter_kernel<true, true, kLookback><<<nblocks, kSortThreads, 0, stream>>>(kin, vin, kout, vout, n, shift, hist, rowtot, nblocks, counter);
+    else if (write_keys)
+        radix_scatter_kernel<false, true, kLookback><<<nblocks, kSortThreads, 0, stream>>>(kin, vin, kout, vout, n, shift, hist, rowtot, nblocks, counter);
+    else
+        radix_scatter_kernel<false, false, kLookback><<<nblocks, kSortThreads, 0, stream>>>(kin, vin, kout, vout, n, shift, hist, rowtot, nblocks, counter);
+}
+
 int radix_sort_pairs(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, bool implicit_vals,
                      uint32_t n, int nbits, uint32_t* hist, uint32_t* rowtot, bool write_last_keys,
                      bool* result_in_second, cudaStream_t stream, bool debug) {
@@ -179,36 +257,52 @@ int radix_sort_pairs(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, boo
     if (n == 0 || nbits <= 0) return VEGS_OK;
     const uint32_t nblocks = div_up(n, kSortTile);
     const int passes = (nbits + kRadixBits - 1) / kRadixBits;
+    if (passes > kSortMaxPasses || n >= (1u << 30)) {
+        set_error("radix sort: at most %d passes and 2^30 items", kSortMaxPasses);
+        return VEGS_EINVAL;
+    }
     {
         // four 43 KB blocks per SM only fit with the shared-memory carve-out at its maximum
         static DeviceOnce once;
         int dev = 0;
         VEGS_CUDA_OK(cudaGetDevice(&dev));
         if (once.need(dev)) {
-            VEGS_CUDA_OK(cudaFuncSetAttribute(radix_scatter_kernel<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-            VEGS_CUDA_OK(cudaFuncSetAttribute(radix_scatter_kernel<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-            VEGS_CUDA_OK(cudaFuncSetAttribute(radix_scatter_kernel<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+            VEGS_CUDA_OK(cudaFuncSetAttribute(radix_scatter_kernel<true, true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+            VEGS_CUDA_OK(cudaFuncSetAttribute(radix_scatter_kernel<false, true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+            VEGS_CUDA_OK(cudaFuncSetAttribute(radix_scatter_kernel<false, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+            VEGS_CUDA_OK(cudaFuncSetAttribute(radix_scatter_kernel<true, true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+            VEGS_CUDA_OK(cudaFuncSetAttribute(radix_scatter_kernel<false, true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+            VEGS_CUDA_OK(cudaFuncSetAttribute(radix_scatter_kernel<false, false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
             once.done(dev);
         }
     }
+    const bool lookback = sort_lookback_enabled();
+    // layout of `hist` (sort_hist_words): status rows of every pass, global histograms, counters
+    const size_t status_words = (size_t)kRadix * nblocks;
+    uint32_t* ghist = hist + status_words * kSortMaxPasses;
+    uint32_t* counters = ghist + (size_t)kSortMaxPasses * kRadix;
     uint32_t *kin = k0, *vin = v0, *kout = k1, *vout = v1;
+    if (lookback) {
+        VEGS_CUDA_OK(cudaMemsetAsync(hist, 0, sort_hist_words(n) * sizeof(uint32_t), stream));
+        prof_mark("memset_sort", stream);
+        const uint32_t hb = nblocks < 148u * 8u ? nblocks : 148u * 8u;
+        radix_hist_all_kernel<<<hb, kSortThreads, 0, stream>>>(kin, n, passes, ghist);
+        VEGS_LAUNCH_CHECK("radix_hist", stream, debug);
+    }
     for (int p = 0; p < passes; p++) {
         const int shift = p * kRadixBits;
         const bool first_implicit = implicit_vals && p == 0;
         const bool write_keys = write_last_keys || p + 1 < passes;
-        radix_hist_kernel<<<nblocks, kSortThreads, 0, stream>>>(kin, n, shift, hist, nblocks);
-        VEGS_LAUNCH_CHECK("radix_hist", stream, debug);
-        radix_rowscan_kernel<<<kRadix, kSortThreads, 0, stream>>>(hist, nblocks, rowtot);
-        VEGS_LAUNCH_CHECK("radix_rowscan", stream, debug);
-        if (first_implicit) {
-            radix_scatter_kernel<true, true><<<nblocks, kSortThreads, 0, stream>>>(
-                kin, vin, kout, vout, n, shift, hist, rowtot, nblocks);
-        } else if (write_keys) {
-            radix_scatter_kernel<false, true><<<nblocks, kSortThreads, 0, stream>>>(
-                kin, vin, kout, vout, n, shift, hist, rowtot, nblocks);
+        if (lookback) {
+            launch_scatter<true>(first_implicit, write_keys, nblocks, stream, kin, vin, kout, vout, n, shift,
+                                 hist + status_words * p, ghist + (size_t)p * kRadix, counters + p);
         } else {
-            radix_scatter_kernel<false, false><<<nblocks, kSortThreads, 0, stream>>>(
-                kin, vin, kout, vout, n, shift, hist, rowtot, nblocks);
+            radix_hist_kernel<<<nblocks, kSortThreads, 0, stream>>>(kin, n, shift, hist, nblocks);
+            VEGS_LAUNCH_CHECK("radix_hist", stream, debug);
+            radix_rowscan_kernel<<<kRadix, kSortThreads, 0, stream>>>(hist, nblocks, rowtot);
+            VEGS_LAUNCH_CHECK("radix_rowscan", stream, debug);
+            launch_scatter<false>(first_implicit, write_keys, nblocks, stream, kin, vin, kout, vout, n, shift, hist,
+                                  rowtot, nullptr);
         }
         VEGS_LAUNCH_CHECK("radix_scatter", stream, debug);
         uint32_t* t;
