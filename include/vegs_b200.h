@@ -293,8 +293,9 @@ typedef struct VegsAdamArgs {
     VegsAdamSegment segments[VEGS_ADAM_MAX_SEGMENTS];
     int32_t num_segments;
     int32_t step;         /* t of the bias corrections, >= 1 */
-    float beta1, beta2, eps;
     int32_t zero_grad;
+    double beta1, beta2, eps;   /* doubles, as Python holds them: 1 - beta is formed in double and
+                                 * rounded to float once, which is what torch's kernels receive */
 } VegsAdamArgs;
 int vegs_adam_step(const VegsAdamArgs* args, void* stream);
 

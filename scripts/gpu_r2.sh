@@ -36,6 +36,8 @@ for s in "$@"; do
       grep -c libvegs_b200 gpurun_out/${tag}_bench_ref.err >> $S ;;
     bench_nobulk)   # A/B: the per-Gaussian kernels on their 16-byte-load paths instead of bulk copies
       VEGS_SH_BULK=0 timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-fused-leg > gpurun_out/${tag}_bench_nobulk.json 2> gpurun_out/${tag}_bench_nobulk.err; echo "bench_nobulk rc=$?" | tee -a $S ;;
+    bench_nolookback)   # A/B: three-kernel radix passes instead of the look-back scatter
+      VEGS_SORT_LOOKBACK=0 timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-fused-leg > gpurun_out/${tag}_bench_nolookback.json 2> gpurun_out/${tag}_bench_nolookback.err; echo "bench_nolookback rc=$?" | tee -a $S ;;
     tests_nobulk)
       VEGS_SH_BULK=0 timeout 600 python -m pytest tests -m gpu -q -x -k "against_oracle or golden or reference_live or forward_raw" -p no:cacheprovider > gpurun_out/${tag}_pytest_nobulk.log 2>&1
       echo "pytest[nobulk] rc=$? $(tail -1 gpurun_out/${tag}_pytest_nobulk.log)" | tee -a $S ;;

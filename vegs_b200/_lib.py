@@ -69,7 +69,7 @@ class VegsAdamSegment(C.Structure):
 
 class VegsAdamArgs(C.Structure):
     _fields_ = [("segments", VegsAdamSegment * ADAM_MAX_SEGMENTS), ("num_segments", C.c_int32), ("step", C.c_int32),
-                ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("zero_grad", C.c_int32)]
+                ("zero_grad", C.c_int32), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double)]
 
 
 # name -> (restype, argtypes); the list doubles as the symbol inventory checked by the tests

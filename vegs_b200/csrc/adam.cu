@@ -41,13 +41,14 @@ struct AdamParams {
     int nseg;
     unsigned long long total;
     float beta1, beta2, eps, sqrt_bc2;
+    float omb1, omb2;    // 1 - beta, formed in double as torch forms them
     int zero_grad;
 };
 
 __device__ __forceinline__ void adam_elem(float& p, float g, float& m, float& v, const AdamParams& a, float step_size) {
     // lerp_(g, 1 - b1); mul_(b2).addcmul_(g, g, 1 - b2); sqrt() / sqrt(bc2) + eps; addcdiv_(m, denom, -step_size)
-    m = __fmaf_rn(1.0f - a.beta1, g - m, m);
-    v = __fmaf_rn((1.0f - a.beta2) * g, g, __fmul_rn(v, a.beta2));
+    m = __fmaf_rn(a.omb1, g - m, m);
+    v = __fmaf_rn(a.omb2 * g, g, __fmul_rn(v, a.beta2));
     const float denom = __fadd_rn(__fdiv_rn(sqrtf(v), a.sqrt_bc2), a.eps);
     p = __fmaf_rn(-step_size, __fdiv_rn(m, denom), p);
 }
@@ -119,10 +120,12 @@ extern "C" int vegs_adam_step(const VegsAdamArgs* args, void* stream_) {
     }
     AdamParams a;
     a.nseg = 0;
-    a.beta1 = args->beta1; a.beta2 = args->beta2; a.eps = args->eps;
-    const double bc1 = 1.0 - std::pow((double)args->beta1, (double)args->step);
-    const double bc2 = 1.0 - std::pow((double)args->beta2, (double)args->step);
+    a.beta1 = (float)args->beta1; a.beta2 = (float)args->beta2; a.eps = (float)args->eps;
+    const double bc1 = 1.0 - std::pow(args->beta1, (double)args->step);
+    const double bc2 = 1.0 - std::pow(args->beta2, (double)args->step);
     a.sqrt_bc2 = (float)std::sqrt(bc2);
+    a.omb1 = (float)(1.0 - args->beta1);
+    a.omb2 = (float)(1.0 - args->beta2);
     a.zero_grad = args->zero_grad;
     for (int i = 0; i < VEGS_ADAM_MAX_SEGMENTS; i++) a.group_begin[i] = 0;
     unsigned long long flat = 0, groups = 0;
