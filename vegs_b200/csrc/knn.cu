@@ -20,6 +20,7 @@
 // Roofline: latency / L2-gather bound; algorithmic HBM bytes 16 per point.
 #include <algorithm>
 #include <cfloat>
+#include <cstdlib>
 #include <mutex>
 #include "common.cuh"
 
@@ -232,6 +233,99 @@ knn3_kernel(uint32_t P, const float4* __restrict__ pts, const float4* __restrict
     out[__float_as_uint(self.w)] = (best[0] + best[1] + best[2]) / 3.0f;
 }
 
+// Lower bound (same float arithmetic) of point_dist2 between ANY point of box g and ANY point of
+// box c: per axis the gap between the boxes (0 when they overlap); float subtraction, squaring and
+// fma are monotone, so the bound never exceeds the computed distance of a pair it covers.
+__device__ __forceinline__ float box_box_dist2(const float4& gmn, const float4& gmx, const float4& cmn, const float4& cmx) {
+    const float dx = fmaxf(0.f, fmaxf(__fsub_rn(cmn.x, gmx.x), __fsub_rn(gmn.x, cmx.x)));
+    const float dy = fmaxf(0.f, fmaxf(__fsub_rn(cmn.y, gmx.y), __fsub_rn(gmn.y, cmx.y)));
+    const float dz = fmaxf(0.f, fmaxf(__fsub_rn(cmn.z, gmx.z), __fsub_rn(gmn.z, cmx.z)));
+    return __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+}
+
+// Warp-cooperative search: one warp answers 32 consecutive queries of the sorted order (spatial
+// neighbours) TOGETHER.  The hierarchy is walked once per warp with the queries' common bounding
+// box and the largest of their current third-best distances as the pruning bound, 32 child boxes
+// tested by the 32 lanes at a time; a surviving leaf's 32 points are loaded by one coalesced read
+// and handed round with shuffles, every lane updating its own three best.  Compared with one
+// private traversal per thread (knn3_kernel) the lanes never diverge and a box test is paid once
+// per warp instead of once per query.  The pairs evaluated are a superset of each query's own, the
+// distance arithmetic is the same, so the three smallest values per query are identical.
+__global__ void __launch_bounds__(128)
+knn3_warp_kernel(uint32_t P, const float4* __restrict__ pts, const float4* __restrict__ box1,
+                 uint32_t n1, const float4* __restrict__ box2, uint32_t n2,
+                 const float4* __restrict__ box3, uint32_t n3, float* __restrict__ out) {
+    const uint32_t i = blockIdx.x * 128u + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const uint32_t warp_first = i - lane;
+    if (warp_first >= P) return;
+    const bool active = i < P;
+    const float4 self = pts[active ? i : P - 1];
+    float best[3] = {FLT_MAX, FLT_MAX, FLT_MAX};
+    if (active) {
+        const uint32_t lo = i >= 3 ? i - 3 : 0u;
+        const uint32_t hi = min(P - 1, i + 3);
+        for (uint32_t k = lo; k <= hi; k++)
+            if (k != i) update3(best, point_dist2(self, pts[k]));
+    }
+    // the seed only provides the pruning bound; the search below counts every point once
+    const float seed = active ? best[2] : 0.f;
+    best[0] = best[1] = best[2] = FLT_MAX;
+    // the queries' common box (inactive lanes of a partial last warp stay out of it)
+    float4 gmn = make_float4(active ? self.x : FLT_MAX, active ? self.y : FLT_MAX, active ? self.z : FLT_MAX, 0.f);
+    float4 gmx = make_float4(active ? self.x : -FLT_MAX, active ? self.y : -FLT_MAX, active ? self.z : -FLT_MAX, 0.f);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        gmn.x = fminf(gmn.x, __shfl_xor_sync(0xffffffffu, gmn.x, o)); gmx.x = fmaxf(gmx.x, __shfl_xor_sync(0xffffffffu, gmx.x, o));
+        gmn.y = fminf(gmn.y, __shfl_xor_sync(0xffffffffu, gmn.y, o)); gmx.y = fmaxf(gmx.y, __shfl_xor_sync(0xffffffffu, gmx.y, o));
+        gmn.z = fminf(gmn.z, __shfl_xor_sync(0xffffffffu, gmn.z, o)); gmx.z = fmaxf(gmx.z, __shfl_xor_sync(0xffffffffu, gmx.z, o));
+    }
+    // pruning bound of the warp: the largest "third best so far" of its queries (non-negative floats
+    // order like their bit patterns)
+    auto group_bound = [&]() {
+        const float mine = active ? fminf(seed, best[2]) : 0.f;
+        return __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(mine)));
+    };
+    float bound = group_bound();
+    for (uint32_t c3 = 0; c3 < n3; c3 += 32) {
+        const uint32_t b3 = c3 + lane;
+        bool hit3 = b3 < n3 && !(box_box_dist2(gmn, gmx, box3[2 * b3], box3[2 * b3 + 1]) > bound);
+        uint32_t m3 = __ballot_sync(0xffffffffu, hit3);
+        while (m3 != 0u) {
+            const uint32_t p3 = c3 + (uint32_t)(__ffs(m3) - 1);
+            m3 &= m3 - 1;
+            const uint32_t b2 = p3 * kFan + lane;
+            bool hit2 = b2 < n2 && !(box_box_dist2(gmn, gmx, box2[2 * b2], box2[2 * b2 + 1]) > bound);
+            uint32_t m2 = __ballot_sync(0xffffffffu, hit2);
+            while (m2 != 0u) {
+                const uint32_t p2 = p3 * kFan + (uint32_t)(__ffs(m2) - 1);
+                m2 &= m2 - 1;
+                const uint32_t b1 = p2 * kFan + lane;
+                bool hit1 = b1 < n1 && !(box_box_dist2(gmn, gmx, box1[2 * (size_t)b1], box1[2 * (size_t)b1 + 1]) > bound);
+                uint32_t m1 = __ballot_sync(0xffffffffu, hit1);
+                while (m1 != 0u) {
+                    const uint32_t p1 = p2 * kFan + (uint32_t)(__ffs(m1) - 1);
+                    m1 &= m1 - 1;
+                    // the bound may have tightened since the ballot: test this leaf again
+                    if (box_box_dist2(gmn, gmx, box1[2 * (size_t)p1], box1[2 * (size_t)p1 + 1]) > bound) continue;
+                    const uint32_t k0 = p1 * kFan;
+                    const uint32_t cnt = min((uint32_t)kFan, P - k0);
+                    const float4 mine = pts[min(k0 + (uint32_t)lane, P - 1)];
+                    for (uint32_t t = 0; t < cnt; t++) {
+                        float4 o;
+                        o.x = __shfl_sync(0xffffffffu, mine.x, (int)t);
+                        o.y = __shfl_sync(0xffffffffu, mine.y, (int)t);
+                        o.z = __shfl_sync(0xffffffffu, mine.z, (int)t);
+                        if (active && k0 + t != i) update3(best, point_dist2(self, o));
+                    }
+                    bound = group_bound();
+                }
+            }
+        }
+    }
+    if (active) out[__float_as_uint(self.w)] = (best[0] + best[1] + best[2]) / 3.0f;
+}
+
 }  // namespace
 
 }  // namespace vegs
@@ -279,7 +373,9 @@ extern "C" int vegs_dist2(int32_t P, const float* points, float* out, void* work
     VEGS_LAUNCH_CHECK("build_boxes2", stream, false);
     build_boxes_kernel<false><<<div_up((uint64_t)n3 * 32, 256), 256, 0, stream>>>(n2, v.box2, n3, v.box3);
     VEGS_LAUNCH_CHECK("build_boxes3", stream, false);
-    knn3_kernel<<<div_up(n, 128), 128, 0, stream>>>(n, v.pts, v.box1, n1, v.box2, n2, v.box3, n3, out);
+    static const bool per_thread = [] { const char* e = getenv("VEGS_KNN_WARP"); return e != nullptr && e[0] == '0'; }();
+    if (per_thread) knn3_kernel<<<div_up(n, 128), 128, 0, stream>>>(n, v.pts, v.box1, n1, v.box2, n2, v.box3, n3, out);
+    else knn3_warp_kernel<<<div_up(n, 128), 128, 0, stream>>>(n, v.pts, v.box1, n1, v.box2, n2, v.box3, n3, out);
     VEGS_LAUNCH_CHECK("knn3", stream, false);
     return VEGS_OK;
 }
