@@ -11,11 +11,13 @@
 //   1. bounding box by atomic min/max on order-preserving integer images of the floats
 //   2. 30-bit Morton codes, radix sort (sort.cu), points gathered into sorted order
 //   3. three levels of AABBs over runs of 32 / 1024 / 32768 consecutive sorted points
-//   4. one thread per point (in sorted order, so a warp's 32 queries are neighbours and traverse
-//      the same boxes): seed the bound with the +-3 sorted neighbours as the reference does, then
-//      descend L3 -> L2 -> L1 -> points, pruning a box when its distance exceeds the current third
-//      best.  The box distance uses the same fma order on component-wise smaller magnitudes, so it
-//      never exceeds the computed distance of a point inside the box: pruning is exact in float.
+//   4. one WARP per 32 consecutive points of the sorted order (spatial neighbours): seed each
+//      query's bound with its +-3 sorted neighbours as the reference does, then descend
+//      L3 -> L2 -> L1 -> points ONCE for the whole warp, with the queries' common box and the
+//      largest of their third-best distances as the bound - 32 child boxes tested by the 32 lanes,
+//      a leaf's 32 points read coalesced and handed round by shuffles (knn3_warp_kernel).  The box
+//      distance uses the same fma order on component-wise smaller magnitudes, so it never exceeds
+//      the computed distance of a pair it covers: pruning is exact in float.
 // The reference tests every one of the P/1024 boxes from every thread (3.5e10 tests at 6 M points).
 // Roofline: latency / L2-gather bound; algorithmic HBM bytes 16 per point.
 #include <algorithm>
