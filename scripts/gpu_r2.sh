@@ -63,6 +63,8 @@ for s in "$@"; do
       done
       touch vegs_b200/csrc/composite_fwd.cu vegs_b200/csrc/composite_bwd.cu
       python vegs_b200/build.py > gpurun_out/${tag}_sweep_build_default.log 2>&1 ;;
+    tilestats)  # per-tile cycles of the compositing kernels (default build: clocks only)
+      timeout 600 python scripts/tile_stats.py 6000000 gpurun_out/${tag}_tile_stats.npz > gpurun_out/${tag}_tile_stats.log 2>&1; echo "tilestats rc=$?" | tee -a $S ;;
     bench_quick)
       timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench_quick rc=$?" | tee -a $S ;;
     configs)
