@@ -73,6 +73,23 @@ def test_against_oracle(P, scale, deg):
     _check_grads(ours, ref["grads"], rtol=3e-3)
 
 
+@pytest.mark.parametrize("M,deg", [(1, 0), (4, 1), (9, 2), (12, 2)])
+def test_sh_coefficient_counts_other_than_16(M, deg):
+    """SH rows of 12, 48, 108 and 144 bytes: M = 4 and 12 take the bulk-copy row path of the
+    per-Gaussian kernels with a run-time row length, M = 1 and 9 (rows that are not a multiple of
+    16 bytes) the 16-byte-load path; an odd Gaussian count adds a partial last warp."""
+    scene = util.scene_with_specials(6001)
+    scene = dict(scene, shs=scene["shs"][:, :M].contiguous())
+    cam = synth.make_camera(0, scale=0.125)
+    cot = util.np_cotangents(cam.W, cam.H)
+    ours = util.run_ours(scene, cam, sh_degree=deg, cot=cot)
+    ref = util.run_oracle(scene, cam, sh_degree=deg, cot=cot)
+    _check_state_exact(ours, ref, ref["radii"] > 0)
+    _check_images(ours, ref, strict=False)
+    _check_grads(ours, ref["grads"], rtol=3e-3)
+    assert ours["grads"]["sh"].shape == (scene["means3D"].shape[0], M, 3)
+
+
 def test_against_oracle_plain_id_lists():
     """Scenes with P >= 2^24 cannot carry the unit masks in the list words; the per-entry box-test path
     they take is forced here at a small size and must give the same result as the default path."""
