@@ -50,7 +50,11 @@ for s in "$@"; do
       timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29518 bench.py --impl reference --gpus $N --steps 4 --warmup 3 > gpurun_out/${tag}_scale_${N}_ref.json 2> gpurun_out/${tag}_scale_${N}_ref.err
       echo "scale ref $N rc=$?" | tee -a $S
       timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29519 scripts/nccl_busbw.py > gpurun_out/${tag}_nccl_busbw_$N.json 2> gpurun_out/${tag}_nccl_busbw_$N.err
-      echo "nccl busbw $N rc=$? $(cat gpurun_out/${tag}_nccl_busbw_$N.json)" | tee -a $S ;;
+      echo "nccl busbw $N rc=$? $(cat gpurun_out/${tag}_nccl_busbw_$N.json)" | tee -a $S
+      for algo in NVLS Ring Tree; do
+        NCCL_ALGO=$algo timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29520 scripts/nccl_busbw.py > gpurun_out/${tag}_nccl_busbw_${N}_$algo.json 2> gpurun_out/${tag}_nccl_busbw_${N}_$algo.err
+        echo "nccl busbw $N NCCL_ALGO=$algo rc=$? $(cat gpurun_out/${tag}_nccl_busbw_${N}_$algo.json)" | tee -a $S
+      done ;;
     sweep)      # working-set size of the compositing kernels: VEGS_SWEEP="F:B F:B ..." (threads = candidates per set)
       for fb in ${VEGS_SWEEP:-512:256 256:512 512:512}; do
         F=${fb%%:*}; B=${fb##*:}
