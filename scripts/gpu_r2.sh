@@ -69,6 +69,19 @@ for s in "$@"; do
       python vegs_b200/build.py > gpurun_out/${tag}_sweep_build_default.log 2>&1 ;;
     tilestats)  # per-tile cycles of the compositing kernels (default build: clocks only)
       timeout 600 python scripts/tile_stats.py 6000000 gpurun_out/${tag}_tile_stats.npz > gpurun_out/${tag}_tile_stats.log 2>&1; echo "tilestats rc=$?" | tee -a $S ;;
+    flags)      # A/B of build flags: VEGS_FLAG_SETS="name=-DA=1 -DB=2;name2=-DC=1" (each: rebuild, bench, parity tests)
+      IFS=';' read -ra SETS <<< "${VEGS_FLAG_SETS:-bulklist=-DVEGS_FWD_BULK_LIST=1}"
+      for fs in "${SETS[@]}"; do
+        NAME=${fs%%=*}; FL=${fs#*=}
+        touch vegs_b200/csrc/*.cu
+        VEGS_NVCC_EXTRA="$FL" python vegs_b200/build.py > gpurun_out/${tag}_flags_build_${NAME}.log 2>&1
+        timeout 600 python bench.py --steps 6 --warmup 3 --no-cpu-baseline --no-fused-leg > gpurun_out/${tag}_flags_${NAME}.json 2> gpurun_out/${tag}_flags_${NAME}.err
+        echo "flags $NAME [$FL] rc=$? $(python -c "import json;d=json.load(open('gpurun_out/${tag}_flags_${NAME}.json'));print(round(d['value'],1), {k: round(v['ms_per_view'],3) for k,v in d['kernels'].items()})" 2>&1 | tail -1)" | tee -a $S
+        timeout 900 python -m pytest tests -m gpu -q -x -k "against_oracle or golden or config3 or config5" -p no:cacheprovider > gpurun_out/${tag}_flags_pytest_${NAME}.log 2>&1
+        echo "flags pytest $NAME rc=$? $(tail -1 gpurun_out/${tag}_flags_pytest_${NAME}.log)" | tee -a $S
+      done
+      touch vegs_b200/csrc/*.cu
+      python vegs_b200/build.py > gpurun_out/${tag}_flags_build_default.log 2>&1 ;;
     bench_quick)
       timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench_quick rc=$?" | tee -a $S ;;
     configs)
