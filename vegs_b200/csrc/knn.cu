@@ -11,13 +11,17 @@
 //   1. bounding box by atomic min/max on order-preserving integer images of the floats
 //   2. 30-bit Morton codes, radix sort (sort.cu), points gathered into sorted order
 //   3. three levels of AABBs over runs of 32 / 1024 / 32768 consecutive sorted points
-//   4. one WARP per 32 consecutive points of the sorted order (spatial neighbours): seed each
-//      query's bound with its +-3 sorted neighbours as the reference does, then descend
-//      L3 -> L2 -> L1 -> points ONCE for the whole warp, with the queries' common box and the
-//      largest of their third-best distances as the bound - 32 child boxes tested by the 32 lanes,
-//      a leaf's 32 points read coalesced and handed round by shuffles (knn3_warp_kernel).  The box
-//      distance uses the same fma order on component-wise smaller magnitudes, so it never exceeds
-//      the computed distance of a pair it covers: pruning is exact in float.
+//   4. one thread per point (in sorted order, so a warp's 32 queries are neighbours and traverse
+//      the same boxes): seed the bound with the +-3 sorted neighbours as the reference does, then
+//      descend L3 -> L2 -> L1 -> points, pruning a box when its distance exceeds the current third
+//      best.  The box distance uses the same fma order on component-wise smaller magnitudes, so it
+//      never exceeds the computed distance of a point inside the box: pruning is exact in float.
+//      (A warp-cooperative variant - one traversal per 32 queries with their common box and the
+//      largest of their bounds, leaf points handed round by shuffles, knn3_warp_kernel,
+//      VEGS_KNN_WARP=1 - gives identical results but measured 4x slower at LiDAR density: the
+//      shared bound is much looser than each query's own, and every visited leaf costs all 32
+//      lanes 32 evaluations.  ncu of the per-thread kernel: 86 % issue utilisation, 16 of 32 lanes
+//      active, 12.6 G warp instructions for 6 M queries.)
 // The reference tests every one of the P/1024 boxes from every thread (3.5e10 tests at 6 M points).
 // Roofline: latency / L2-gather bound; algorithmic HBM bytes 16 per point.
 #include <algorithm>
@@ -245,8 +249,9 @@ __device__ __forceinline__ float box_box_dist2(const float4& gmn, const float4& 
     return __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
 }
 
-// Warp-cooperative search: one warp answers 32 consecutive queries of the sorted order (spatial
-// neighbours) TOGETHER.  The hierarchy is walked once per warp with the queries' common bounding
+// Warp-cooperative search (opt-in experiment, slower than knn3_kernel on the benchmark scene, see
+// the header): one warp answers 32 consecutive queries of the sorted order (spatial neighbours)
+// TOGETHER.  The hierarchy is walked once per warp with the queries' common bounding
 // box and the largest of their current third-best distances as the pruning bound, 32 child boxes
 // tested by the 32 lanes at a time; a surviving leaf's 32 points are loaded by one coalesced read
 // and handed round with shuffles, every lane updating its own three best.  Compared with one
@@ -375,7 +380,8 @@ extern "C" int vegs_dist2(int32_t P, const float* points, float* out, void* work
     VEGS_LAUNCH_CHECK("build_boxes2", stream, false);
     build_boxes_kernel<false><<<div_up((uint64_t)n3 * 32, 256), 256, 0, stream>>>(n2, v.box2, n3, v.box3);
     VEGS_LAUNCH_CHECK("build_boxes3", stream, false);
-    static const bool per_thread = [] { const char* e = getenv("VEGS_KNN_WARP"); return e != nullptr && e[0] == '0'; }();
+    // measured at 6 M points: per-thread traversal 13.4 ms, warp-cooperative 52 ms (below) - default per thread
+    static const bool per_thread = [] { const char* e = getenv("VEGS_KNN_WARP"); return !(e != nullptr && e[0] == '1'); }();
     if (per_thread) knn3_kernel<<<div_up(n, 128), 128, 0, stream>>>(n, v.pts, v.box1, n1, v.box2, n2, v.box3, n3, out);
     else knn3_warp_kernel<<<div_up(n, 128), 128, 0, stream>>>(n, v.pts, v.box1, n1, v.box2, n2, v.box3, n3, out);
     VEGS_LAUNCH_CHECK("knn3", stream, false);

@@ -8,7 +8,12 @@
 //   2. emit tile instances in that order and sort them by tile id only (ceil(log2 T / 8) passes
 //      over R items of 8 bytes instead of 6 passes over R items of 12 bytes).
 //
-// A sort = one histogram launch + one launch per pass ("onesweep" structure):
+// Two ways to run a pass; measured on the 6 M scene (profiles/r02d_bench*.json): the three-kernel
+// pass below is the default - all radix launches of a view take 0.53 ms with it against 0.62 ms
+// with the look-back scatter (which saves the histogram and row-scan launches, 0.09 ms, but whose
+// scatter launches grow from 0.38 to 0.55 ms: the chained waits of 1 500 - 3 100 blocks on their
+// predecessors' published counts cost more than the extra read of the keys).
+// VEGS_SORT_LOOKBACK=1 selects: one histogram launch + one launch per pass ("onesweep" structure):
 //   radix_hist_all global digit histograms of ALL passes in one read of the keys
 //   radix_scatter  (one per pass) stable in-block ranking (warp ballots + per-warp counters),
 //                  staging of the block's 4096 items in digit order in shared memory, coalesced
@@ -19,7 +24,7 @@
 //                  (flag "aggregate"), walk back over their predecessors' published words until
 //                  they meet an "inclusive" one, and publish their own inclusive prefix.  Value
 //                  and flag share one 32-bit word, so no fence is needed.
-// Fallback (VEGS_SORT_LOOKBACK=0, kept for A/B): three kernels per pass -
+// Default: three kernels per pass -
 //   radix_hist     per-block digit histogram, stored digit-major  hist[d * nblocks + b]
 //   radix_rowscan  one block per digit: exclusive scan of its row + row total
 //   radix_scatter  as above with the offsets read from the scanned histogram.
@@ -234,7 +239,7 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
 }  // namespace
 
 static bool sort_lookback_enabled() {
-    static const bool on = [] { const char* e = getenv("VEGS_SORT_LOOKBACK"); return !(e != nullptr && e[0] == '0'); }();
+    static const bool on = [] { const char* e = getenv("VEGS_SORT_LOOKBACK"); return e != nullptr && e[0] == '1'; }();
     return on;
 }
 
