@@ -44,7 +44,6 @@
 #include <cfloat>
 #include "common.cuh"
 #include "composite_common.cuh"
-#include "bulk.cuh"
 
 namespace vegs {
 
@@ -60,12 +59,6 @@ constexpr int kScanSub = 2;                 // list entries per thread and scan 
 constexpr int kScanStep = kScanSub * kSuper;
 constexpr int kRow = kSuper + 1;             // row stride of the pixel x slot matrix
 constexpr int kRing = 4 * kSuper;            // candidate ring (>= 2 * kSuper + kScanStep, power of two)
-// VEGS_FWD_BULK_LIST=1: the raw list words of a scan step (2 KB, contiguous) travel by asynchronous
-// bulk copy (cp.async.bulk + mbarrier, double-buffered in shared memory, two steps ahead) instead of
-// one load per thread one step ahead.  A/B switch; see DESIGN.md for what was measured.
-#ifndef VEGS_FWD_BULK_LIST
-#define VEGS_FWD_BULK_LIST 0
-#endif
 
 struct FwdParams {
     const uint2* ranges;
@@ -94,10 +87,6 @@ struct FwdSmem {
     uint32_t seg_bal[kWarps];       // per segment: ballot of the slots with a hit
     uint32_t scan_cnt[2][kScanSub * kWarps];   // survivors per (sub-step, warp) of a scan step (double-buffered)
     int all_done;
-#if VEGS_FWD_BULK_LIST
-    alignas(16) uint32_t lbuf[2][kScanStep + 4];   // list words of two scan steps (+ the alignment slack)
-    alignas(8) uint64_t lbar[2];
-#endif
 };
 
 static_assert(sizeof(FwdSmem) <= 227 * 1024, "forward working set does not fit the 227 KB of shared memory per CTA");
@@ -168,50 +157,8 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
     // raw-list pipeline of the scan: the list words of the next step are loaded during this one
     int raw_base = 0;
     uint32_t w_cur[kScanSub];
-#if VEGS_FWD_BULK_LIST
-    // step s covers list[s * kScanStep, +kScanStep); its copy starts at the 16-byte boundary at or
-    // below the first word and is rounded up to 16 bytes (the list's allocation is padded)
-    int issued_upto = -1, fetched_upto = -1;      // same in every thread
-    auto issue_step = [&](int step) {
-        const int rb = step * kScanStep;
-        if (rb >= n) return;
-        issued_upto = step;
-        if (tid == 0) {
-            const uint32_t* g0 = list + rb;
-            const uint32_t off = (uint32_t)((reinterpret_cast<uintptr_t>(g0) >> 2) & 3u);
-            const uint32_t cnt = (uint32_t)min(kScanStep, n - rb);
-            const uint32_t bytes = ((off + cnt + 3u) & ~3u) * 4u;
-            mbar_arrive_expect_tx(&sm.lbar[step & 1], bytes);
-            bulk_g2s(sm.lbuf[step & 1], g0 - off, bytes, &sm.lbar[step & 1]);
-        }
-    };
-    auto fetch_step = [&](int step, uint32_t* w) {
-        const int rb = step * kScanStep;
-#pragma unroll
-        for (int j = 0; j < kScanSub; j++) w[j] = 0u;
-        if (rb >= n) return;
-        fetched_upto = step;
-        mbar_wait(&sm.lbar[step & 1], (uint32_t)((step >> 1) & 1));
-        const uint32_t off = (uint32_t)((reinterpret_cast<uintptr_t>(list + rb) >> 2) & 3u);
-#pragma unroll
-        for (int j = 0; j < kScanSub; j++)
-            if (rb + j * kSuper + tid < n) w[j] = sm.lbuf[step & 1][off + j * kSuper + tid];
-    };
-    if (tid == 0) {
-        mbar_init(&sm.lbar[0], 1);
-        mbar_init(&sm.lbar[1], 1);
-        mbar_init_fence();
-    }
-    __syncthreads();
-    issue_step(0);
-    issue_step(1);
-    fetch_step(0, w_cur);
-    __syncthreads();                       // everyone has read buffer 0
-    issue_step(2);
-#else
 #pragma unroll
     for (int j = 0; j < kScanSub; j++) w_cur[j] = (j * kSuper + tid < n) ? list[j * kSuper + tid] : 0u;
-#endif
     uint32_t head = 0, tail = 0;            // ring positions, same in every thread
     int scan_par = 0;
     // working-set pipeline: this thread's candidate of the next working set, when already queued
@@ -226,16 +173,11 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
         bool scanned = false;
         while (tail - head < 2u * kSuper && raw_base < n) {
             uint32_t w_nxt[kScanSub];
-#if VEGS_FWD_BULK_LIST
-            const int sstep = raw_base / kScanStep;
-            fetch_step(sstep + 1, w_nxt);
-#else
 #pragma unroll
             for (int j = 0; j < kScanSub; j++) {
                 const int r = raw_base + kScanStep + j * kSuper + tid;
                 w_nxt[j] = (r < n) ? list[r] : 0u;
             }
-#endif
             bool keep[kScanSub];
             uint32_t bal[kScanSub];
             if (kMasks) {
@@ -260,9 +202,6 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
                 if (lane == 0) sm.scan_cnt[scan_par][j * kWarps + warp] = __popc(bal[j]);
             }
             __syncthreads();
-#if VEGS_FWD_BULK_LIST
-            issue_step(sstep + 3);          // its buffer held step sstep + 1, which everyone has read
-#endif
             uint32_t run = 0;
 #pragma unroll
             for (int j = 0; j < kScanSub; j++) {
@@ -525,10 +464,6 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
         head += (uint32_t)m;
     }
 
-#if VEGS_FWD_BULK_LIST
-    // no copy may still be in flight into this CTA's shared memory when it exits
-    for (int st = fetched_upto + 1; st <= issued_upto; st++) mbar_wait(&sm.lbar[st & 1], (uint32_t)((st >> 1) & 1));
-#endif
     // final transmittance to warp 1 (stop_at is free now), which owns the colour sums
     if (warp == 0) sm.stop_at[lane] = __float_as_uint(T);
     __syncthreads();
