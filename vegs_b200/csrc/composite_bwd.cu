@@ -51,7 +51,11 @@ __device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float
 #define VEGS_BWD_SUPER 256
 #endif
 constexpr int kSuper = VEGS_BWD_SUPER;      // entries per working set = threads per CTA
+#ifdef VEGS_BWD_MINCTAS
+constexpr int kMinCtas = VEGS_BWD_MINCTAS;
+#else
 constexpr int kMinCtas = kSuper <= 256 ? 3 : 1;
+#endif
 constexpr int kWarps = kSuper / 32;
 
 struct BwdParams {

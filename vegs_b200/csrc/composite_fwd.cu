@@ -54,11 +54,15 @@ namespace {
 #endif
 constexpr int kSuper = VEGS_FWD_SUPER;      // candidates per working set = threads per CTA
 constexpr int kWarps = kSuper / 32;
-constexpr int kMinCtas = kSuper > 256 ? 1 : (kSuper == 256 ? 2 : 4);
+#ifdef VEGS_FWD_MINCTAS
+constexpr int kMinCtas = VEGS_FWD_MINCTAS;
+#else
+constexpr int kMinCtas = kSuper > 256 ? 1 : (kSuper == 256 ? 2 : (kSuper == 192 ? 3 : 4));
+#endif
 constexpr int kScanSub = 2;                 // list entries per thread and scan step
 constexpr int kScanStep = kScanSub * kSuper;
 constexpr int kRow = kSuper + 1;             // row stride of the pixel x slot matrix
-constexpr int kRing = 4 * kSuper;            // candidate ring (>= 2 * kSuper + kScanStep, power of two)
+constexpr int kRing = (kSuper & (kSuper - 1)) == 0 ? 4 * kSuper : 2 * kSuper + kScanStep;   // candidate ring (>= 2 * kSuper + kScanStep)
 
 struct FwdParams {
     const uint2* ranges;
@@ -209,7 +213,7 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
                 for (int w = 0; w < kWarps; w++) {
                     if (w == warp && keep[j]) {
                         const uint32_t gid = kMasks ? (w_cur[j] & kListIdMask) : w_cur[j];
-                        sm.ring[(tail + run + __popc(bal[j] & ((1u << lane) - 1u))) & (kRing - 1)] =
+                        sm.ring[(tail + run + __popc(bal[j] & ((1u << lane) - 1u))) % (uint32_t)kRing] =
                             make_uint2(gid, (uint32_t)(raw_base + j * kSuper + tid));
                         // the candidate's records will be gathered by another thread one or two
                         // working sets from now: start them on their way to L2
@@ -240,7 +244,7 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
             if (pre_pos == head + tid) {
                 ord = pre_ord; id = pre_id; a_cur = pre_a; b_cur = pre_b;
             } else {
-                const uint2 ent = sm.ring[(head + tid) & (kRing - 1)];
+                const uint2 ent = sm.ring[(head + tid) % (uint32_t)kRing];
                 id = ent.x; ord = ent.y;
                 a_cur = ldg_f4(p.recA + (size_t)kGeomRecStride * id);
                 b_cur = ldg_f4(p.recB + (size_t)kGeomRecStride * id);
@@ -249,7 +253,7 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
         pre_pos = 0xffffffffu;
         if (head + kSuper + tid < tail) {
             pre_pos = head + kSuper + tid;
-            const uint2 ent = sm.ring[pre_pos & (kRing - 1)];
+            const uint2 ent = sm.ring[pre_pos % (uint32_t)kRing];
             pre_id = ent.x; pre_ord = ent.y;
             pre_a = ldg_f4(p.recA + (size_t)kGeomRecStride * pre_id);
             pre_b = ldg_f4(p.recB + (size_t)kGeomRecStride * pre_id);
@@ -360,7 +364,7 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
                 if (last_w >= 0) {
                     // slot of the last blended hit: the (last_j + 1)-th set bit of its segment's mask
                     const int last_t = last_w * 32 + (int)__fns(sm.bits[last_w][lane], 0, last_j + 1);
-                    last_contributor = sm.ring[(head + last_t) & (kRing - 1)].y + 1u;   // ordinal in the tile's list
+                    last_contributor = sm.ring[(head + last_t) % (uint32_t)kRing].y + 1u;   // ordinal in the tile's list
                     uint32_t idx = hit_base;                                           // position in the unit's hit list
                     for (int w2 = 0; w2 < last_w; w2++) idx += __popc(sm.seg_bal[w2]);
                     last_hit = idx + __popc(sm.seg_bal[last_w] & ((1u << (last_t & 31)) - 1u)) + 1u;
