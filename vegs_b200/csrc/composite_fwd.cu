@@ -49,8 +49,11 @@ namespace vegs {
 
 namespace {
 
+// 192 candidates per working set: 73.5 KB of shared memory and 96 registers, i.e. THREE CTAs per SM;
+// measured against 256 (two CTAs, 1.665 ms) and 128 (four, 1.875 ms): 1.598 ms per view at 6 M
+// (profiles/r02_composite_working_set_sweep.json)
 #ifndef VEGS_FWD_SUPER
-#define VEGS_FWD_SUPER 256
+#define VEGS_FWD_SUPER 192
 #endif
 constexpr int kSuper = VEGS_FWD_SUPER;      // candidates per working set = threads per CTA
 constexpr int kWarps = kSuper / 32;
