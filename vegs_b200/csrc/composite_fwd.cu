@@ -1,5 +1,6 @@
-// Front-to-back alpha compositing.  One CTA of 8 warps per 8x4 pixel block ("unit"), 8 units per
-// 16x16 tile; a unit walks its tile's depth-sorted list.
+// Front-to-back alpha compositing.  One CTA of W = 6 warps (kSuper = 192 threads = candidates per
+// working set; a build parameter) per 8x4 pixel block ("unit"), 8 units per 16x16 tile; a unit walks
+// its tile's depth-sorted list.
 //
 // Replaces FORWARD::render / renderCUDA (reference cuda_rasterizer/forward.cu:262-441), including
 // the VEGS additions: depth map, alpha map, accumulated covariance quaternion map (sequential
@@ -10,15 +11,15 @@
 // Gaussians, each touching a handful of pixels, and one block walks them while the other SMs
 // idle.  The only truly sequential part of compositing is the transmittance chain
 // T <- T * (1 - alpha) with its saturation test; everything else is parallel.
-//   SCAN  512 raw list entries per step, two per thread: keep the entries whose conservative box
+//   SCAN  2 x kSuper raw list entries per step, two per thread: keep the entries whose conservative box
 //         (preprocess stage) reaches the unit's 32 pixels - one bit of the list word, set by the
 //         emission kernel (binning.cu); survivors are appended in list order to a ring of
-//         candidates (ballot + prefix over the 8 warps).  Repeated until two working sets are
+//         candidates (ballot + prefix over the W warps).  Repeated until two working sets are
 //         queued or the list ends.
-//   then, per working set of 256 candidates:
+//   then, per working set of kSuper candidates:
 //   S0  entry-parallel: run the reference's exact contribution test on the pixels inside the box
 //       (each pixel row narrowed to the interval the quadratic can reach), keep a 32-bit hit mask
-//       and (1 - alpha, depth * alpha) of each hit in a 32 x 257 shared matrix; entries with a hit
+//       and (1 - alpha, depth * alpha) of each hit in a 32 x (kSuper + 1) shared matrix; entries with a hit
 //       stage their packed records and are appended to the unit's hit list for the backward pass
 //   S1  each warp bit-transposes its 32 hit masks into per-pixel hit lists and compacts each
 //       pixel's operands to the front of its row segment
@@ -26,21 +27,22 @@
 //       list order and in the reference's float operation order: T before each hit, the
 //       saturation point (T(1-alpha) < 1e-4 stops the pixel, that Gaussian is not blended),
 //       n_contrib, plus the depth sum — branch-free rounds of four hits over dense arrays
-//   S3  pixel-parallel per 32-candidate segment (8 warps, lane = pixel): colour and scale sums and
+//   S3  pixel-parallel per 32-candidate segment (W warps, lane = pixel): colour and scale sums and
 //       the slerp quaternion product of the segment's hits, from the (1 - alpha, T) pairs S2 left
 //       in the matrix (no second exp per hit)
-//   S4  warps 0 and 1 fold the eight segment partials into the pixel state, in list order
-// so the expensive work (exp, sin, cos, quaternion product per contribution) is spread over 8
-// warps per pixel block and 64 warps per tile, the fixed costs of a working set are paid per 256
-// candidates rather than per 256 list entries, units are issued longest-list-first, and a unit
+//   S4  warps 0 and 1 fold the W segment partials into the pixel state, in list order
+// so the expensive work (exp, sin, cos, quaternion product per contribution) is spread over W
+// warps per pixel block and 8 W warps per tile, the fixed costs of a working set are paid per kSuper
+// candidates rather than per kSuper list entries, units are issued longest-list-first, and a unit
 // stops as soon as its 32 pixels are saturated.
 // Exactness: which Gaussians contribute to a pixel, alpha, T, n_contrib, depth and alpha map are
 // bit-identical to the reference (same float operations in the same order).  The colour / scale
 // sums and the quaternion product are associated per 32-candidate segment instead of in one
 // running chain, a last-bit difference far inside the 1e-5 tolerance (values of magnitude <= 1).
 // Roofline: not HBM-bound (4 B per list entry per unit from L2, 36 B more per candidate, 48 B
-// more per entry with a hit, 52 B written per pixel); the bound is instruction issue of the
-// per-hit blend and the box tests.
+// more per entry with a hit, 52 B written per pixel); the launch is bound by CTA
+// residency (shared memory: three CTAs per SM) times the latency of a working set's phase chain;
+// profiles/r02e_tile_stats.txt, DESIGN.md §8.
 #include <cfloat>
 #include "common.cuh"
 #include "composite_common.cuh"
