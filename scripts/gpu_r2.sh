@@ -102,7 +102,7 @@ for s in "$@"; do
       # one --set full capture of every kernel of the second pass of scripts/profile_all.py
       CMD="python scripts/profile_all.py"
       timeout 600 $CMD > gpurun_out/${tag}_profile_all.log 2>&1 &&
-      timeout 1500 ncu --set full --clock-control none -k regex:'bbox|build_boxes|composite|emit_kernel|gather_points|knn3|mark_visible|morton|preprocess|radix|tile_' -s ${NCU_SKIP:-48} -c ${NCU_COUNT:-48} -f -o gpurun_out/${tag}_prof_all $CMD > gpurun_out/${tag}_ncu_all.log 2>&1
+      timeout 1500 ncu --set full --clock-control none -k regex:'adam_kernel|bbox|build_boxes|composite|emit_kernel|gather_points|knn3|mark_visible|morton|normal_guidance|preprocess|radix|tile_' -s ${NCU_SKIP:-50} -c ${NCU_COUNT:-50} -f -o gpurun_out/${tag}_prof_all $CMD > gpurun_out/${tag}_ncu_all.log 2>&1
       echo "ncu all rc=$?" | tee -a $S
       python scripts/ncu_table.py gpurun_out/${tag}_prof_all.ncu-rep gpurun_out/${tag}_ncu_all.md "ncu --set full --clock-control none, every kernel of one pass over the 6 M scene ($tag): \`$CMD\`" > /dev/null 2>&1
       ls -la gpurun_out/${tag}_prof_all.ncu-rep >> $S

@@ -20,12 +20,21 @@ cam = synth.make_camera(0, device=dev)
 rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, torch.zeros(3, device=dev), 1.0,
                                        cam.viewmatrix, cam.projmatrix, 3, cam.campos, False, False)
 rast = dgr.GaussianRasterizer(rs)
+from types import SimpleNamespace  # noqa: E402
+import numpy as np  # noqa: E402
+from vegs_b200.losses import loss_normal_guidance  # noqa: E402
+from vegs_b200.optim import FusedAdam  # noqa: E402
+opt = FusedAdam([{"params": [sc[k]], "lr": 1e-3, "name": k} for k in ("means3D", "shs", "opacities", "scales", "rotations")],
+                lr=0.0, eps=1e-15)
+ng_cam = SimpleNamespace(original_normal=torch.nn.functional.normalize(torch.randn(3, cam.H, cam.W, device=dev), dim=0),
+                         R=np.array([[0.0, 0.0, 1.0], [-1.0, 0.0, 0.0], [0.0, -1.0, 0.0]]))
 for it in range(2):          # the second pass is the one to look at (first touches cold memory)
     vis = rast.markVisible(sc["means3D"].detach())
     m2 = torch.zeros_like(sc["means3D"], requires_grad=True)
     out = rast(means3D=sc["means3D"], means2D=m2, opacities=sc["opacities"], shs=sc["shs"], scales=sc["scales"],
                rotations=sc["rotations"])
-    (out[0].sum() + out[1].mean() + out[4].mean()).backward()
+    (out[0].sum() + out[1].mean() + out[4].mean() + loss_normal_guidance(ng_cam, out[2], out[3])).backward()
+    opt.step(zero_grad=True)
     d = distCUDA2(sc["means3D"].detach())
     torch.cuda.synchronize()
 print("visible", int(vis.sum()), "radii>0", int((out[5] > 0).sum()), "dist2 mean", float(d.mean()))
