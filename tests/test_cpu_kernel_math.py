@@ -268,3 +268,60 @@ def test_unit_masks_from_pixel_boxes_equal_the_per_entry_box_test():
                 & (np.maximum(gy0, by0) <= np.minimum(gy1, by1))
             assert np.array_equal(keep_box, keep_mask), f"unit {blk}: {int((keep_box != keep_mask).sum())} differ"
     assert keep_box.sum() > 100
+
+
+def test_margins_scale_with_the_cancelling_terms_for_long_thin_splats():
+    """Long thin splats sampled far from their centre along the major axis: the terms
+    A dx^2, C dy^2, 2 B dx dy reach 1e5 - 1e7 and cancel to a power of a few units, so the float32
+    evaluation of the reference is off by far more than a fixed 0.01.  The box extents of
+    preprocess.cu widen tau by 4e-6 of those terms; with that every pixel that passes the
+    reference's float32 test lies inside the box, while the fixed margin alone misses some."""
+    rng = np.random.default_rng(21)
+    f = np.float32
+    n = 400000
+    ang = rng.uniform(0.2, np.pi / 2 - 0.2, n)                  # well away from the axes: all three terms large
+    s1, s2 = 10 ** rng.uniform(4.5, 6.5, n), 10 ** rng.uniform(-2, 0, n)   # sigma 180 - 1800 px by ~0.1 - 1 px
+    ca, sa = np.cos(ang), np.sin(ang)
+    cxx = (ca * ca * s1 + sa * sa * s2 + 0.3).astype(f)
+    cyy = (sa * sa * s1 + ca * ca * s2 + 0.3).astype(f)
+    cxy = (ca * sa * (s1 - s2)).astype(f)
+    det = (cxx.astype(np.float64) * cyy - (cxy * cxy).astype(f).astype(np.float64)).astype(f)
+    det_inv = (f(1) / det).astype(f)
+    A, B, C = (cyy * det_inv).astype(f), (-cxy * det_inv).astype(f), (cxx * det_inv).astype(f)
+    op = rng.uniform(0.3, 1.0, n).astype(f)
+    tau = (np.log(f(255.0) * op) + f(0.01)).astype(f)
+    cdet = (A * C - B * B).astype(f)
+    ok = (det > 0) & (cdet > 0) & np.isfinite(A) & np.isfinite(C)
+
+    def extents(t):
+        with np.errstate(invalid="ignore", divide="ignore"):
+            s2t = (f(2.0) * t / cdet).astype(f)
+            return np.sqrt(s2t * C).astype(f), np.sqrt(s2t * A).astype(f)
+
+    tx, ty = extents(tau)
+    mag = (A * tx * tx + C * ty * ty + f(2.0) * np.abs(B) * tx * ty).astype(f)
+    tx2, ty2 = extents((tau + f(4e-6) * mag).astype(f))
+    ex_new = (tx2 * f(1.002) + f(0.01)).astype(np.float16).astype(f)
+    ey_new = (ty2 * f(1.002) + f(0.01)).astype(np.float16).astype(f)
+    ex_old = (tx * f(1.002) + f(0.01)).astype(np.float16).astype(f)
+    ey_old = (ty * f(1.002) + f(0.01)).astype(np.float16).astype(f)
+    ok &= np.isfinite(ex_new) & np.isfinite(ey_new)               # inf = "test the whole tile", always safe
+    missed_new = missed_old = checked = 0
+    for _ in range(8):
+        # points on the major axis near the end of the box, jittered across it by a pixel or so
+        r = (rng.uniform(0.9, 1.02, n) * np.hypot(tx, ty)).astype(np.float64) * rng.choice([-1.0, 1.0], n)
+        jit = rng.uniform(-1.5, 1.5, n)
+        dx = np.rint(ca * r - sa * jit).astype(f)               # whole-pixel offsets, as pixel centres are
+        dy = np.rint(sa * r + ca * jit).astype(f)
+        p1 = ((A * dx).astype(f) * dx).astype(f)
+        p2 = ((C * dy).astype(f) * dy).astype(f)
+        power = ((p1.astype(np.float64) + p2).astype(f).astype(np.float64) * -0.5
+                 - ((B * dx).astype(f) * dy).astype(f)).astype(f)
+        alpha = np.minimum(f(0.99), (op * np.exp(np.minimum(power, 0).astype(np.float64)).astype(f)).astype(f))
+        hit = ok & (power <= 0) & (alpha >= f(1.0 / 255.0))
+        missed_new += int((hit & ~((np.abs(dx) <= ex_new) & (np.abs(dy) <= ey_new))).sum())
+        missed_old += int((hit & ~((np.abs(dx) <= ex_old) & (np.abs(dy) <= ey_old))).sum())
+        checked += int(hit.sum())
+    assert checked > 1000
+    assert missed_new == 0, missed_new
+    print("fixed-margin box would have missed", missed_old, "of", checked)
