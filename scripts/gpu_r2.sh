@@ -49,6 +49,7 @@ for s in "$@"; do
       fi
       timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --steps ${STEPS:-10} --warmup 3 > gpurun_out/${tag}_scale_$N.json 2> gpurun_out/${tag}_scale_$N.err
       echo "scale $N rc=$?" | tee -a $S
+      if [ -n "${MULTI_OURS_ONLY:-}" ]; then cat $S; exit 0; fi
       timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29518 bench.py --impl reference --gpus $N --steps 4 --warmup 3 > gpurun_out/${tag}_scale_${N}_ref.json 2> gpurun_out/${tag}_scale_${N}_ref.err
       echo "scale ref $N rc=$?" | tee -a $S
       timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29519 scripts/nccl_busbw.py > gpurun_out/${tag}_nccl_busbw_$N.json 2> gpurun_out/${tag}_nccl_busbw_$N.err
