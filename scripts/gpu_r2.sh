@@ -85,6 +85,15 @@ for s in "$@"; do
       done
       touch vegs_b200/csrc/*.cu
       python vegs_b200/build.py > gpurun_out/${tag}_flags_build_default.log 2>&1 ;;
+    ncu_phases)  # per-phase stall / instruction shares of the two compositing kernels (source page cut at the barriers)
+      CMD="python bench.py --P 6000000 --views 2 --steps 1 --warmup 3 --no-cpu-baseline --no-fused-leg"
+      timeout 900 ncu --set full --clock-control none --import-source on -k regex:'composite_(fwd|bwd)_kernel' -s 6 -c 2 -f -o gpurun_out/${tag}_prof_composite $CMD > gpurun_out/${tag}_ncu_composite.log 2>&1
+      echo "ncu composite rc=$?" | tee -a $S
+      ncu -i gpurun_out/${tag}_prof_composite.ncu-rep --page source --csv --print-source sass > gpurun_out/${tag}_composite_source.csv 2> gpurun_out/${tag}_composite_source.err
+      python scripts/ncu_phases.py gpurun_out/${tag}_composite_source.csv > gpurun_out/${tag}_ncu_phases.txt 2>&1
+      python scripts/ncu_table.py gpurun_out/${tag}_prof_composite.ncu-rep gpurun_out/${tag}_ncu_composite.md "ncu --set full --clock-control none --import-source on, compositing kernels ($tag): \`$CMD\`" > /dev/null 2>&1
+      rm -f gpurun_out/${tag}_composite_source.csv
+      echo "ncu phases rc=$? $(wc -l < gpurun_out/${tag}_ncu_phases.txt) lines" | tee -a $S ;;
     bench_quick)
       timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench_quick rc=$?" | tee -a $S ;;
     configs)
