@@ -158,8 +158,9 @@ class Workload:
         my_views = self.my_views if views is None else views
         if fused:
             if self.buf is None:
-                self.buf = self.vdist.FlatGradBuffer(p)
-            self.buf.begin_step()
+                self.buf = self.vdist.FlatGradBuffer(p, defer_sh=("shs",), sh_degree=3, views_per_step=self.n_views)
+            # camera centres of the step's views in batch order (the deferred SH gradient is rebuilt from them)
+            self.buf.begin_step([self.cams[v].campos for v in range(self.n_views)] if views is None else None)
             stats = self.buf.step_stats
         else:
             for t in p.values():
@@ -179,7 +180,7 @@ class Workload:
                 torch.cuda.current_stream(self.device).wait_event(ev)
                 pending = self._stage_target(my_views[i + 1]) if i + 1 < len(my_views) else None
             means2D = torch.zeros_like(p["means3D"], requires_grad=True)
-            ext = self.buf.rasterizer_kwargs(mod, first=(i == 0)) if fused else {}
+            ext = self.buf.rasterizer_kwargs(mod, first=(i == 0), slot=i) if fused else {}
             rast = mod.GaussianRasterizer(self.settings(mod, self.cams[v % len(self.cams)]), **ext)
             color, depth, quat, scale, alpha, radii = rast(
                 means3D=p["means3D"], means2D=means2D, opacities=p["opacities"], shs=p["shs"],
@@ -403,8 +404,10 @@ def main():
         ms_fe = timed(lambda: wl.step(mod, False, fused=True), args.steps, 2, device, world)
         line["e2e_fused"] = dict(value=args.views / (ms_fe / args.steps / 1000.0), unit=UNIT,
                                  h2d_bytes_per_step=h2d, d2h_bytes_per_step=4 * world)
-        line["fused_what"] = ("GaussianRasterizer(settings, fused_grad_accumulation=..., densification_accumulators=...): "
-                              ".grad tensors and the step statistics are views of one flat all-reduce buffer")
+        line["fused_what"] = ("GaussianRasterizer(settings, fused_grad_accumulation=..., densification_accumulators=..., "
+                              "deferred_sh_grad=...): .grad tensors and the step statistics are views of one flat "
+                              "all-reduce buffer; each view leaves dL/dRGB [P,3] instead of dL/dSH, the ranks all-gather "
+                              "those and rebuild the SH gradient (vegs_sh_grad_from_views)")
     if world > 1:
         # weak scaling beside the fixed-batch figure: every rank renders 8 views per step (8 x N per step)
         wv = list(range(rank * args.views, (rank + 1) * args.views))

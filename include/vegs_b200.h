@@ -180,6 +180,14 @@ typedef struct VegsBackwardArgs {
      * No term flows through the weights themselves (they do not feed dL/dalpha). */
     int32_t live_map_gradients;
     const float* out_cov_quat;    /* [4,H,W] from the forward; only read when live_map_gradients != 0 */
+    /* Deferred SH gradient (no reference counterpart).  The gradient of the colour with respect to
+     * the SH coefficients of one view is an outer product, dL_dsh[k][c] = basis_k(view direction) *
+     * dL_dRGB[c] (clamped channels zeroed).  When dL_drgb_deferred [P,3] is given, the kernel writes
+     * that dL_dRGB (zeros for radii == 0) INSTEAD of the dL_dsh rows (dL_dsh / dL_dsh_rest may then
+     * be NULL; VEGS_ACC_SH is ignored) and vegs_sh_grad_from_views rebuilds the sum over a step's
+     * views from 12 bytes per view and Gaussian instead of 12 M bytes - what a view-parallel step
+     * exchanges between GPUs.  dL_dmeans3D still contains the SH direction term. */
+    float* dL_drgb_deferred;
 } VegsBackwardArgs;
 
 #define VEGS_ACC_MEANS3D   1u
@@ -298,6 +306,18 @@ typedef struct VegsAdamArgs {
                                  * rounded to float once, which is what torch's kernels receive */
 } VegsAdamArgs;
 int vegs_adam_step(const VegsAdamArgs* args, void* stream);
+
+/*
+ * SH gradient of a step from the per-view colour gradients (no counterpart in the reference; see
+ * VegsBackwardArgs.dL_drgb_deferred):
+ *   dL_dsh[i][k][c] (+)= sum_v basis_k(normalize(means3D[i] - campos[v])) * dL_drgb[v][i][c],  k < (D+1)^2,
+ * the remaining coefficients of the M stored ones get zero.  campos [V,3] and dL_drgb [V,P,3] are
+ * device arrays.  With dL_dsh_rest != NULL the result is split as VEGS's f_dc [P,1,3] (dL_dsh) and
+ * f_rest [P,M-1,3] (dL_dsh_rest).  accumulate != 0 adds to the destination.  M <= 16.
+ */
+int vegs_sh_grad_from_views(int32_t P, int32_t D, int32_t M, int32_t V, const float* means3D,
+                            const float* campos, const float* dL_drgb, float* dL_dsh, float* dL_dsh_rest,
+                            int32_t accumulate, void* stream);
 
 /*
  * Normal-guidance loss on the covariance maps, value and both gradients in one pass (no

@@ -1,9 +1,10 @@
 """Hardware multi-GPU equivalence: the view-parallel step on 2 GPUs over NCCL with
 the REAL rasterizer equals the same 8-view batch accumulated on one GPU, gradients within 1e-4 of
 each tensor's max norm, integer statistics exactly.  Both routes are covered: the plain drop-in
-step (autograd accumulation + vegs_b200.dist.allreduce_step) and the fused one (FlatGradBuffer:
+step (autograd accumulation + vegs_b200.dist.allreduce_step), the fused one (FlatGradBuffer:
 .grad tensors and step statistics as views of the all-reduce buffer, written by the backward
-kernel).  Skipped on a box with fewer than 2 GPUs (run it with `gpurun --gpus 2`)."""
+kernel) and the fused one with the deferred SH gradient (an all-gather of each view's dL/dRGB
+instead of the all-reduce of the SH gradient).  Skipped on a box with fewer than 2 GPUs (run it with `gpurun --gpus 2`)."""
 import os
 import socket
 
@@ -53,10 +54,11 @@ def _run_step(rank, world, fused, dev):
     tg = [t.to(dev) for t in _targets(cams)]
     mine = vdist.shard_views(N_VIEWS, rank, world)
     if fused:
-        buf = vdist.FlatGradBuffer(params)
-        buf.begin_step()
+        defer = fused == "defer"
+        buf = vdist.FlatGradBuffer(params, defer_sh=("shs",) if defer else (), views_per_step=N_VIEWS)
+        buf.begin_step([c.campos for c in cams] if defer else None)
         for i, v in enumerate(mine):
-            vg, radii = _view_step(dgr, params, cams[v], tg[v], buf.rasterizer_kwargs(dgr, first=(i == 0)), dev)
+            vg, radii = _view_step(dgr, params, cams[v], tg[v], buf.rasterizer_kwargs(dgr, first=(i == 0), slot=i), dev)
             buf.step_stats.add_view(vg, radii)
         buf.allreduce()
         stats = buf.step_stats
@@ -85,14 +87,14 @@ def _worker(rank, world, port, fused, out):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("fused", [False, True])
+@pytest.mark.parametrize("fused", [False, True, "defer"])
 def test_two_gpu_step_equals_one_gpu_accumulation(fused, tmp_path):
     import torch.multiprocessing as mp
     out = str(tmp_path / "r0.pt")
     mp.spawn(_worker, args=(2, _free_port(), fused, out), nprocs=2, join=True)
     two = torch.load(out, weights_only=False)
     one = _run_step(0, 1, fused, torch.device("cuda", 0))
-    rec = util.parity_record(f"multi_gpu_2x_{'fused' if fused else 'dropin'}_{P}_{N_VIEWS}views")
+    rec = util.parity_record(f"multi_gpu_2x_{'fused_' + str(fused) if fused else 'dropin'}_{P}_{N_VIEWS}views")
     for k in one["grads"]:
         assert float(one["grads"][k].abs().max()) > 0, k
         rec[k] = float(util.grad_close(two["grads"][k].numpy(), one["grads"][k].numpy(), f"2-GPU all-reduced grad {k}", rtol=1e-4))

@@ -472,6 +472,54 @@ def test_live_map_gradients_are_the_weighted_map_cotangents():
         assert abs(lhs_q - rhs_q) <= 2e-4 * max(abs(rhs_q), 1.0), (lhs_q, rhs_q)
 
 
+def test_deferred_sh_gradient_equals_the_accumulated_one():
+    """FlatGradBuffer(defer_sh=...): every view's backward leaves only its dL/dRGB [P,3] and the step's
+    SH gradient is rebuilt from the camera centres (vegs_sh_grad_from_views).  It must equal the SH
+    gradient accumulated row by row, and nothing else may change; the split (f_dc, f_rest) output
+    of the rebuild kernel must equal the cat'ed one."""
+    import ctypes as C
+    import vegs_b200.diff_gaussian_rasterization as dgr
+    from vegs_b200 import dist as vdist, _lib
+    dev = torch.device("cuda")
+    scene = util.scene_with_specials(40003)
+    cams = [synth.make_camera(k, scale=0.25, device=dev) for k in range(3)]
+    gen = torch.Generator().manual_seed(3)
+    tg = [torch.rand(3, c.H, c.W, generator=gen).to(dev) for c in cams]
+
+    def step(defer, deg):
+        params = {k: v.to(dev).clone().requires_grad_(True) for k, v in scene.items()}
+        buf = vdist.FlatGradBuffer(params, defer_sh=("shs",) if defer else (), sh_degree=deg, views_per_step=len(cams))
+        buf.begin_step([c.campos for c in cams] if defer else None)
+        for i, cam in enumerate(cams):
+            rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, torch.zeros(3, device=dev), 1.0,
+                                                   cam.viewmatrix, cam.projmatrix, deg, cam.campos, False, False)
+            m2 = torch.zeros_like(params["means3D"], requires_grad=True)
+            out = dgr.GaussianRasterizer(rs, **buf.rasterizer_kwargs(dgr, first=(i == 0), slot=i))(
+                means3D=params["means3D"], means2D=m2, opacities=params["opacities"], shs=params["shs"],
+                scales=params["scales"], rotations=params["rotations"])
+            ((out[0] - tg[i]).abs().mean() * (1 + i) + 0.1 * out[1].mean()).backward()
+            buf.step_stats.add_view(m2.grad, out[5])
+        buf.allreduce()
+        return {k: v.grad.detach().clone() for k, v in params.items()}, buf
+
+    for deg in (3, 1):
+        ga, _ = step(False, deg)
+        gb, buf = step(True, deg)
+        for k in ga:
+            assert float(ga[k].abs().max()) > 0, k
+            util.grad_close(gb[k].cpu().numpy(), ga[k].cpu().numpy(), f"deferred SH route, grad {k}", rtol=2e-5)
+        if deg < 3:
+            assert float(gb["shs"][:, (deg + 1) ** 2:].abs().max()) == 0.0
+        # the same rebuild into the split layout
+        P = ga["shs"].shape[0]
+        dc = torch.full((P, 1, 3), 7.0, device=dev); rest = torch.full((P, 15, 3), 7.0, device=dev)
+        rc = _lib.load().vegs_sh_grad_from_views(P, deg, 16, int(buf.drgb_all.shape[0]), scene["means3D"].to(dev).data_ptr(),
+                                                  buf.campos_all.data_ptr(), buf.drgb_all.data_ptr(), dc.data_ptr(),
+                                                  rest.data_ptr(), 0, C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        _lib.check(rc, "vegs_sh_grad_from_views")
+        assert torch.equal(torch.cat((dc, rest), 1), gb["shs"])
+
+
 def test_modes_colors_precomp_and_cov3d_precomp_against_oracle():
     scene = util.scene_with_specials(4000)
     cam = synth.make_camera(0, scale=0.125)

@@ -56,6 +56,7 @@ class VegsBackwardArgs(C.Structure):
         ("activations", C.c_uint32), ("opacities", C.c_void_p), ("shs_rest", C.c_void_p),
         ("dL_dsh_rest", C.c_void_p),
         ("live_map_gradients", C.c_int32), ("out_cov_quat", C.c_void_p),
+        ("dL_drgb_deferred", C.c_void_p),
     ]
 
 
@@ -92,6 +93,8 @@ SIGNATURES = {
                              C.c_void_p]),
     "vegs_dist2_noalloc": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "vegs_adam_step": (C.c_int, [C.POINTER(VegsAdamArgs), C.c_void_p]),
+    "vegs_sh_grad_from_views": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
     "vegs_normal_guidance": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float,
                                        C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "vegs_export_state": (C.c_int, [C.POINTER(VegsForwardArgs), C.c_int32] + [C.c_void_p] * 10),

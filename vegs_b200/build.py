@@ -28,6 +28,7 @@ SOURCES = [
     "knn.cu",
     "adam.cu",
     "normal_guidance.cu",
+    "sh_views.cu",
 ]
 
 NVCC_FLAGS = [

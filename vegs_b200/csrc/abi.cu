@@ -252,7 +252,7 @@ extern "C" int vegs_backward(const VegsBackwardArgs* a, void* stream_) {
         set_error("vegs_backward: a required pointer is null");
         return VEGS_EINVAL;
     }
-    if (a->shs && !a->dL_dsh) { set_error("shs given but dL_dsh is null"); return VEGS_EINVAL; }
+    if (a->shs && !a->dL_dsh && !a->dL_drgb_deferred) { set_error("shs given but neither dL_dsh nor dL_drgb_deferred"); return VEGS_EINVAL; }
     if ((a->scales != nullptr) != (a->rotations != nullptr)) {
         set_error("scales and rotations must be given together");
         return VEGS_EINVAL;

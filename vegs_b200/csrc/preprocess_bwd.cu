@@ -56,6 +56,7 @@ struct PbParams {
     float* dL_dmeans2D;
     float* dL_dsh;
     float* dL_dsh_rest;
+    float* dL_drgb;      // deferred SH gradient: the clamp-masked dL/dRGB [P,3] instead of dL/dSH rows, or NULL
     float* dL_dcolors;
     float* dL_dopacity;
     float* dL_dscales;
@@ -70,7 +71,7 @@ struct PbParams {
 };
 
 // Dense output staging of one warp (overlays the input blocks once they are in registers).
-constexpr int kOutMeans3D = 0, kOutMeans2D = 96, kOutScales = 192, kOutRots = 288, kOutOpac = 416, kOutFloats = 448;
+constexpr int kOutMeans3D = 0, kOutMeans2D = 96, kOutScales = 192, kOutRots = 288, kOutOpac = 416, kOutRgb = 448;   // 544 floats in all
 
 struct __align__(16) BwdWarpStage {
     float sh[kShWarpFloats];              // SH rows in, dL/dSH rows out
@@ -144,7 +145,8 @@ __global__ void __launch_bounds__(kPwThreads, 5) preprocess_bwd_kernel(const PbP
     const bool have_sr = p.cov3D_precomp == nullptr;
     const bool in_bulk = full && p.in_bulk_ok;
     const bool out_bulk = full && p.out_bulk_ok;
-    const bool use_sh = p.shs != nullptr && p.dL_dsh != nullptr;
+    const bool defer_sh = p.dL_drgb != nullptr;    // only dL/dRGB leaves the kernel; dL/dSH is rebuilt later (sh_views.cu)
+    const bool use_sh = p.shs != nullptr && (p.dL_dsh != nullptr || defer_sh);
     const bool staged_sh = use_sh && M <= kMaxStageCoeffs;
     const bool sh_block_bulk = staged_sh && kSh == kShSplit && full && p.shs_vec_ok;   // whole-warp blocks in
     const bool act_op = (p.act & VEGS_ACT_OPACITY_SIGMOID) != 0u;
@@ -359,9 +361,9 @@ __global__ void __launch_bounds__(kPwThreads, 5) preprocess_bwd_kernel(const PbP
 
     // ---- SH backward: dL/dSH rows built in the staging rows, dL/dmean through the view direction
     const bool acc_sh = (p.accum & VEGS_ACC_SH) != 0u;
-    bool dsh_done = !use_sh;
+    bool dsh_done = !use_sh || defer_sh;
+    float dRGB[3] = {0.f, 0.f, 0.f};
     if (use_sh) {
-        float dRGB[3] = {0.f, 0.f, 0.f};
         if (visible) {
             const uint32_t cb = p.clamped[idx];
             dRGB[0] = (cb & 1u) ? 0.f : dcol[0];
@@ -405,8 +407,9 @@ __global__ void __launch_bounds__(kPwThreads, 5) preprocess_bwd_kernel(const PbP
                 const float3 dm = sh_bwd_end(sb, dox, doy, doz);
                 dmean[0] += dm.x; dmean[1] += dm.y; dmean[2] += dm.z;
             }
-            // ---- dL/dSH rows to global memory
-            if (kSh == kShBulkRows && p.dsh_vec_ok) {
+            // ---- dL/dSH rows to global memory (not when the SH gradient is deferred)
+            if (defer_sh) {
+            } else if (kSh == kShBulkRows && p.dsh_vec_ok) {
                 // one bulk store (or L2 reduction, when accumulating) per row, issued by the row's lane
                 fence_smem_to_async_proxy();
                 if (in_range && (visible || !acc_sh)) {
@@ -469,9 +472,9 @@ __global__ void __launch_bounds__(kPwThreads, 5) preprocess_bwd_kernel(const PbP
                     for (int k = 0; k < rowlen; k++) dst[k] = acc_sh ? dst[k] + row[k] : row[k];
                 }
             }
-        } else if (in_range) {
+        } else if (in_range && !defer_sh) {
             // M > 16: no staging; work in a local copy of the first 16 coefficients
-            // (accumulation is refused for M > 16 by the launcher)
+            // (accumulation and deferral are refused for M > 16 by the launcher)
             float* dst = p.dL_dsh + (size_t)idx * 3 * M;
             if (visible) {
                 const float* src = p.shs + (size_t)idx * 3 * M;
@@ -530,6 +533,10 @@ __global__ void __launch_bounds__(kPwThreads, 5) preprocess_bwd_kernel(const PbP
         }
         *reinterpret_cast<float4*>(&o[kOutRots + 4 * lane]) = make_float4(drot[0], drot[1], drot[2], drot[3]);
         o[kOutOpac + lane] = dopac;
+        if (defer_sh) {
+#pragma unroll
+            for (int k = 0; k < 3; k++) o[kOutRgb + 3 * lane + k] = dRGB[k];
+        }
         fence_smem_to_async_proxy();
         __syncwarp();
         if (lane == 0) {
@@ -543,6 +550,7 @@ __global__ void __launch_bounds__(kPwThreads, 5) preprocess_bwd_kernel(const PbP
             put_block(p.dL_dopacity ? p.dL_dopacity + (size_t)warp_base : nullptr, kOutOpac, 128u, VEGS_ACC_OPACITY);
             put_block(p.dL_dscales ? p.dL_dscales + 3 * (size_t)warp_base : nullptr, kOutScales, 384u, VEGS_ACC_SCALES);
             put_block(p.dL_drots ? p.dL_drots + 4 * (size_t)warp_base : nullptr, kOutRots, 512u, VEGS_ACC_ROTATIONS);
+            put_block(defer_sh ? p.dL_drgb + 3 * (size_t)warp_base : nullptr, kOutRgb, 384u, 0u);
         }
     }
     if (in_range) {
@@ -560,6 +568,7 @@ __global__ void __launch_bounds__(kPwThreads, 5) preprocess_bwd_kernel(const PbP
             put(p.dL_dopacity ? p.dL_dopacity + idx : nullptr, 1, &dopac, VEGS_ACC_OPACITY);
             put(p.dL_dscales ? p.dL_dscales + i3 : nullptr, 3, dscale, VEGS_ACC_SCALES);
             put(p.dL_drots ? p.dL_drots + 4 * (size_t)idx : nullptr, 4, drot, VEGS_ACC_ROTATIONS);
+            put(defer_sh ? p.dL_drgb + i3 : nullptr, 3, dRGB, 0u);
         }
         // the two rarely used outputs (colors_precomp / cov3D_precomp modes) are written directly
         put(p.dL_dcolors ? p.dL_dcolors + i3 : nullptr, 3, dcol, VEGS_ACC_COLORS);
@@ -592,6 +601,7 @@ int launch_preprocess_bwd(const VegsBackwardArgs& a, const GeomView& g, const fl
     p.acc = acc;
     p.map_acc = map_acc;
     p.dL_dmeans3D = a.dL_dmeans3D; p.dL_dmeans2D = a.dL_dmeans2D; p.dL_dsh = a.dL_dsh; p.dL_dsh_rest = a.dL_dsh_rest;
+    p.dL_drgb = a.dL_drgb_deferred;
     p.dL_dcolors = a.dL_dcolors; p.dL_dopacity = a.dL_dopacity; p.dL_dscales = a.dL_dscales;
     p.dL_drots = a.dL_drotations; p.dL_dcov3D = a.dL_dcov3D;
     auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };   // NULL counts as aligned
@@ -605,7 +615,7 @@ int launch_preprocess_bwd(const VegsBackwardArgs& a, const GeomView& g, const fl
                    (a.cov3D_precomp != nullptr || (al16(a.scales) && al16(a.rotations))) &&
                    (!(a.activations & VEGS_ACT_OPACITY_SIGMOID) || al16(a.opacities));
     p.out_bulk_ok = !bulk_off && al16(a.dL_dmeans3D) && al16(a.dL_dmeans2D) && al16(a.dL_dopacity) &&
-                    al16(a.dL_dscales) && al16(a.dL_drotations);
+                    al16(a.dL_dscales) && al16(a.dL_drotations) && al16(a.dL_drgb_deferred);
     p.stat_grad = a.stat_grad_accum; p.stat_denom = a.stat_denom; p.stat_maxr = a.stat_max_radii;
     if ((p.stat_grad != nullptr) != (p.stat_denom != nullptr) || (p.stat_grad != nullptr) != (p.stat_maxr != nullptr)) {
         set_error("vegs_backward: stat_grad_accum, stat_denom and stat_max_radii go together");
@@ -619,13 +629,18 @@ int launch_preprocess_bwd(const VegsBackwardArgs& a, const GeomView& g, const fl
         set_error("vegs_backward: VEGS_ACT_OPACITY_SIGMOID needs the raw opacities");
         return VEGS_EINVAL;
     }
-    if (a.shs_rest != nullptr && (a.shs == nullptr || a.dL_dsh_rest == nullptr || a.M < 1 || a.M > kMaxStageCoeffs)) {
-        set_error("vegs_backward: shs_rest needs shs (= f_dc), dL_dsh_rest and 1 <= M <= %d", kMaxStageCoeffs);
+    if (a.dL_drgb_deferred != nullptr && (a.shs == nullptr || a.M > kMaxStageCoeffs)) {
+        set_error("vegs_backward: dL_drgb_deferred needs shs and M <= %d", kMaxStageCoeffs);
+        return VEGS_EINVAL;
+    }
+    if (a.shs_rest != nullptr && (a.shs == nullptr || (a.dL_dsh_rest == nullptr && a.dL_drgb_deferred == nullptr) || a.M < 1 ||
+                                  a.M > kMaxStageCoeffs)) {
+        set_error("vegs_backward: shs_rest needs shs (= f_dc), dL_dsh_rest (or the deferred form) and 1 <= M <= %d", kMaxStageCoeffs);
         return VEGS_EINVAL;
     }
     int mode = kShLdg;
     if (a.shs_rest != nullptr) mode = kShSplit;
-    else if (a.shs != nullptr && a.dL_dsh != nullptr && a.M <= kMaxStageCoeffs && (12 * a.M) % 16 == 0 &&
+    else if (a.shs != nullptr && (a.dL_dsh != nullptr || a.dL_drgb_deferred != nullptr) && a.M <= kMaxStageCoeffs && (12 * a.M) % 16 == 0 &&
              p.shs_vec_ok && !bulk_off)
         mode = kShBulkRows;
     const int blocks = (a.P + kPwThreads - 1) / kPwThreads;

@@ -231,6 +231,13 @@ class RasterizerOptions:
         `xyz_gradient_accum += ||means2D.grad[:, :2]||`, `denom += 1`,
         `max_radii2D = max(., radii)` - what train.py:300-301 + add_densification_stats do in
         separate passes over all Gaussians.
+    deferred_sh_grad
+        A `[P,3]` tensor.  The backward pass of this instance writes the view's clamp-masked dL/dRGB
+        into it INSTEAD of producing dL/dSH (the SH inputs get no gradient from this call); the sum
+        over a step's views is rebuilt later from those 12 bytes per view and Gaussian by
+        `vegs_sh_grad_from_views` (vegs_b200.dist.FlatGradBuffer does both ends).  The gradient of one
+        view is the outer product basis(view direction) x dL/dRGB, so nothing is lost; a
+        view-parallel step then exchanges 3 instead of 3 M words per view and Gaussian.
     live_map_gradients
         CHANGES RESULTS, never default.  The reference computes a gradient of the covariance maps
         (cov_quat, cov_scale) towards the Gaussians' rotations and scales and then overwrites it
@@ -239,10 +246,17 @@ class RasterizerOptions:
         `rotations`, with the blending weights held constant (see VegsBackwardArgs in
         include/vegs_b200.h for the exact definition).
     """
-    __slots__ = ("fused_grad_accumulation", "densification_accumulators", "live_map_gradients")
+    __slots__ = ("fused_grad_accumulation", "densification_accumulators", "live_map_gradients", "deferred_sh_grad")
 
-    def __init__(self, fused_grad_accumulation=False, densification_accumulators=None, live_map_gradients=False):
+    def __init__(self, fused_grad_accumulation=False, densification_accumulators=None, live_map_gradients=False,
+                 deferred_sh_grad=None):
         self.live_map_gradients = bool(live_map_gradients)
+        if deferred_sh_grad is not None:
+            t = deferred_sh_grad
+            if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()
+                    and t.dim() == 2 and t.shape[1] == 3):
+                raise ValueError("deferred_sh_grad must be a contiguous float32 CUDA tensor [P,3]")
+        self.deferred_sh_grad = deferred_sh_grad
         if fused_grad_accumulation not in (False, True, "add", "assign"):
             raise ValueError("fused_grad_accumulation must be False, True / 'add', or 'assign'")
         self.fused_grad_accumulation = "add" if fused_grad_accumulation is True else fused_grad_accumulation
@@ -261,7 +275,7 @@ class RasterizerOptions:
     @property
     def any(self) -> bool:
         return bool(self.fused_grad_accumulation) or self.densification_accumulators is not None \
-            or self.live_map_gradients
+            or self.live_map_gradients or self.deferred_sh_grad is not None
 
 
 def _accum_target(t, shape, mode):
@@ -337,11 +351,14 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
         dmeans3D = out("means3D", (P, 3))
         dmeans2D = torch.empty((P, 3), **f32)
         dopac = out("opacity", tuple(opacities_shape))
+        defer = options.deferred_sh_grad if (options is not None and have_sh and M <= 16) else None
+        if defer is not None and (defer.shape[0] != P or defer.device != device):
+            raise RuntimeError("deferred_sh_grad does not match this call (P or device)")
         if split and (_accum_target(leaves.get("sh"), (P, 1, 3), acc_mode) is None
                       or _accum_target(leaves.get("sh_rest"), (P, M - 1, 3), acc_mode) is None):
             leaves = {k: v for k, v in leaves.items() if k not in ("sh", "sh_rest")}   # VEGS_ACC_SH covers both
-        dsh = out("sh", (P, M_dc, 3), have_sh)
-        dsh_rest = out("sh_rest", (P, M - 1, 3), split)
+        dsh = out("sh", (P, M_dc, 3), have_sh and defer is None)
+        dsh_rest = out("sh_rest", (P, M - 1, 3), split and defer is None)
         dcolors = out("colors", (P, 3), not have_sh)
         dscales = out("scales", (P, 3), have_sr)
         drots = out("rotations", (P, 4), have_sr)
@@ -379,6 +396,7 @@ def _backward_impl(st: _State, bg, means3D, radii, colors_precomp, scales, rotat
         b.opacities = _ptr(opacities_raw)
         b.shs_rest = _ptr(sh_rest)
         b.dL_dsh_rest = _ptr(dsh_rest)
+        b.dL_drgb_deferred = defer.data_ptr() if defer is not None else None
         if options is not None and options.live_map_gradients:
             if out_cov_quat is None or not have_sr:
                 raise RuntimeError("live_map_gradients needs the scale / rotation inputs")
@@ -529,13 +547,14 @@ class GaussianRasterizationSettings(NamedTuple):
 
 class GaussianRasterizer(nn.Module):
     def __init__(self, raster_settings, *, fused_grad_accumulation=False, densification_accumulators=None,
-                 live_map_gradients=False):
+                 live_map_gradients=False, deferred_sh_grad=None):
         """`GaussianRasterizer(raster_settings)` is the reference's constructor (:195-198).  The two
         keyword-only arguments are this package's opt-in extensions for THIS instance; see
         RasterizerOptions."""
         super().__init__()
         self.raster_settings = raster_settings
-        self.options = RasterizerOptions(fused_grad_accumulation, densification_accumulators, live_map_gradients)
+        self.options = RasterizerOptions(fused_grad_accumulation, densification_accumulators, live_map_gradients,
+                                         deferred_sh_grad)
 
     def markVisible(self, positions):
         """Boolean mask of the points in front of the near plane (view z > 0.2)."""

@@ -83,7 +83,7 @@ def _order(params: Dict[str, torch.Tensor], order=None):
     return PARAM_ORDER if all(k in params for k in PARAM_ORDER) and len(params) == len(PARAM_ORDER) else tuple(params.keys())
 
 
-def _layout(params: Dict[str, torch.Tensor], order=None):
+def _layout(params: Dict[str, torch.Tensor], order=None, tail=()):
     """[(name, offset, numel)] of the flat buffer: the five gradients, then the two additive
     statistics.  Every segment starts on a multiple of four floats, so that each `.grad` view is
     16-byte aligned (what the backward kernel's bulk stores / reductions need) whatever P is."""
@@ -91,9 +91,13 @@ def _layout(params: Dict[str, torch.Tensor], order=None):
     out, off = [], 0
     al = lambda n: (n + 3) // 4 * 4
     for k in _order(params, order):
+        if k in tail:
+            continue
         out.append((k, off, params[k].numel())); off = al(off + params[k].numel())
     out.append(("xyz_gradient_accum", off, P)); off = al(off + P)
     out.append(("denom", off, P)); off = al(off + P)
+    for k in tail:                       # segments placed after the statistics (see FlatGradBuffer, deferred SH)
+        out.append((k, off, params[k].numel())); off = al(off + params[k].numel())
     return out, off
 
 
@@ -209,10 +213,19 @@ class FlatGradBuffer:
                    buf.allreduce(accumulate_into=running_stats)
     """
 
-    def __init__(self, params: Dict[str, torch.Tensor], order=None):
+    def __init__(self, params: Dict[str, torch.Tensor], order=None, defer_sh=(), sh_degree: int = 3,
+                 views_per_step: int = 0):
         """`params`: name -> leaf tensor; must contain "means3D" (its first dimension is the Gaussian
-        count).  `order` fixes the segment order (default: PARAM_ORDER, else the dict's order)."""
-        layout, total = _layout(params, order)
+        count).  `order` fixes the segment order (default: PARAM_ORDER, else the dict's order).
+
+        Deferred SH gradient (fewer bytes between the GPUs): `defer_sh` names the SH parameter(s) -
+        ("shs",) or ("shs_dc", "shs_rest") - and `views_per_step` the batch size.  Each view's
+        backward then leaves only its dL/dRGB [P,3] (RasterizerOptions.deferred_sh_grad); the step
+        all-gathers those (3 words per view and Gaussian), all-reduces everything except the SH
+        segments, and rebuilds the SH gradient from the views' camera centres
+        (vegs_sh_grad_from_views): 13 + 3 V instead of 13 + 3 M words per Gaussian on the wire."""
+        self.defer_names = tuple(defer_sh)
+        layout, total = _layout(params, order, tail=self.defer_names)
         dev = params["means3D"].device
         P = params["means3D"].shape[0]
         self.params = params
@@ -227,37 +240,75 @@ class FlatGradBuffer:
                 setattr(self.step_stats, name, v.view(P, 1))
         self.step_stats.max_radii2D = torch.zeros((P,), device=dev)
         self.step_stats.fused = False
-        self._stat_off = layout[-2][1]
+        self._stat_off = [off for name, off, _ in layout if name == "xyz_gradient_accum"][0]
         self._dirty = True        # gradient slices hold stale values until the first view assigns
+        # deferred SH: the SH segments lie after the statistics, everything before them is reduced as usual
+        self._sh_off = layout[-len(self.defer_names)][1] if self.defer_names else total
+        self._defer_active = False
+        self.sh_degree = sh_degree
+        if self.defer_names:
+            rank, world = (dist.get_rank(), dist.get_world_size()) if (dist.is_available() and dist.is_initialized()) else (0, 1)
+            self._rank, self._world = rank, world
+            self.slots_per_rank = max(1, -(-int(views_per_step) // world))
+            self.drgb_all = torch.zeros((world * self.slots_per_rank, P, 3), dtype=torch.float32, device=dev)
+            self.drgb_local = self.drgb_all[rank * self.slots_per_rank:(rank + 1) * self.slots_per_rank]
+            self.campos_all = torch.zeros((world * self.slots_per_rank, 3), dtype=torch.float32, device=dev)
 
-    def begin_step(self) -> None:
+    def begin_step(self, view_campos=None) -> None:
         """Bind every parameter's `.grad` to its slice and clear the step's statistics.  The gradient
         slices are NOT cleared here when the first view is rendered with `first=True` (the kernel
-        overwrites them); call `zero_grads()` for a path that only ever adds."""
+        overwrites them); call `zero_grads()` for a path that only ever adds.
+
+        With a deferred SH gradient, `view_campos` = the camera centres ([3] tensors) of ALL views of
+        the step in batch order (view j is rendered by rank j % world as its (j // world)-th view)."""
         for k, v in self.grad_views.items():
             self.params[k].grad = v
-        self.flat[self._stat_off:].zero_()
+        self.flat[self._stat_off:self._sh_off].zero_()
         self.step_stats.max_radii2D.zero_()
         self._dirty = True
+        self._defer_active = False
+        if self.defer_names and view_campos is not None:
+            if len(view_campos) > self._world * self.slots_per_rank:
+                raise ValueError("more views in the step than views_per_step")
+            self.campos_all.zero_()
+            self.drgb_local.zero_()                 # unused slots must reduce as "not rendered"
+            for j, c in enumerate(view_campos):
+                self.campos_all[(j % self._world) * self.slots_per_rank + j // self._world].copy_(c.reshape(3))
+            self._defer_active = True
 
     def zero_grads(self) -> None:
         self.flat[:self._stat_off].zero_()
+        self.flat[self._sh_off:].zero_()
         self._dirty = False
 
-    def rasterizer_kwargs(self, rasterizer_module, first: bool) -> dict:
+    def rasterizer_kwargs(self, rasterizer_module, first: bool, slot: int = None) -> dict:
         """Constructor keyword arguments for the rasterizer of one view of the step ({} for a module
         without the extensions, e.g. the reference: then autograd adds into the bound `.grad` views,
-        which needs `zero_grads()` first)."""
+        which needs `zero_grads()` first).  `slot` = the index of the view among this rank's views of
+        the step (needed for the deferred SH gradient)."""
         kw = self.step_stats.rasterizer_kwargs(rasterizer_module)
         if self.step_stats.fused:
             kw["fused_grad_accumulation"] = "assign" if (first and self._dirty) else "add"
             self._dirty = False
-        elif self._dirty:
-            self.zero_grads()
+            if self._defer_active:
+                if slot is None or not (0 <= slot < self.slots_per_rank):
+                    raise ValueError("deferred SH gradient: pass the view's slot (0 .. views per rank - 1)")
+                kw["deferred_sh_grad"] = self.drgb_local[slot]
+        else:
+            self._defer_active = False           # a module without the extension: plain accumulation
+            if self._dirty:
+                self.zero_grads()
         return kw
 
     def allreduce(self, group=None, accumulate_into: DensificationStats = None) -> None:
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        active = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+        if self._defer_active:
+            if active:
+                dist.all_gather_into_tensor(self.drgb_all.view(-1), self.drgb_local.reshape(-1).clone(), group=group)
+                dist.all_reduce(self.flat[:self._sh_off], op=dist.ReduceOp.SUM, group=group)
+                dist.all_reduce(self.step_stats.max_radii2D, op=dist.ReduceOp.MAX, group=group)
+            self._rebuild_sh_grad()
+        elif active:
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
             dist.all_reduce(self.step_stats.max_radii2D, op=dist.ReduceOp.MAX, group=group)
         if accumulate_into is not None:
@@ -265,3 +316,24 @@ class FlatGradBuffer:
             accumulate_into.xyz_gradient_accum += s.xyz_gradient_accum
             accumulate_into.denom += s.denom
             torch.maximum(accumulate_into.max_radii2D, s.max_radii2D, out=accumulate_into.max_radii2D)
+
+    def _rebuild_sh_grad(self) -> None:
+        """dL/dSH of the whole step from every view's dL/dRGB (vegs_sh_grad_from_views), written
+        straight into the SH gradient segment(s) of the flat buffer."""
+        import ctypes as C
+        from . import _lib
+        lib = _lib.load()
+        names = self.defer_names
+        dc = self.grad_views[names[0]]
+        rest = self.grad_views[names[1]] if len(names) > 1 else None
+        M = int(dc.shape[1]) + (int(rest.shape[1]) if rest is not None else 0)
+        means = self.params["means3D"].detach()
+        P = int(means.shape[0])
+        dev = means.device
+        with torch.cuda.device(dev):
+            stream = torch.cuda.current_stream(dev)
+            rc = lib.vegs_sh_grad_from_views(P, int(self.sh_degree), M, int(self.drgb_all.shape[0]), means.data_ptr(),
+                                             self.campos_all.data_ptr(), self.drgb_all.data_ptr(), dc.data_ptr(),
+                                             rest.data_ptr() if (rest is not None and rest.numel()) else None, 0,
+                                             C.c_void_p(stream.cuda_stream))
+            _lib.check(rc, "vegs_sh_grad_from_views")
