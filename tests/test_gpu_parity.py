@@ -327,8 +327,8 @@ def test_fused_adam_matches_torch_adam_step_for_step():
 
 def test_view_parallel_trainer_single_gpu():
     """The view-parallel driver (vegs_b200/parallel_train.py) end to end on one GPU: SplatModel with
-    FusedAdam, views rendered through forward_raw with the fused accumulation into the flat buffer,
-    a densification inside the run; and the first step's parameters against the same step done the
+    FusedAdam, views rendered through forward_raw with the fused accumulation into the flat buffer and
+    the deferred SH gradient (split f_dc / f_rest layout), a densification inside the run; and the first step's parameters against the same step done the
     reference's way (getters + drop-in forward, autograd accumulation, torch.optim.Adam)."""
     import vegs_b200.diff_gaussian_rasterization as dgr
     from vegs_b200.optim import FusedAdam
@@ -363,7 +363,7 @@ def test_view_parallel_trainer_single_gpu():
     fused = SplatModel(scene, device=dev); fused.training_setup(args, FusedAdam)
     plain = SplatModel(scene, device=dev); plain.training_setup(args)
     tf = ViewParallelTrainer(fused, list(range(4)), render_raw, args, views_per_step=4, rasterizer_module=dgr,
-                             cameras_extent=50.0, seed=5)
+                             cameras_extent=50.0, seed=5, camera_center=lambda ci: cams[ci].campos)
     tp = ViewParallelTrainer(plain, list(range(4)), render_plain, args, views_per_step=4, cameras_extent=50.0, seed=5)
     a, b = tf.step(), tp.step()
     assert a["views"] == b["views"] and abs(a["loss"] - b["loss"]) < 1e-4

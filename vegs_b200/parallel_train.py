@@ -45,7 +45,10 @@ class ViewParallelTrainer:
     def __init__(self, model, cameras: Sequence, render_view: Callable, args, *, views_per_step: int = 8,
                  rasterizer_module=None, cameras_extent: float = 1.0, group=None, seed: int = 0,
                  checkpoint_dir: Optional[str] = None, checkpoint_iterations: Sequence[int] = (),
-                 white_background: bool = False):
+                 white_background: bool = False, camera_center: Optional[Callable] = None):
+        """`camera_center(camera) -> [3] tensor` (optional, with a rasterizer module that has the
+        extensions): switches the step to the deferred SH gradient - every view leaves dL/dRGB [P,3],
+        the ranks all-gather those instead of all-reducing the SH gradient (FlatGradBuffer)."""
         self.model, self.cameras, self.render_view, self.args = model, list(cameras), render_view, args
         self.views_per_step = views_per_step
         self.module = rasterizer_module
@@ -55,6 +58,7 @@ class ViewParallelTrainer:
         self.seed = seed
         self.ckpt_dir, self.ckpt_iters = checkpoint_dir, set(checkpoint_iterations)
         self.white_background = white_background
+        self.camera_center = camera_center
         self._order_rng = random.Random(seed)        # the same camera order on every rank
         self._stack: List[int] = []
         self._buf = None
@@ -87,16 +91,19 @@ class ViewParallelTrainer:
         params = self._flat_params()
         ids = tuple(id(v) for v in params.values())
         if self._buf is None or self._buf_ids != ids:       # first step, or densification replaced the tensors
-            self._buf = vdist.FlatGradBuffer(params, order=tuple(params.keys()))
+            defer = ("shs_dc", "shs_rest") if (self.camera_center is not None and self.module is not None) else ()
+            self._buf = vdist.FlatGradBuffer(params, order=tuple(params.keys()), defer_sh=defer,
+                                             views_per_step=self.views_per_step)
             self._buf_ids = ids
         buf = self._buf
-        buf.begin_step()
         batch = self._next_batch()
+        buf.sh_degree = int(getattr(m, "active_sh_degree", 3))
+        buf.begin_step([self.camera_center(self.cameras[v]) for v in batch] if buf.defer_names else None)
         mine = [batch[i] for i in vdist.shard_views(len(batch), self.rank, self.world)]
         module = self.module if self.module is not None else object
         loss_sum = 0.0
         for i, v in enumerate(mine):
-            kw = buf.rasterizer_kwargs(module, first=(i == 0))
+            kw = buf.rasterizer_kwargs(module, first=(i == 0), slot=i)
             loss, viewspace, radii = self.render_view(m, self.cameras[v], kw)
             loss.backward()
             buf.step_stats.add_view(viewspace.grad, radii)
