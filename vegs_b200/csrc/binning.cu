@@ -7,10 +7,10 @@
 // consecutive sorted positions:
 //   tile_count   sums the tiles touched by the chunk                    -> chunksum[chunk]
 //   tile_spine   exclusive scan over chunks, total = num_rendered       -> chunksum, *num_rendered
-//   emit         scans the chunk locally, then writes the chunk's instances (tile id, Gaussian id)
-//                with one thread per INSTANCE (binary search for the owning Gaussian), so big
-//                splats do not serialise a thread as the reference's per-Gaussian loop does and
-//                the writes are fully coalesced.
+//   emit         scans the chunk locally, then writes the chunk's instances (tile id, Gaussian id):
+//                a Gaussian of up to four tiles by the thread that scanned it, a bigger one by a
+//                whole warp with one lane per INSTANCE, so big splats do not serialise a thread
+//                as the reference's per-Gaussian loop does.
 // Instances of one Gaussian are emitted in row-major rectangle order and Gaussians in depth
 // order, so a stable sort by tile id alone reproduces the reference's (tile, depth, index) order.
 // Roofline: HBM; algorithmic bytes: 12 per sorted Gaussian (index + rectangle) per pass and
@@ -139,6 +139,43 @@ tile_spine_kernel(uint32_t* __restrict__ chunksum, uint32_t* __restrict__ partba
     }
 }
 
+constexpr int kEmitSmall = 4;      // a Gaussian with at most this many tiles is emitted by its own thread
+
+// One instance: the tile id as the sort key, the Gaussian id as the value.  With unit masks
+// (ids < 2^24, common.cuh) the top byte of the value says which of the tile's eight 8x4 compositing
+// units the Gaussian can reach: its pixel box (preprocess.cu; r.z, r.w) against 2 unit columns and
+// 4 unit rows - the same outcome as unit_box() (composite_common.cuh).
+__device__ __forceinline__ void emit_instance(uint32_t out, uint32_t tx, uint32_t ty, uint32_t g, const uint4 r,
+                                              int grid_x, uint32_t* __restrict__ tkeys,
+                                              uint32_t* __restrict__ tvals, uint32_t R, bool has_masks, int W, int H) {
+    if (out >= R) return;
+    tkeys[out] = ty * (uint32_t)grid_x + tx;
+    uint32_t val = g;
+    if (has_masks) {
+        const int gx0 = (int)(r.z & 0xffffu), gx1 = (int)(r.z >> 16) - 1;
+        const int gy0 = (int)(r.w & 0xffffu), gy1 = (int)(r.w >> 16) - 1;
+        uint32_t okx = 0, oky = 0;
+#pragma unroll
+        for (int hx = 0; hx < 2; hx++) {
+            const int bx0 = (int)tx * kTile + hx * 8;
+            const int bx1 = min(bx0 + 7, W - 1);
+            okx |= ((bx0 < W && max(gx0, bx0) <= min(gx1, bx1)) ? 1u : 0u) << hx;
+        }
+#pragma unroll
+        for (int hy = 0; hy < 4; hy++) {
+            const int by0 = (int)ty * kTile + hy * 4;
+            const int by1 = min(by0 + 3, H - 1);
+            oky |= ((by0 < H && max(gy0, by0) <= min(gy1, by1)) ? 1u : 0u) << hy;
+        }
+        uint32_t mask = 0;      // bit blk = (row hy) * 2 + (column hx)
+#pragma unroll
+        for (int hy = 0; hy < 4; hy++)
+            if ((oky >> hy) & 1u) mask |= okx << (2 * hy);
+        val |= mask << 24;
+    }
+    tvals[out] = val;
+}
+
 __global__ void __launch_bounds__(kEmitThreads)
 emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__ rect,
             const uint32_t* __restrict__ chunksum, const uint32_t* __restrict__ partbase,
@@ -148,6 +185,9 @@ emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__
     __shared__ uint4 s_rect[kEmitChunk];   // tile rect (x, y) and pixel box (z, w) of the chunk's Gaussians
     __shared__ uint32_t s_off[kEmitChunk + 1];
     __shared__ uint32_t s_warp[kEmitThreads / 32];
+    __shared__ uint16_t s_big[kEmitChunk];  // chunk positions of the Gaussians emitted by a warp
+    __shared__ uint32_t s_nbig;
+    const bool has_masks = pbox != nullptr;
 
     // the grid is an upper bound of the work items (abi.cu): surplus CTAs have nothing to do
     if (blockIdx.x >= partbase[nchunks]) return;
@@ -165,6 +205,7 @@ emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__
     const uint32_t i_begin = part * kEmitPart;
     const uint32_t i_end = min(n_inst, i_begin + kEmitPart);
     if (i_begin >= n_inst) return;
+    if (threadIdx.x == 0) s_nbig = 0;
 
     // Thread t owns kEmitPerThread consecutive sorted positions (position order = depth order).
     uint32_t cnt[kEmitPerThread];
@@ -207,50 +248,46 @@ emit_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__
     if (threadIdx.x == kEmitThreads - 1) s_off[kEmitChunk] = run;
     __syncthreads();
 
-    // One thread per instance.
-    for (uint32_t i = i_begin + threadIdx.x; i < i_end; i += kEmitThreads) {
-        uint32_t lo = 0, hi = kEmitChunk;
-        while (hi - lo > 1) {
-            const uint32_t mid = (lo + hi) >> 1;
-            if (s_off[mid] <= i) lo = mid; else hi = mid;
-        }
-        const uint4 r = s_rect[lo];
-        const uint32_t k = i - s_off[lo];
-        const uint32_t x0 = r.x & 0xffffu, w = (r.x >> 16) - x0, y0 = r.y & 0xffffu;
-        const uint32_t ty = y0 + k / w;
-        const uint32_t tx = x0 + k % w;
-        const uint32_t out = gbase + i;
-        if (out < R) {
-            tkeys[out] = ty * (uint32_t)grid_x + tx;
-            uint32_t val = s_g[lo];
-            if (pbox != nullptr) {
-                // Which of the tile's eight 8x4 compositing units can the Gaussian reach: its pixel
-                // box (preprocess.cu) against 2 unit columns and 4 unit rows - the same outcome as
-                // unit_box() (composite_common.cuh); carried in the top byte of the list word (ids
-                // are < 2^24 in this mode).
-                const uint2 pb = make_uint2(r.z, r.w);
-                const int gx0 = (int)(pb.x & 0xffffu), gx1 = (int)(pb.x >> 16) - 1;
-                const int gy0 = (int)(pb.y & 0xffffu), gy1 = (int)(pb.y >> 16) - 1;
-                uint32_t okx = 0, oky = 0;
+    // Emission.  Most Gaussians at LiDAR density touch one to four tiles: those are written by the
+    // thread that already holds their count and offset (no search, no division; a warp's stores
+    // land in one short run of the output).  A Gaussian with more tiles goes on a work list and is
+    // emitted by a whole warp, one lane per instance, so a big splat does not serialise a thread.
+    // Either way only the instances inside this part's range [i_begin, i_end) are written.
+    {
+        uint32_t off = woff + inc - tsum;
 #pragma unroll
-                for (int hx = 0; hx < 2; hx++) {
-                    const int bx0 = (int)tx * kTile + hx * 8;
-                    const int bx1 = min(bx0 + 7, W - 1);
-                    okx |= ((bx0 < W && max(gx0, bx0) <= min(gx1, bx1)) ? 1u : 0u) << hx;
+        for (int j = 0; j < kEmitPerThread; j++) {
+            const uint32_t l = threadIdx.x * kEmitPerThread + j;
+            if (cnt[j] > (uint32_t)kEmitSmall) {
+                if (off < i_end && off + cnt[j] > i_begin) s_big[atomicAdd(&s_nbig, 1u)] = (uint16_t)l;
+            } else if (cnt[j] != 0u) {
+                const uint4 r = s_rect[l];
+                const uint32_t x0 = r.x & 0xffffu, x1 = r.x >> 16;
+                uint32_t tx = x0, ty = r.y & 0xffffu;
+                for (uint32_t k = 0; k < cnt[j]; k++) {
+                    const uint32_t i = off + k;
+                    if (i >= i_begin && i < i_end)
+                        emit_instance(gbase + i, tx, ty, s_g[l], r, grid_x, tkeys, tvals, R, has_masks, W, H);
+                    if (++tx == x1) { tx = x0; ty++; }
                 }
-#pragma unroll
-                for (int hy = 0; hy < 4; hy++) {
-                    const int by0 = (int)ty * kTile + hy * 4;
-                    const int by1 = min(by0 + 3, H - 1);
-                    oky |= ((by0 < H && max(gy0, by0) <= min(gy1, by1)) ? 1u : 0u) << hy;
-                }
-                uint32_t mask = 0;      // bit blk = (row hy) * 2 + (column hx)
-#pragma unroll
-                for (int hy = 0; hy < 4; hy++)
-                    if ((oky >> hy) & 1u) mask |= okx << (2 * hy);
-                val |= mask << 24;
             }
-            tvals[out] = val;
+            off += cnt[j];
+        }
+    }
+    __syncthreads();
+    const uint32_t nbig = s_nbig;
+    for (uint32_t b = warp; b < nbig; b += kEmitThreads / 32) {
+        const uint32_t l = s_big[b];
+        const uint4 r = s_rect[l];
+        const uint32_t g = s_g[l];
+        const uint32_t first = s_off[l], n_l = s_off[l + 1] - first;
+        const uint32_t x0 = r.x & 0xffffu, w = (r.x >> 16) - x0, y0 = r.y & 0xffffu;
+        const uint32_t k_lo = i_begin > first ? i_begin - first : 0u;
+        const uint32_t k_hi = min(n_l, i_end - first);          // first < i_end for every listed Gaussian
+        for (uint32_t k = k_lo + lane; k < k_hi; k += 32) {
+            const uint32_t row = k / w;
+            emit_instance(gbase + first + k, x0 + (k - row * w), y0 + row, g, r, grid_x, tkeys, tvals, R, has_masks,
+                          W, H);
         }
     }
 }
