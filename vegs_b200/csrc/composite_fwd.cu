@@ -24,12 +24,13 @@
 //   S1  each warp bit-transposes its 32 hit masks into per-pixel hit lists and compacts each
 //       pixel's operands to the front of its row segment
 //   S2  warp 0, lane = pixel: the sequential chain over that pixel's hits of the working set, in
-//       list order and in the reference's float operation order: T before each hit, the
-//       saturation point (T(1-alpha) < 1e-4 stops the pixel, that Gaussian is not blended),
-//       n_contrib, plus the depth sum — branch-free rounds of four hits over dense arrays
+//       list order and in the reference's float operation order: T, the saturation point
+//       (T(1-alpha) < 1e-4 stops the pixel, that Gaussian is not blended), n_contrib, plus the
+//       depth sum — rounds of four hits over dense arrays, a bare multiply chain with a fallback
+//       for the rare round that holds a saturation; T at the start of each segment is kept for S3
 //   S3  pixel-parallel per 32-candidate segment (W warps, lane = pixel): colour and scale sums and
-//       the slerp quaternion product of the segment's hits, from the (1 - alpha, T) pairs S2 left
-//       in the matrix (no second exp per hit)
+//       the slerp quaternion product of the segment's hits, from the stored 1 - alpha (no second
+//       exp per hit) and the segment's incoming T, advanced by the same multiplies as in S2
 //   S4  warps 0 and 1 fold the W segment partials into the pixel state, in list order
 // so the expensive work (exp, sin, cos, quaternion product per contribution) is spread over W
 // warps per pixel block and 8 W warps per tile, the fixed costs of a working set are paid per kSuper
@@ -87,15 +88,18 @@ struct FwdParams {
 struct FwdSmem {
     float2 M[32 * kRow + 4];        // [pixel][slot], rows padded by one entry so that lanes reading the same
                                     // column of their own rows spread over the banks: (1 - alpha, depth * alpha)
-                                    // after S0; S2 replaces the second word by T, the transmittance before the hit
     float4 C[kSuper], D[kSuper], E[kSuper];   // blend records of candidates with a hit (colour, scale, rotation)
     uint2 ring[kRing];              // candidates in list order: (Gaussian id, ordinal in the tile's list)
     uint32_t bits[kWarps][32];      // [segment][pixel]: hits of the pixel inside the segment
     uint32_t stop_at[32];           // first (segment * 32 + hit index) the pixel does not blend (kSuper = none)
     float part[kWarps][10][32];     // segment partials: rows 0-2 colour, 3-5 scale, 6-9 quaternion
+    float tin[kWarps][32];          // [segment][pixel]: transmittance in front of the segment's first hit
     uint32_t seg_bal[kWarps];       // per segment: ballot of the slots with a hit
     uint32_t scan_cnt[2][kScanSub * kWarps];   // survivors per (sub-step, warp) of a scan step (double-buffered)
     int all_done;
+#ifdef VEGS_FWD_PAD
+    unsigned char pad[VEGS_FWD_PAD];    // occupancy experiments: lowers the number of resident CTAs
+#endif
 };
 
 static_assert(sizeof(FwdSmem) <= 227 * 1024, "forward working set does not fit the 227 KB of shared memory per CTA");
@@ -324,56 +328,84 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
         dbg_sets++; dbg_cand += (uint32_t)m; dbg_pix += (uint32_t)__syncthreads_count(0) + __reduce_add_sync(0xffffffffu, (uint32_t)__popc(h));
 #endif
 
-        // ---- S2: warp 0, lane = pixel: sequential transmittance chain over the working set
+        // ---- S2: warp 0, lane = pixel: sequential transmittance chain over the working set.
+        // This is the one phase the other warps of the CTA wait for, and it is a dependent chain, so
+        // what counts is the number of dependent operations per hit.  Rounds of four hits: the four
+        // products T(1 - alpha) are formed as a bare multiply chain (a slot past the end of the
+        // pixel's list multiplies by one); T never grows, so the round contains a saturation
+        // (T(1 - alpha) < 1e-4: that Gaussian is not blended and the pixel is finished,
+        // forward.cu:382-386) exactly when its last product is below the threshold.  That happens at
+        // most once per pixel in the whole launch: a round without one in any lane - nearly all -
+        // takes the products as they are, and the depth sum runs beside them as a second,
+        // independent chain of four fused multiply-adds; a round with one falls back to the
+        // hit-by-hit form.  Same float operations in the same order as the reference either way.
         if (warp == 0) {
             // first (segment * 32 + hit index) the pixel does not blend; a finished pixel blends nothing
             uint32_t stop = done ? 0u : (uint32_t)kSuper;
-            {
-                int last_w = -1, last_j = 0;
-                bool stopped = done;         // every lane stays in the loops below (warp votes)
+            int last_w = -1, last_j = 0;
+            bool stopped = done;             // every lane stays in the loops below (warp votes)
 #pragma unroll 1
-                for (int w = 0; w < kWarps; w++) {
-                    if (((seg_mask >> w) & 1u) == 0u) continue;     // no hit in this segment at all
-                    const int cnt = stopped ? 0 : __popc(sm.bits[w][lane]);
-                    float2* row = sm.M + lane * kRow + w * 32;
-                    // the lanes run in lock step: rounds of four hits until the longest list of the
-                    // segment is done.  A round is branch-free: a slot past the end of the pixel's
-                    // list (or past its saturation) acts as alpha = 0, which leaves T and the depth
-                    // sum exactly unchanged.
-                    const int rounds = (__reduce_max_sync(0xffffffffu, cnt) + 3) >> 2;
-                    for (int r = 0; r < rounds; r++) {
-                        float2 m[4];
+            for (int w = 0; w < kWarps; w++) {
+                if (((seg_mask >> w) & 1u) == 0u) continue;     // no hit in this segment at all
+                int cnt = stopped ? 0 : __popc(sm.bits[w][lane]);
+                const float2* row = sm.M + lane * kRow + w * 32;
+                sm.tin[w][lane] = T;         // S3 rebuilds the transmittance in front of each hit from here
+                const int rounds = (__reduce_max_sync(0xffffffffu, cnt) + 3) >> 2;
+                float2 m[4];
 #pragma unroll
-                        for (int k = 0; k < 4; k++) m[k] = row[4 * r + k];   // may run into the next columns: unused
+                for (int k = 0; k < 4; k++) m[k] = row[k];      // may run into the next columns: unused
+                for (int r = 0; r < rounds; r++) {
+                    float x[4], y[4];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        const bool active = 4 * r + k < cnt;
+                        x[k] = active ? m[k].x : 1.0f;          // 1 - alpha
+                        y[k] = active ? m[k].y : 0.0f;          // depth * alpha
+                    }
+                    if (r + 1 < rounds) {
+#pragma unroll
+                        for (int k = 0; k < 4; k++) m[k] = row[4 * (r + 1) + k];
+                    }
+                    const float t1 = __fmul_rn(T, x[0]), t2 = __fmul_rn(t1, x[1]), t3 = __fmul_rn(t2, x[2]),
+                                t4 = __fmul_rn(t3, x[3]);
+                    if (!__any_sync(0xffffffffu, t4 < 0.0001f)) {
+                        // depth is accumulated here, in the reference's running order, so it stays
+                        // bit-identical: depth values are ~1e2, re-associating that sum per segment
+                        // already costs more than the 1e-5 tolerance
+                        Dacc = __fmaf_rn(y[0], T, Dacc);
+                        Dacc = __fmaf_rn(y[1], t1, Dacc);
+                        Dacc = __fmaf_rn(y[2], t2, Dacc);
+                        Dacc = __fmaf_rn(y[3], t3, Dacc);
+                        T = t4;
+                    } else {
 #pragma unroll
                         for (int k = 0; k < 4; k++) {
                             const int j = 4 * r + k;
-                            const bool active = j < cnt && !stopped;
-                            const float test_T = __fmul_rn(T, active ? m[k].x : 1.0f);   // T * (1 - alpha)
-                            // T(1 - alpha) < 1e-4: not blended, the pixel is finished (forward.cu:382-386)
+                            const bool active = j < cnt;
+                            const float test_T = __fmul_rn(T, x[k]);
                             const bool sat = active && test_T < 0.0001f;
-                            // transmittance in front of this hit, in the word whose depth * alpha
-                            // has just been consumed: S3 reads (1 - alpha, T) and needs no exp
-                            if (active && !sat) row[j].y = T;
-                            // depth is accumulated here, in the reference's running order, so it
-                            // stays bit-identical: depth values are ~1e2, re-associating that sum
-                            // per segment already costs more than the 1e-5 tolerance
-                            Dacc = __fmaf_rn((active && !sat) ? m[k].y : 0.0f, T, Dacc);
-                            if (active && !sat) { last_w = w; last_j = j; }
-                            if (sat) { stop = (uint32_t)(w * 32 + j); stopped = true; }
-                            T = sat ? T : test_T;
+                            if (active && !sat) {
+                                Dacc = __fmaf_rn(y[k], T, Dacc);
+                                T = test_T;
+                            }
+                            if (sat) {           // hits j.. of this pixel are not blended, here or later
+                                stop = (uint32_t)(w * 32 + j);
+                                stopped = true;
+                                cnt = j;
+                            }
                         }
                     }
                 }
-                done = stopped;
-                if (last_w >= 0) {
-                    // slot of the last blended hit: the (last_j + 1)-th set bit of its segment's mask
-                    const int last_t = last_w * 32 + (int)__fns(sm.bits[last_w][lane], 0, last_j + 1);
-                    last_contributor = sm.ring[(head + last_t) % (uint32_t)kRing].y + 1u;   // ordinal in the tile's list
-                    uint32_t idx = hit_base;                                           // position in the unit's hit list
-                    for (int w2 = 0; w2 < last_w; w2++) idx += __popc(sm.seg_bal[w2]);
-                    last_hit = idx + __popc(sm.seg_bal[last_w] & ((1u << (last_t & 31)) - 1u)) + 1u;
-                }
+                if (cnt > 0) { last_w = w; last_j = cnt - 1; }      // hits 0 .. cnt-1 of the segment were blended
+            }
+            done = stopped;
+            if (last_w >= 0) {
+                // slot of the last blended hit: the (last_j + 1)-th set bit of its segment's mask
+                const int last_t = last_w * 32 + (int)__fns(sm.bits[last_w][lane], 0, last_j + 1);
+                last_contributor = sm.ring[(head + last_t) % (uint32_t)kRing].y + 1u;   // ordinal in the tile's list
+                uint32_t idx = hit_base;                                           // position in the unit's hit list
+                for (int w2 = 0; w2 < last_w; w2++) idx += __popc(sm.seg_bal[w2]);
+                last_hit = idx + __popc(sm.seg_bal[last_w] & ((1u << (last_t & 31)) - 1u)) + 1u;
             }
             sm.stop_at[lane] = stop;
             const bool all = __all_sync(0xffffffffu, done);
@@ -390,15 +422,18 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
             float c0 = 0.f, c1 = 0.f, c2 = 0.f, s0 = 0.f, s1 = 0.f, s2 = 0.f;
             float qw = 1.f, qx = 0.f, qy = 0.f, qz = 0.f;
             int j = 0;
+            float Tn = sm.tin[warp][lane];   // transmittance in front of the segment's first hit (S2)
             while (bits != 0u) {
                 const int t = warp * 32 + __ffs(bits) - 1;
                 bits &= bits - 1;
                 if ((uint32_t)(warp * 32 + j) >= stop) break;
                 // alpha from the stored 1 - alpha (exact to half an ulp of 1: 3e-8, far inside the 1e-5
-                // tolerance of the colour / scale / quaternion maps), T from the sequential pass
-                const float2 mt = sm.M[lane * kRow + warp * 32 + j];
-                const float alpha = __fsub_rn(1.0f, mt.x);
-                const float Tb = mt.y;
+                // tolerance of the colour / scale / quaternion maps); T by the same multiply chain as
+                // the sequential pass, so it is that pass's T bit for bit
+                const float om_alpha = sm.M[lane * kRow + warp * 32 + j].x;
+                const float alpha = __fsub_rn(1.0f, om_alpha);
+                const float Tb = Tn;
+                Tn = __fmul_rn(Tn, om_alpha);
                 j++;
                 const float4 c = sm.C[t];    // r, g, b, 1 / sin(theta)
                 const float4 d = sm.D[t];    // scale xyz, rot.r
