@@ -208,17 +208,19 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_bwd_kernel(const B
             const float2* Mrow = sm.M + lane * kSuper + warp * 32;
             // ---- S2 pass 1: warp = segment, lane = pixel: the segment as an affine map
             {
-                float P = 1.0f, a = 0.0f, b = 1.0f;
+                float a = 0.0f, b = 1.0f;
                 uint32_t bits = mybits & valid;
                 while (bits != 0u) {
                     const int sl = __ffs(bits) - 1;
                     bits &= bits - 1;
                     const float2 m = Mrow[swz(sl, lane)];
                     const float om = 1.0f - m.x;
-                    P *= __frcp_rn(om);
                     a = m.x * m.y + om * a;
                     b *= om;
                 }
+                // transmittance ratio across the segment: one reciprocal of the product (blended
+                // hits keep T >= 1e-4, so b >= 1e-4: no underflow) instead of one per hit
+                const float P = __frcp_rn(b);
                 sm.agg[warp][0][lane] = P;
                 sm.agg[warp][1][lane] = a;
                 sm.agg[warp][2][lane] = b;
