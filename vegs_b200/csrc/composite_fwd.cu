@@ -400,8 +400,10 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
             }
             done = stopped;
             if (last_w >= 0) {
-                // slot of the last blended hit: the (last_j + 1)-th set bit of its segment's mask
-                const int last_t = last_w * 32 + (int)__fns(sm.bits[last_w][lane], 0, last_j + 1);
+                // slot of the last blended hit: the (last_j + 1)-th set bit of its segment's mask -
+                // the highest one unless the pixel saturated inside that segment
+                const uint32_t lb = sm.bits[last_w][lane];
+                const int last_t = last_w * 32 + (last_j + 1 == __popc(lb) ? 31 - __clz(lb) : (int)__fns(lb, 0, last_j + 1));
                 last_contributor = sm.ring[(head + last_t) % (uint32_t)kRing].y + 1u;   // ordinal in the tile's list
                 uint32_t idx = hit_base;                                           // position in the unit's hit list
                 for (int w2 = 0; w2 < last_w; w2++) idx += __popc(sm.seg_bal[w2]);
@@ -438,14 +440,16 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
                 const float4 c = sm.C[t];    // r, g, b, 1 / sin(theta)
                 const float4 d = sm.D[t];    // scale xyz, rot.r
                 const float4 e = sm.E[t];    // rot xyz, theta
-                c0 = __fmaf_rn(__fmul_rn(c.x, alpha), Tb, c0);
-                c1 = __fmaf_rn(__fmul_rn(c.y, alpha), Tb, c1);
-                c2 = __fmaf_rn(__fmul_rn(c.z, alpha), Tb, c2);
-                s0 = __fmaf_rn(__fmul_rn(d.x, alpha), Tb, s0);
-                s1 = __fmaf_rn(__fmul_rn(d.y, alpha), Tb, s1);
-                s2 = __fmaf_rn(__fmul_rn(d.z, alpha), Tb, s2);
-                // r = mix(identity, q, w) with q = (w = rot.r, x, y, z), w = alpha * T
+                // blend weight alpha * T, formed once: value * (alpha * T) instead of the reference's
+                // (value * alpha) * T differs in the last bit of each term only
                 const float wgt = __fmul_rn(alpha, Tb);
+                c0 = __fmaf_rn(c.x, wgt, c0);
+                c1 = __fmaf_rn(c.y, wgt, c1);
+                c2 = __fmaf_rn(c.z, wgt, c2);
+                s0 = __fmaf_rn(d.x, wgt, s0);
+                s1 = __fmaf_rn(d.y, wgt, s1);
+                s2 = __fmaf_rn(d.z, wgt, s2);
+                // r = mix(identity, q, w) with q = (w = rot.r, x, y, z), w = alpha * T
                 const float om = __fsub_rn(1.0f, wgt);
                 float rw, rx, ry, rz;
                 if (d.w > 1.0f - FLT_EPSILON) {
