@@ -147,6 +147,16 @@ __global__ void __launch_bounds__(kSuper, kMinCtas) composite_fwd_kernel(const F
     const int bx0 = tile_x * kTile + (blk & 1) * kUnitW;
     const int by0 = tile_y * kTile + (blk >> 1) * kUnitH;
     if (bx0 >= p.W || by0 >= p.H) return;                     // block entirely outside the image
+#ifdef VEGS_FWD_SKIP_TOP
+    if ((int)(unit >> 3) < VEGS_FWD_SKIP_TOP) {               // timing experiment: without the longest lists
+        const int qx = bx0 + (threadIdx.x & 7), qy = by0 + ((threadIdx.x >> 3) & 3);
+        if (threadIdx.x < 32 && qx < p.W && qy < p.H) {
+            const size_t q = (size_t)qy * p.W + qx;
+            p.n_contrib[q] = 0; p.last_hit[q] = 0; p.out_alpha[q] = 0.f;
+        }
+        return;
+    }
+#endif
     const int bx1 = min(bx0 + kUnitW - 1, p.W - 1), by1 = min(by0 + kUnitH - 1, p.H - 1);
     // lane = pixel (used by S2..S4)
     const int px = bx0 + (lane & 7), py = by0 + (lane >> 3);
