@@ -125,6 +125,8 @@ class Workload:
         self.my_views = vdist.shard_views(args.views, rank, world)
         self.flat = None
         self.buf = None
+        self.factor_sh = False           # set by main(): vegs_b200 arm, exactly one view per rank
+        self.campos_all = torch.stack([c.campos for c in self.cams]).contiguous()
         self.h2d_bytes = sum(self.host_targets[v].numel() * 4 for v in range(args.views))
 
     def settings(self, mod, cam):
@@ -194,7 +196,10 @@ class Workload:
             if fused:
                 self.buf.allreduce()
             else:
-                self.flat = self.vdist.allreduce_step(p, stats, flat=self.flat)
+                # one view per rank (vegs_b200 arm only): the SH gradient crosses NVLink as its rank-one
+                # factor dL/dRGB and is rebuilt by the library's kernel (vegs_b200/dist.py)
+                single = self.campos_all if (self.factor_sh and views is None) else None
+                self.flat = self.vdist.allreduce_step(p, stats, flat=self.flat, single_view_campos=single)
         if not resident:
             return float(total.item())   # device -> host read of the step's result
         return total
@@ -368,6 +373,7 @@ def main():
         # only the vegs_b200 arm may map libvegs_b200.so: the reference process must stay free of it
         from vegs_b200 import _lib
     wl = Workload(args, device, rank, world)
+    wl.factor_sh = ours and world > 1 and world == args.views
 
     launches0 = _lib.launch_count() if ours else 0
     sampler = ClockSampler(local_rank) if rank == 0 else None
@@ -392,6 +398,10 @@ def main():
                             grad_accumulation="autograd add per view, densification statistics by the caller "
                                               "(the reference's own calling convention, identical in both arms)"),
                 rasterizer=kind,
+                reduction=("none (one GPU)" if world == 1 else
+                           "vegs_b200.dist.allreduce_step: NCCL all-reduce of the .grad tensors and statistics" +
+                           ("; one view per rank, so the SH gradient is exchanged as dL/dRGB (all-gather of 3 words "
+                            "per Gaussian and rank) and rebuilt by vegs_sh_grad_from_views" if wl.factor_sh else "")),
                 e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=4 * world),
                 gpu_launches=int(launches), clocks=clocks)
 

@@ -49,7 +49,13 @@ for s in "$@"; do
       fi
       timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --steps ${STEPS:-10} --warmup 3 > gpurun_out/${tag}_scale_$N.json 2> gpurun_out/${tag}_scale_$N.err
       echo "scale $N rc=$?" | tee -a $S
-      if [ -n "${MULTI_OURS_ONLY:-}" ]; then cat $S; exit 0; fi
+      if [ -n "${MULTI_OURS_ONLY:-}" ]; then
+        if [ -n "${MULTI_BUSBW:-}" ]; then
+          timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29519 scripts/nccl_busbw.py > gpurun_out/${tag}_nccl_busbw_$N.json 2> gpurun_out/${tag}_nccl_busbw_$N.err
+          echo "nccl busbw $N rc=$? $(cat gpurun_out/${tag}_nccl_busbw_$N.json)" | tee -a $S
+        fi
+        cat $S; exit 0
+      fi
       timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29518 bench.py --impl reference --gpus $N --steps 4 --warmup 3 > gpurun_out/${tag}_scale_${N}_ref.json 2> gpurun_out/${tag}_scale_${N}_ref.err
       echo "scale ref $N rc=$?" | tee -a $S
       timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29519 scripts/nccl_busbw.py > gpurun_out/${tag}_nccl_busbw_$N.json 2> gpurun_out/${tag}_nccl_busbw_$N.err
@@ -116,7 +122,7 @@ for s in "$@"; do
       # one --set full capture of every kernel of the second pass of scripts/profile_all.py
       CMD="python scripts/profile_all.py"
       timeout 600 $CMD > gpurun_out/${tag}_profile_all.log 2>&1 &&
-      timeout 1500 ncu --set full --clock-control none -k regex:'adam_kernel|bbox|build_boxes|composite|emit_kernel|gather_points|knn3|mark_visible|morton|normal_guidance|preprocess|radix|tile_' -s ${NCU_SKIP:-50} -c ${NCU_COUNT:-50} -f -o gpurun_out/${tag}_prof_all $CMD > gpurun_out/${tag}_ncu_all.log 2>&1
+      timeout 1500 ncu --set full --clock-control none -k regex:'adam_kernel|bbox|build_boxes|composite|emit_kernel|gather_points|knn3|mark_visible|morton|normal_guidance|preprocess|radix|sh_grad_from_views|tile_' -s ${NCU_SKIP:-51} -c ${NCU_COUNT:-51} -f -o gpurun_out/${tag}_prof_all $CMD > gpurun_out/${tag}_ncu_all.log 2>&1
       echo "ncu all rc=$?" | tee -a $S
       python scripts/ncu_table.py gpurun_out/${tag}_prof_all.ncu-rep gpurun_out/${tag}_ncu_all.md "ncu --set full --clock-control none, every kernel of one pass over the 6 M scene ($tag): \`$CMD\`" > /dev/null 2>&1
       ls -la gpurun_out/${tag}_prof_all.ncu-rep >> $S

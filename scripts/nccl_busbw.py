@@ -44,11 +44,31 @@ def per_tensor():
     dist.all_reduce(maxr, op=dist.ReduceOp.MAX)
 
 
+# the exchange with the SH gradient sent as its factor: all-gather of every view's dL/dRGB (8 views
+# over the ranks), all-reduce of the other 13 + 2 words per Gaussian, MAX of the radii
+V = 8
+drgb_local = torch.ones(V // world if V >= world else 1, P, 3, device=dev)
+drgb_all = torch.empty(drgb_local.shape[0] * world, P, 3, device=dev)
+rest = torch.ones(15 * P, device=dev)
+
+
+def gather_only():
+    dist.all_gather_into_tensor(drgb_all, drgb_local)
+
+
+def rest_only():
+    dist.all_reduce(rest); dist.all_reduce(maxr, op=dist.ReduceOp.MAX)
+
+
 res = {}
 for name, fn in (("flat_buffer", one_flat), ("per_tensor", per_tensor)):
     ms = timed(fn)
     nbytes = 4 * 62 * P
     res[name] = dict(ms=ms, algbw_GBs=nbytes / ms / 1e6, busbw_GBs=nbytes / ms / 1e6 * 2 * (world - 1) / world)
+ms_g, ms_r = timed(gather_only), timed(rest_only)
+res["factor_exchange"] = dict(all_gather_ms=ms_g, all_gather_bytes_out=4 * drgb_all.numel(),
+                              all_gather_busbw_GBs=4 * drgb_all.numel() * (world - 1) / world / ms_g / 1e6,
+                              all_reduce_15_words_ms=ms_r)
 if rank == 0:
     print(json.dumps(dict(world=world, bytes=4 * 62 * P, **res)))
 dist.barrier()

@@ -28,6 +28,12 @@ opt = FusedAdam([{"params": [sc[k]], "lr": 1e-3, "name": k} for k in ("means3D",
                 lr=0.0, eps=1e-15)
 ng_cam = SimpleNamespace(original_normal=torch.nn.functional.normalize(torch.randn(3, cam.H, cam.W, device=dev), dim=0),
                          R=np.array([[0.0, 0.0, 1.0], [-1.0, 0.0, 0.0], [0.0, -1.0, 0.0]]))
+import ctypes as C  # noqa: E402
+from vegs_b200 import _lib  # noqa: E402
+lib = _lib.load()
+campos8 = torch.stack([synth.make_camera(k, device=dev).campos for k in range(8)]).contiguous()
+drgb8 = torch.randn(8, P, 3, device=dev) * (torch.rand(8, P, 1, device=dev) < 0.9)
+dsh = torch.empty(P, 16, 3, device=dev)
 for it in range(2):          # the second pass is the one to look at (first touches cold memory)
     vis = rast.markVisible(sc["means3D"].detach())
     m2 = torch.zeros_like(sc["means3D"], requires_grad=True)
@@ -35,6 +41,10 @@ for it in range(2):          # the second pass is the one to look at (first touc
                rotations=sc["rotations"])
     (out[0].sum() + out[1].mean() + out[4].mean() + loss_normal_guidance(ng_cam, out[2], out[3])).backward()
     opt.step(zero_grad=True)
+    # the deferred SH gradient of an 8-view step, rebuilt from the views' colour gradients (sh_views.cu)
+    rc = lib.vegs_sh_grad_from_views(P, 3, 16, 8, sc["means3D"].data_ptr(), campos8.data_ptr(), drgb8.data_ptr(),
+                                     dsh.data_ptr(), None, 0, C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    _lib.check(rc, "vegs_sh_grad_from_views")
     d = distCUDA2(sc["means3D"].detach())
     torch.cuda.synchronize()
 print("visible", int(vis.sum()), "radii>0", int((out[5] > 0).sum()), "dist2 mean", float(d.mean()))

@@ -4,7 +4,9 @@ each tensor's max norm, integer statistics exactly.  Both routes are covered: th
 step (autograd accumulation + vegs_b200.dist.allreduce_step), the fused one (FlatGradBuffer:
 .grad tensors and step statistics as views of the all-reduce buffer, written by the backward
 kernel) and the fused one with the deferred SH gradient (an all-gather of each view's dL/dRGB
-instead of the all-reduce of the SH gradient).  Skipped on a box with fewer than 2 GPUs (run it with `gpurun --gpus 2`)."""
+instead of the all-reduce of the SH gradient), and the drop-in step of ONE view per rank whose SH
+gradient is exchanged as its rank-one factor (allreduce_step(single_view_campos=...)).
+Skipped on a box with fewer than 2 GPUs (run it with `gpurun --gpus 2`)."""
 import os
 import socket
 
@@ -44,16 +46,27 @@ def _targets(cams):
 
 
 def _run_step(rank, world, fused, dev):
-    """One 8-view step for `rank` of `world`; returns gradients and statistics (CPU tensors)."""
+    """One step (8 views; 2 for the single-view-per-rank route) for `rank` of `world`; returns
+    gradients and statistics (CPU tensors)."""
     import torch.distributed as dist
     import vegs_b200.diff_gaussian_rasterization as dgr
     from vegs_b200 import dist as vdist
     sc = util.scene_with_specials(P)
     params = {k: v.to(dev).requires_grad_(True) for k, v in sc.items()}
-    cams = [synth.make_camera(k, scale=SCALE, device=dev) for k in range(N_VIEWS)]
+    n_views = 2 if fused == "single" else N_VIEWS
+    cams = [synth.make_camera(k, scale=SCALE, device=dev) for k in range(n_views)]
     tg = [t.to(dev) for t in _targets(cams)]
-    mine = vdist.shard_views(N_VIEWS, rank, world)
-    if fused:
+    mine = vdist.shard_views(n_views, rank, world)
+    if fused == "single":
+        # plain module, autograd accumulation; with 2 ranks each has one view and the SH gradient
+        # travels as dL/dRGB (on one GPU the same call is the plain 2-view accumulation)
+        stats = vdist.DensificationStats(params["means3D"].shape[0], dev)
+        for v in mine:
+            vg, radii = _view_step(dgr, params, cams[v], tg[v], {}, dev)
+            stats.add_view(vg, radii)
+        assert world == 1 or len(mine) == 1
+        vdist.allreduce_step(params, stats, single_view_campos=torch.stack([c.campos for c in cams]) if world > 1 else None)
+    elif fused:
         defer = fused == "defer"
         buf = vdist.FlatGradBuffer(params, defer_sh=("shs",) if defer else (), views_per_step=N_VIEWS)
         buf.begin_step([c.campos for c in cams] if defer else None)
@@ -87,14 +100,14 @@ def _worker(rank, world, port, fused, out):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("fused", [False, True, "defer"])
+@pytest.mark.parametrize("fused", [False, True, "defer", "single"])
 def test_two_gpu_step_equals_one_gpu_accumulation(fused, tmp_path):
     import torch.multiprocessing as mp
     out = str(tmp_path / "r0.pt")
     mp.spawn(_worker, args=(2, _free_port(), fused, out), nprocs=2, join=True)
     two = torch.load(out, weights_only=False)
     one = _run_step(0, 1, fused, torch.device("cuda", 0))
-    rec = util.parity_record(f"multi_gpu_2x_{'fused_' + str(fused) if fused else 'dropin'}_{P}_{N_VIEWS}views")
+    rec = util.parity_record(f"multi_gpu_2x_{'fused_' + str(fused) if fused else 'dropin'}_{P}_{2 if fused == 'single' else N_VIEWS}views")
     for k in one["grads"]:
         assert float(one["grads"][k].abs().max()) > 0, k
         rec[k] = float(util.grad_close(two["grads"][k].numpy(), one["grads"][k].numpy(), f"2-GPU all-reduced grad {k}", rtol=1e-4))

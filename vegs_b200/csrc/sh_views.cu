@@ -60,19 +60,32 @@ __global__ void __launch_bounds__(kPwThreads) sh_grad_from_views_kernel(const Sh
     for (int k = 0; k < 48; k++) acc[k] = 0.f;
     if (in_range) {
         const float mx = p.means[3 * (size_t)idx], my = p.means[3 * (size_t)idx + 1], mz = p.means[3 * (size_t)idx + 2];
-        for (int v = 0; v < p.V; v++) {
-            const float* g3 = p.drgb + ((size_t)v * p.P + idx) * 3;
-            const float g[3] = {g3[0], g3[1], g3[2]};
-            if (g[0] == 0.f && g[1] == 0.f && g[2] == 0.f) continue;     // not rendered by this view
-            const float dox = mx - p.campos[3 * v], doy = my - p.campos[3 * v + 1], doz = mz - p.campos[3 * v + 2];
-            const float len = sqrtf(dox * dox + doy * doy + doz * doz);   // as sh_bwd_begin
-            const float x = dox / len, y = doy / len, z = doz / len;
-            add_coeff<0>(acc, used, x, y, z, g); add_coeff<1>(acc, used, x, y, z, g); add_coeff<2>(acc, used, x, y, z, g);
-            add_coeff<3>(acc, used, x, y, z, g); add_coeff<4>(acc, used, x, y, z, g); add_coeff<5>(acc, used, x, y, z, g);
-            add_coeff<6>(acc, used, x, y, z, g); add_coeff<7>(acc, used, x, y, z, g); add_coeff<8>(acc, used, x, y, z, g);
-            add_coeff<9>(acc, used, x, y, z, g); add_coeff<10>(acc, used, x, y, z, g); add_coeff<11>(acc, used, x, y, z, g);
-            add_coeff<12>(acc, used, x, y, z, g); add_coeff<13>(acc, used, x, y, z, g); add_coeff<14>(acc, used, x, y, z, g);
-            add_coeff<15>(acc, used, x, y, z, g);
+        // four views at a time: their twelve gradient words are requested before any of them is
+        // used, so that the loop waits for memory once per four views instead of once per view
+        for (int v0 = 0; v0 < p.V; v0 += 4) {
+            float g[4][3];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const bool on = v0 + u < p.V;
+                const float* g3 = p.drgb + ((size_t)(on ? v0 + u : v0) * p.P + idx) * 3;
+                g[u][0] = on ? __ldg(g3) : 0.f;
+                g[u][1] = on ? __ldg(g3 + 1) : 0.f;
+                g[u][2] = on ? __ldg(g3 + 2) : 0.f;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (g[u][0] == 0.f && g[u][1] == 0.f && g[u][2] == 0.f) continue;     // not rendered by this view
+                const int v = v0 + u;
+                const float dox = mx - p.campos[3 * v], doy = my - p.campos[3 * v + 1], doz = mz - p.campos[3 * v + 2];
+                const float len = sqrtf(dox * dox + doy * doy + doz * doz);   // as sh_bwd_begin
+                const float x = dox / len, y = doy / len, z = doz / len;
+                add_coeff<0>(acc, used, x, y, z, g[u]); add_coeff<1>(acc, used, x, y, z, g[u]); add_coeff<2>(acc, used, x, y, z, g[u]);
+                add_coeff<3>(acc, used, x, y, z, g[u]); add_coeff<4>(acc, used, x, y, z, g[u]); add_coeff<5>(acc, used, x, y, z, g[u]);
+                add_coeff<6>(acc, used, x, y, z, g[u]); add_coeff<7>(acc, used, x, y, z, g[u]); add_coeff<8>(acc, used, x, y, z, g[u]);
+                add_coeff<9>(acc, used, x, y, z, g[u]); add_coeff<10>(acc, used, x, y, z, g[u]); add_coeff<11>(acc, used, x, y, z, g[u]);
+                add_coeff<12>(acc, used, x, y, z, g[u]); add_coeff<13>(acc, used, x, y, z, g[u]); add_coeff<14>(acc, used, x, y, z, g[u]);
+                add_coeff<15>(acc, used, x, y, z, g[u]);
+            }
         }
     }
     const int rowlen = 3 * M;
@@ -92,8 +105,13 @@ __global__ void __launch_bounds__(kPwThreads) sh_grad_from_views_kernel(const Sh
         const int rs = 3 * (M - 1);
         float* rest = s_rows[warp] + lane * rs;
         float* dc = s_rows[warp] + 32 * rs + 3 * lane;
+        // every index into acc[] is a compile-time constant (guards instead of run-time bounds), so
+        // the 48 sums stay in registers
+#pragma unroll
         for (int k = 0; k < 3; k++) dc[k] = acc[k];
-        for (int k = 0; k < rs; k++) rest[k] = acc[3 + k];
+#pragma unroll
+        for (int k = 0; k < 45; k++)
+            if (k < rs) rest[k] = acc[3 + k];
         fence_smem_to_async_proxy();
         __syncwarp();
         if (lane == 0) {
@@ -110,10 +128,14 @@ __global__ void __launch_bounds__(kPwThreads) sh_grad_from_views_kernel(const Sh
     } else if (in_range) {
         float* d0 = p.dsh + (size_t)idx * (p.dsh_rest ? 3 : rowlen);
         const int n0 = p.dsh_rest ? 3 : rowlen;
-        for (int k = 0; k < n0; k++) d0[k] = p.accumulate ? d0[k] + acc[k] : acc[k];
+#pragma unroll
+        for (int k = 0; k < 48; k++)
+            if (k < n0) d0[k] = p.accumulate ? d0[k] + acc[k] : acc[k];
         if (p.dsh_rest) {
             float* d1 = p.dsh_rest + (size_t)idx * 3 * (M - 1);
-            for (int k = 0; k < 3 * (M - 1); k++) d1[k] = p.accumulate ? d1[k] + acc[3 + k] : acc[3 + k];
+#pragma unroll
+            for (int k = 0; k < 45; k++)
+                if (k < 3 * (M - 1)) d1[k] = p.accumulate ? d1[k] + acc[3 + k] : acc[3 + k];
         }
     }
     bulk_commit();

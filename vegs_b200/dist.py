@@ -145,9 +145,43 @@ def unpack(flat: torch.Tensor, params: Dict[str, torch.Tensor], stats: Densifica
                 t.copy_(src)
 
 
+SH_C0 = 0.28209479177387814      # the constant SH basis function (reference cuda_rasterizer/auxiliary.h:23)
+
+
+def _exchange_single_view_sh(params, sh_names, campos, sh_degree, group):
+    """The SH gradient of a step in which EVERY rank rendered exactly one view, without sending it.
+    One view's dL/dSH is an outer product: dL/dsh[k][c] = basis_k(direction) * dL/dRGB[c] (the colour
+    is linear in the coefficients; clamped channels are already zero), and basis_0 is the constant
+    SH_C0, so the DC coefficient's gradient IS dL/dRGB up to that factor.  The ranks therefore
+    all-gather 3 words per Gaussian instead of all-reducing 48, and each rebuilds the sum over the
+    views from the views' camera centres (vegs_sh_grad_from_views, csrc/sh_views.cu) in place of
+    its own `.grad`.  `campos`: [world, 3], row r = camera centre of rank r's view."""
+    import ctypes as C
+    from . import _lib
+    lib = _lib.load()
+    world = dist.get_world_size(group)
+    dc = params[sh_names[0]].grad
+    rest = params[sh_names[1]].grad if len(sh_names) > 1 else None
+    means = params["means3D"].detach()
+    P, dev = int(means.shape[0]), means.device
+    M = int(dc.shape[1]) + (int(rest.shape[1]) if rest is not None else 0)
+    campos = campos.to(device=dev, dtype=torch.float32).contiguous()
+    if tuple(campos.shape) != (world, 3):
+        raise ValueError(f"single_view_campos must be [world_size, 3] = [{world}, 3], got {tuple(campos.shape)}")
+    drgb_all = torch.empty(world, P, 3, device=dev, dtype=torch.float32)
+    dist.all_gather_into_tensor(drgb_all, (dc[:, 0, :] * (1.0 / SH_C0)).contiguous(), group=group)
+    with torch.cuda.device(dev):
+        rc = lib.vegs_sh_grad_from_views(P, int(sh_degree), M, world, means.data_ptr(), campos.data_ptr(),
+                                         drgb_all.data_ptr(), dc.data_ptr(),
+                                         rest.data_ptr() if (rest is not None and rest.numel()) else None, 0,
+                                         C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+        _lib.check(rc, "vegs_sh_grad_from_views")
+
+
 def allreduce_step(params: Dict[str, torch.Tensor], stats: DensificationStats, group=None,
                    flat: torch.Tensor = None, accumulate_into: DensificationStats = None,
-                   per_tensor: bool = None) -> torch.Tensor:
+                   per_tensor: bool = None, single_view_campos: torch.Tensor = None,
+                   sh_degree: int = 3) -> torch.Tensor:
     """The reduction of a step whose gradients live in autograd's own `.grad` tensors (the plain
     drop-in module, either arm of bench.py): SUM over ranks of the five gradients and the two
     additive statistics, MAX of max_radii2D.
@@ -159,12 +193,20 @@ def allreduce_step(params: Dict[str, torch.Tensor], stats: DensificationStats, g
     no pack copy of the 1.15 GB SH gradient (0.35 ms at the 6 M scene), three collectives in all.
     Default: per tensor on NCCL, packed elsewhere (gloo pays per call).
 
+    `single_view_campos` ([world, 3], row r = camera centre of rank r's view; per-tensor route on
+    CUDA): promise that every rank rendered exactly ONE view this step.  The SH gradient is then
+    exchanged as its rank-one factor (_exchange_single_view_sh): 37 instead of 61 words per Gaussian
+    between the GPUs; `sh_degree` is the active degree the views were rendered with.  The result
+    equals the plain all-reduce to rounding (tests/test_gpu_multi.py).
+
     `stats` must hold THIS STEP's contribution only (fresh or zeroed at the start of the step): the
     SUM over ranks of a running accumulator would count the earlier steps world-size times.  Pass
     the running accumulator as `accumulate_into` to have the reduced step added to it."""
     active = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
     if per_tensor is None:
         per_tensor = active and dist.get_backend(group) == "nccl" and flat is None
+    if single_view_campos is not None and active and not per_tensor:
+        raise ValueError("single_view_campos is a per-tensor-route option (per_tensor=True, no `flat` buffer)")
     if per_tensor:
         if active:
             # the large tensors (the SH gradient is 48 of the 61 words per Gaussian) are reduced where
@@ -175,8 +217,15 @@ def allreduce_step(params: Dict[str, torch.Tensor], stats: DensificationStats, g
             for k in names:
                 if params[k].grad is None:
                     params[k].grad = torch.zeros_like(params[k])
-            big = [k for k in names if params[k].numel() >= 8 * params["means3D"].numel()]
-            small = [params[k].grad for k in names if k not in big] + [stats.xyz_gradient_accum, stats.denom]
+            sh_names = []
+            if single_view_campos is not None:
+                sh_names = ["shs"] if "shs" in params else [k for k in ("shs_dc", "shs_rest") if k in params]
+                if not sh_names or not params["means3D"].is_cuda:
+                    raise ValueError("single_view_campos needs an SH parameter ('shs' or 'shs_dc' + 'shs_rest') on a CUDA device")
+                _exchange_single_view_sh(params, sh_names, single_view_campos, sh_degree, group)
+            big = [k for k in names if params[k].numel() >= 8 * params["means3D"].numel() and k not in sh_names]
+            small = [params[k].grad for k in names if k not in big and k not in sh_names]
+            small += [stats.xyz_gradient_accum, stats.denom]
             for k in big:
                 dist.all_reduce(params[k].grad, op=dist.ReduceOp.SUM, group=group)
             stage = torch.cat([t.reshape(-1) for t in small])
