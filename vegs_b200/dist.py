@@ -155,7 +155,9 @@ def _exchange_single_view_sh(params, sh_names, campos, sh_degree, group):
     SH_C0, so the DC coefficient's gradient IS dL/dRGB up to that factor.  The ranks therefore
     all-gather 3 words per Gaussian instead of all-reducing 48, and each rebuilds the sum over the
     views from the views' camera centres (vegs_sh_grad_from_views, csrc/sh_views.cu) in place of
-    its own `.grad`.  `campos`: [world, 3], row r = camera centre of rank r's view."""
+    its own `.grad`.  `campos`: [world, 3], row r = camera centre of rank r's view.
+    Returns the rebuild as a callable: the caller starts its other collectives first, so that the
+    rebuild kernel (HBM-bound) runs underneath them (NVLink-bound)."""
     import ctypes as C
     from . import _lib
     lib = _lib.load()
@@ -170,12 +172,15 @@ def _exchange_single_view_sh(params, sh_names, campos, sh_degree, group):
         raise ValueError(f"single_view_campos must be [world_size, 3] = [{world}, 3], got {tuple(campos.shape)}")
     drgb_all = torch.empty(world, P, 3, device=dev, dtype=torch.float32)
     dist.all_gather_into_tensor(drgb_all, (dc[:, 0, :] * (1.0 / SH_C0)).contiguous(), group=group)
-    with torch.cuda.device(dev):
-        rc = lib.vegs_sh_grad_from_views(P, int(sh_degree), M, world, means.data_ptr(), campos.data_ptr(),
-                                         drgb_all.data_ptr(), dc.data_ptr(),
-                                         rest.data_ptr() if (rest is not None and rest.numel()) else None, 0,
-                                         C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
-        _lib.check(rc, "vegs_sh_grad_from_views")
+
+    def rebuild():
+        with torch.cuda.device(dev):
+            rc = lib.vegs_sh_grad_from_views(P, int(sh_degree), M, world, means.data_ptr(), campos.data_ptr(),
+                                             drgb_all.data_ptr(), dc.data_ptr(),
+                                             rest.data_ptr() if (rest is not None and rest.numel()) else None, 0,
+                                             C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+            _lib.check(rc, "vegs_sh_grad_from_views")
+    return rebuild
 
 
 def allreduce_step(params: Dict[str, torch.Tensor], stats: DensificationStats, group=None,
@@ -222,18 +227,21 @@ def allreduce_step(params: Dict[str, torch.Tensor], stats: DensificationStats, g
                 sh_names = ["shs"] if "shs" in params else [k for k in ("shs_dc", "shs_rest") if k in params]
                 if not sh_names or not params["means3D"].is_cuda:
                     raise ValueError("single_view_campos needs an SH parameter ('shs' or 'shs_dc' + 'shs_rest') on a CUDA device")
-                _exchange_single_view_sh(params, sh_names, single_view_campos, sh_degree, group)
+                rebuild_sh = _exchange_single_view_sh(params, sh_names, single_view_campos, sh_degree, group)
             big = [k for k in names if params[k].numel() >= 8 * params["means3D"].numel() and k not in sh_names]
             small = [params[k].grad for k in names if k not in big and k not in sh_names]
             small += [stats.xyz_gradient_accum, stats.denom]
-            for k in big:
-                dist.all_reduce(params[k].grad, op=dist.ReduceOp.SUM, group=group)
+            works = [dist.all_reduce(params[k].grad, op=dist.ReduceOp.SUM, group=group, async_op=True) for k in big]
             stage = torch.cat([t.reshape(-1) for t in small])
-            dist.all_reduce(stage, op=dist.ReduceOp.SUM, group=group)
+            works.append(dist.all_reduce(stage, op=dist.ReduceOp.SUM, group=group, async_op=True))
+            works.append(dist.all_reduce(stats.max_radii2D, op=dist.ReduceOp.MAX, group=group, async_op=True))
+            if sh_names:
+                rebuild_sh()         # on the current stream, underneath the collectives above
+            for w in works:
+                w.wait()
             off = 0
             for t in small:
                 t.copy_(stage[off:off + t.numel()].view_as(t)); off += t.numel()
-            dist.all_reduce(stats.max_radii2D, op=dist.ReduceOp.MAX, group=group)
     else:
         flat = pack(params, stats, flat)
         if active:
@@ -354,9 +362,13 @@ class FlatGradBuffer:
         if self._defer_active:
             if active:
                 dist.all_gather_into_tensor(self.drgb_all.view(-1), self.drgb_local.reshape(-1).clone(), group=group)
-                dist.all_reduce(self.flat[:self._sh_off], op=dist.ReduceOp.SUM, group=group)
-                dist.all_reduce(self.step_stats.max_radii2D, op=dist.ReduceOp.MAX, group=group)
-            self._rebuild_sh_grad()
+                works = [dist.all_reduce(self.flat[:self._sh_off], op=dist.ReduceOp.SUM, group=group, async_op=True),
+                         dist.all_reduce(self.step_stats.max_radii2D, op=dist.ReduceOp.MAX, group=group, async_op=True)]
+                self._rebuild_sh_grad()          # HBM-bound, underneath the NVLink-bound all-reduce
+                for w in works:
+                    w.wait()
+            else:
+                self._rebuild_sh_grad()
         elif active:
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
             dist.all_reduce(self.step_stats.max_radii2D, op=dist.ReduceOp.MAX, group=group)
