@@ -156,8 +156,7 @@ def _exchange_single_view_sh(params, sh_names, campos, sh_degree, group):
     all-gather 3 words per Gaussian instead of all-reducing 48, and each rebuilds the sum over the
     views from the views' camera centres (vegs_sh_grad_from_views, csrc/sh_views.cu) in place of
     its own `.grad`.  `campos`: [world, 3], row r = camera centre of rank r's view.
-    Returns the rebuild as a callable: the caller starts its other collectives first, so that the
-    rebuild kernel (HBM-bound) runs underneath them (NVLink-bound)."""
+    Returns the rebuild as a callable (the caller runs it after its other collectives)."""
     import ctypes as C
     from . import _lib
     lib = _lib.load()
@@ -231,17 +230,18 @@ def allreduce_step(params: Dict[str, torch.Tensor], stats: DensificationStats, g
             big = [k for k in names if params[k].numel() >= 8 * params["means3D"].numel() and k not in sh_names]
             small = [params[k].grad for k in names if k not in big and k not in sh_names]
             small += [stats.xyz_gradient_accum, stats.denom]
-            works = [dist.all_reduce(params[k].grad, op=dist.ReduceOp.SUM, group=group, async_op=True) for k in big]
+            for k in big:
+                dist.all_reduce(params[k].grad, op=dist.ReduceOp.SUM, group=group)
             stage = torch.cat([t.reshape(-1) for t in small])
-            works.append(dist.all_reduce(stage, op=dist.ReduceOp.SUM, group=group, async_op=True))
-            works.append(dist.all_reduce(stats.max_radii2D, op=dist.ReduceOp.MAX, group=group, async_op=True))
-            if sh_names:
-                rebuild_sh()         # on the current stream, underneath the collectives above
-            for w in works:
-                w.wait()
+            dist.all_reduce(stage, op=dist.ReduceOp.SUM, group=group)
             off = 0
             for t in small:
                 t.copy_(stage[off:off + t.numel()].view_as(t)); off += t.numel()
+            dist.all_reduce(stats.max_radii2D, op=dist.ReduceOp.MAX, group=group)
+            if sh_names:
+                # (running this kernel underneath the collectives above - async collectives, kernel on
+                # the current stream - was measured at 8 GPUs: 1010 against 1021 views/s, no gain)
+                rebuild_sh()
     else:
         flat = pack(params, stats, flat)
         if active:
@@ -362,13 +362,9 @@ class FlatGradBuffer:
         if self._defer_active:
             if active:
                 dist.all_gather_into_tensor(self.drgb_all.view(-1), self.drgb_local.reshape(-1).clone(), group=group)
-                works = [dist.all_reduce(self.flat[:self._sh_off], op=dist.ReduceOp.SUM, group=group, async_op=True),
-                         dist.all_reduce(self.step_stats.max_radii2D, op=dist.ReduceOp.MAX, group=group, async_op=True)]
-                self._rebuild_sh_grad()          # HBM-bound, underneath the NVLink-bound all-reduce
-                for w in works:
-                    w.wait()
-            else:
-                self._rebuild_sh_grad()
+                dist.all_reduce(self.flat[:self._sh_off], op=dist.ReduceOp.SUM, group=group)
+                dist.all_reduce(self.step_stats.max_radii2D, op=dist.ReduceOp.MAX, group=group)
+            self._rebuild_sh_grad()
         elif active:
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
             dist.all_reduce(self.step_stats.max_radii2D, op=dist.ReduceOp.MAX, group=group)
