@@ -63,6 +63,13 @@ def _worker(rank, world, port, P, n_views, out):
     for k in params:
         assert torch.allclose(params[k].grad, params2[k].grad, rtol=1e-6, atol=1e-6), k
     assert torch.equal(stats.denom, stats2.denom) and torch.equal(stats.max_radii2D, stats2.max_radii2D)
+    # the single-view SH factor exchange is a CUDA, per-tensor-route option: refused (on every rank,
+    # before any collective) on the packed route and for host tensors
+    import pytest
+    with pytest.raises(ValueError, match="per-tensor"):
+        vdist.allreduce_step(params2, stats2, single_view_campos=torch.zeros(world, 3))
+    with pytest.raises(ValueError, match="CUDA"):
+        vdist.allreduce_step(params2, stats2, per_tensor=True, single_view_campos=torch.zeros(world, 3))
     if rank == 0:
         torch.save(dict(grads={k: v.grad.clone() for k, v in params.items()},
                         accum=stats.xyz_gradient_accum.clone(), denom=stats.denom.clone(),
