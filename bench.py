@@ -125,7 +125,8 @@ class Workload:
         self.my_views = vdist.shard_views(args.views, rank, world)
         self.flat = None
         self.buf = None
-        self.factor_sh = False           # set by main(): vegs_b200 arm, exactly one view per rank
+        self.factor_sh = False           # set by main(): vegs_b200 arm at N > 1 - the SH gradient crosses as dL/dRGB
+        self.capture = None              # ... kept per view by a hook on the SH leaf when a rank has several views
         self.campos_all = torch.stack([c.campos for c in self.cams]).contiguous()
         self.h2d_bytes = sum(self.host_targets[v].numel() * 4 for v in range(args.views))
 
@@ -168,6 +169,8 @@ class Workload:
             for t in p.values():
                 t.grad = None
             stats = self.vdist.DensificationStats(self.P, self.device)
+            if self.capture is not None and views is None and reduce:
+                self.capture.begin_step()
         total = torch.zeros((), device=self.device)
         # e2e leg: each view's target planes come from pinned host memory inside the step; the copy of
         # view i+1 runs on a side stream while view i is rendered (what a data loader would do)
@@ -198,8 +201,11 @@ class Workload:
             else:
                 # one view per rank (vegs_b200 arm only): the SH gradient crosses NVLink as its rank-one
                 # factor dL/dRGB and is rebuilt by the library's kernel (vegs_b200/dist.py)
-                single = self.campos_all if (self.factor_sh and views is None) else None
-                self.flat = self.vdist.allreduce_step(p, stats, flat=self.flat, single_view_campos=single)
+                use = self.factor_sh and views is None
+                single = self.campos_all if (use and self.capture is None) else None
+                self.flat = self.vdist.allreduce_step(p, stats, flat=self.flat, single_view_campos=single,
+                                                      sh_factor=self.capture if use else None,
+                                                      view_campos=self.campos_all if (use and self.capture is not None) else None)
         if not resident:
             return float(total.item())   # device -> host read of the step's result
         return total
@@ -373,7 +379,9 @@ def main():
         # only the vegs_b200 arm may map libvegs_b200.so: the reference process must stay free of it
         from vegs_b200 import _lib
     wl = Workload(args, device, rank, world)
-    wl.factor_sh = ours and world > 1 and world == args.views
+    wl.factor_sh = ours and world > 1
+    if wl.factor_sh and world != args.views:          # some rank renders several views (or none)
+        wl.capture = wl.vdist.ShFactorCapture(wl.params["shs"], slots=(args.views + world - 1) // world)
 
     launches0 = _lib.launch_count() if ours else 0
     sampler = ClockSampler(local_rank) if rank == 0 else None
@@ -400,8 +408,10 @@ def main():
                 rasterizer=kind,
                 reduction=("none (one GPU)" if world == 1 else
                            "vegs_b200.dist.allreduce_step: NCCL all-reduce of the .grad tensors and statistics" +
-                           ("; one view per rank, so the SH gradient is exchanged as dL/dRGB (all-gather of 3 words "
-                            "per Gaussian and rank) and rebuilt by vegs_sh_grad_from_views" if wl.factor_sh else "")),
+                           ("; the SH gradient is exchanged as every view's dL/dRGB (all-gather of 3 words per Gaussian "
+                            "and view, " + ("kept by a hook on the SH leaf" if wl.capture is not None else
+                                            "one view per rank: read off the DC row of .grad") +
+                            ") and rebuilt by vegs_sh_grad_from_views" if wl.factor_sh else "")),
                 e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=4 * world),
                 gpu_launches=int(launches), clocks=clocks)
 

@@ -228,3 +228,51 @@ def test_two_steps_with_persistent_buffers(tmp_path):
     assert torch.allclose(got["accum"], running.xyz_gradient_accum, rtol=1e-6, atol=1e-6)
     assert torch.equal(got["denom"], running.denom)
     assert torch.equal(got["maxr"], running.max_radii2D)
+
+
+def test_sh_factor_capture_keeps_each_pass_and_leaves_autograd_alone():
+    """The hook behind allreduce_step(sh_factor=...): every backward pass leaves grad[:, 0, :] / SH_C0 in
+    the next slot, `.grad` accumulates as if the hook were not there, a pass too many is refused,
+    and nothing is captured outside begin_step() .. end_step()."""
+    import pytest
+    g = torch.Generator().manual_seed(5)
+    shs = torch.randn(50, 4, 3, generator=g).requires_grad_(True)
+    w = [torch.randn(50, 4, 3, generator=g) for _ in range(3)]
+    cap = vdist.ShFactorCapture(shs, slots=2)
+    (shs * w[0]).sum().backward()                       # before begin_step: not captured
+    assert cap.n == 0 and float(cap.buf.abs().max()) == 0.0
+    shs.grad = None
+    cap.begin_step()
+    (shs * w[0]).sum().backward()
+    (shs * w[1]).sum().backward()
+    assert cap.n == 2
+    assert torch.allclose(cap.buf[0], w[0][:, 0, :] / vdist.SH_C0) and torch.allclose(cap.buf[1], w[1][:, 0, :] / vdist.SH_C0)
+    assert torch.allclose(shs.grad, w[0] + w[1])
+    with pytest.raises(RuntimeError, match="more than 2"):
+        (shs * w[2]).sum().backward()
+    cap.end_step()
+    (shs * w[2]).sum().backward()                       # after end_step: not captured, no complaint
+    assert cap.n == 2
+    cap.begin_step()
+    assert cap.n == 0 and float(cap.buf.abs().max()) == 0.0
+    cap.remove()
+    with pytest.raises(ValueError):
+        vdist.ShFactorCapture(torch.zeros(5, 3, requires_grad=True), slots=1)
+
+
+def test_slot_campos_follows_the_round_robin_sharding():
+    """View j of the batch is rank j % world's (j // world)-th view: its camera centre must sit in
+    row (j % world) * slots + j // world of the all-gathered order; rows of unused slots are zero."""
+    V, world, slots = 5, 2, 3
+    vc = torch.arange(V * 3, dtype=torch.float32).reshape(V, 3) + 1.0
+    out = vdist._slot_campos(vc, world, slots, "cpu")
+    assert out.shape == (world * slots, 3)
+    for r in range(world):
+        mine = vdist.shard_views(V, r, world)
+        for i in range(slots):
+            want = vc[mine[i]] if i < len(mine) else torch.zeros(3)
+            assert torch.equal(out[r * slots + i], want), (r, i)
+    assert torch.equal(vdist._slot_campos([vc[j] for j in range(V)], world, slots, "cpu"), out)
+    import pytest
+    with pytest.raises(ValueError):
+        vdist._slot_campos(vc, 2, 2, "cpu")

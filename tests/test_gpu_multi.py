@@ -5,7 +5,8 @@ step (autograd accumulation + vegs_b200.dist.allreduce_step), the fused one (Fla
 .grad tensors and step statistics as views of the all-reduce buffer, written by the backward
 kernel) and the fused one with the deferred SH gradient (an all-gather of each view's dL/dRGB
 instead of the all-reduce of the SH gradient), and the drop-in step of ONE view per rank whose SH
-gradient is exchanged as its rank-one factor (allreduce_step(single_view_campos=...)).
+gradient is exchanged as its rank-one factor (allreduce_step(single_view_campos=...)), and the same
+for several views per rank with the factors kept by a hook on the SH leaf (ShFactorCapture).
 Skipped on a box with fewer than 2 GPUs (run it with `gpurun --gpus 2`)."""
 import os
 import socket
@@ -66,6 +67,20 @@ def _run_step(rank, world, fused, dev):
             stats.add_view(vg, radii)
         assert world == 1 or len(mine) == 1
         vdist.allreduce_step(params, stats, single_view_campos=torch.stack([c.campos for c in cams]) if world > 1 else None)
+    elif fused == "hook":
+        # plain module, autograd accumulation over the rank's 4 views; a hook on the SH leaf keeps each
+        # view's dL/dRGB and the SH gradient travels as those (8 x 3 words per Gaussian instead of 48)
+        stats = vdist.DensificationStats(params["means3D"].shape[0], dev)
+        cap = vdist.ShFactorCapture(params["shs"], slots=len(mine)) if world > 1 else None
+        if cap is not None:
+            cap.begin_step()
+        for v in mine:
+            vg, radii = _view_step(dgr, params, cams[v], tg[v], {}, dev)
+            stats.add_view(vg, radii)
+        vdist.allreduce_step(params, stats, sh_factor=cap, view_campos=[c.campos for c in cams] if cap is not None else None)
+        if cap is not None:
+            assert cap.n == len(mine) and not cap.enabled
+            cap.remove()
     elif fused:
         defer = fused == "defer"
         buf = vdist.FlatGradBuffer(params, defer_sh=("shs",) if defer else (), views_per_step=N_VIEWS)
@@ -100,7 +115,7 @@ def _worker(rank, world, port, fused, out):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("fused", [False, True, "defer", "single"])
+@pytest.mark.parametrize("fused", [False, True, "defer", "single", "hook"])
 def test_two_gpu_step_equals_one_gpu_accumulation(fused, tmp_path):
     import torch.multiprocessing as mp
     out = str(tmp_path / "r0.pt")

@@ -148,14 +148,59 @@ def unpack(flat: torch.Tensor, params: Dict[str, torch.Tensor], stats: Densifica
 SH_C0 = 0.28209479177387814      # the constant SH basis function (reference cuda_rasterizer/auxiliary.h:23)
 
 
-def _exchange_single_view_sh(params, sh_names, campos, sh_degree, group):
-    """The SH gradient of a step in which EVERY rank rendered exactly one view, without sending it.
-    One view's dL/dSH is an outer product: dL/dsh[k][c] = basis_k(direction) * dL/dRGB[c] (the colour
-    is linear in the coefficients; clamped channels are already zero), and basis_0 is the constant
-    SH_C0, so the DC coefficient's gradient IS dL/dRGB up to that factor.  The ranks therefore
-    all-gather 3 words per Gaussian instead of all-reducing 48, and each rebuilds the sum over the
-    views from the views' camera centres (vegs_sh_grad_from_views, csrc/sh_views.cu) in place of
-    its own `.grad`.  `campos`: [world, 3], row r = camera centre of rank r's view.
+class ShFactorCapture:
+    """Keeps, for every backward pass of a step, the factor of that view's SH gradient.
+
+    One view's dL/dSH is an outer product: dL/dsh[k][c] = basis_k(view direction) * dL/dRGB[c] (the
+    colour is linear in the coefficients; clamped channels are already zero), and basis_0 is the
+    constant SH_C0, so the DC row of the gradient a backward pass hands to the SH leaf IS that
+    view's dL/dRGB up to that factor.  A tensor hook on the leaf (the `shs` parameter, or
+    `features_dc` when the coefficients are split) copies `grad[:, 0, :] / SH_C0` of each pass into
+    the next of `slots` rows; autograd's accumulation into `.grad` goes on untouched, so the caller
+    and the rasterizer (the plain drop-in module) see nothing.  `allreduce_step(..., sh_factor=...)`
+    then sends these rows instead of the SH gradient.
+
+        cap = ShFactorCapture(params["shs"], slots=views_per_rank)
+        per step:  cap.begin_step();  <views: forward, loss.backward()>;
+                   allreduce_step(params, stats, sh_factor=cap, view_campos=<[V, 3], batch order>)
+    """
+
+    def __init__(self, sh_dc_param: torch.Tensor, slots: int):
+        if sh_dc_param.dim() != 3 or sh_dc_param.shape[2] != 3:
+            raise ValueError("the SH parameter must be [P, M, 3]")
+        self.slots = int(slots)
+        self.buf = torch.zeros(max(self.slots, 1), sh_dc_param.shape[0], 3, device=sh_dc_param.device,
+                               dtype=torch.float32)
+        self.n = 0
+        self.enabled = False
+        self._handle = sh_dc_param.register_hook(self._hook)
+
+    def _hook(self, grad):
+        if self.enabled:
+            if self.n >= self.slots:
+                raise RuntimeError(f"ShFactorCapture: more than {self.slots} backward passes in one step")
+            torch.mul(grad[:, 0, :], 1.0 / SH_C0, out=self.buf[self.n])
+            self.n += 1
+        return None
+
+    def begin_step(self) -> None:
+        self.buf.zero_()              # a slot without a view reduces as "not rendered"
+        self.n = 0
+        self.enabled = True
+
+    def end_step(self) -> None:
+        self.enabled = False
+
+    def remove(self) -> None:
+        self._handle.remove()
+
+
+def _exchange_sh_factor(params, sh_names, drgb_local, campos_all, sh_degree, group):
+    """All-gather of every rank's dL/dRGB rows ([slots, P, 3] each) and the rebuild of the step's SH
+    gradient from them (vegs_sh_grad_from_views, csrc/sh_views.cu) in place of this rank's own
+    `.grad`: 3 words per view and Gaussian between the GPUs instead of 48 per Gaussian.
+    `campos_all`: [world * slots, 3], row r * slots + i = camera centre of rank r's i-th view (rows of
+    unused slots are never read: their dL/dRGB is zero).
     Returns the rebuild as a callable (the caller runs it after its other collectives)."""
     import ctypes as C
     from . import _lib
@@ -166,26 +211,43 @@ def _exchange_single_view_sh(params, sh_names, campos, sh_degree, group):
     means = params["means3D"].detach()
     P, dev = int(means.shape[0]), means.device
     M = int(dc.shape[1]) + (int(rest.shape[1]) if rest is not None else 0)
-    campos = campos.to(device=dev, dtype=torch.float32).contiguous()
-    if tuple(campos.shape) != (world, 3):
-        raise ValueError(f"single_view_campos must be [world_size, 3] = [{world}, 3], got {tuple(campos.shape)}")
-    drgb_all = torch.empty(world, P, 3, device=dev, dtype=torch.float32)
-    dist.all_gather_into_tensor(drgb_all, (dc[:, 0, :] * (1.0 / SH_C0)).contiguous(), group=group)
+    slots = int(drgb_local.shape[0])
+    campos_all = campos_all.to(device=dev, dtype=torch.float32).contiguous()
+    if tuple(campos_all.shape) != (world * slots, 3) or tuple(drgb_local.shape) != (slots, P, 3):
+        raise ValueError(f"SH factor exchange: camera centres must be [{world * slots}, 3] and the local factors "
+                         f"[{slots}, {P}, 3], got {tuple(campos_all.shape)} and {tuple(drgb_local.shape)}")
+    drgb_all = torch.empty(world * slots, P, 3, device=dev, dtype=torch.float32)
+    dist.all_gather_into_tensor(drgb_all.view(-1), drgb_local.contiguous().view(-1), group=group)
 
     def rebuild():
         with torch.cuda.device(dev):
-            rc = lib.vegs_sh_grad_from_views(P, int(sh_degree), M, world, means.data_ptr(), campos.data_ptr(),
-                                             drgb_all.data_ptr(), dc.data_ptr(),
+            rc = lib.vegs_sh_grad_from_views(P, int(sh_degree), M, world * slots, means.data_ptr(),
+                                             campos_all.data_ptr(), drgb_all.data_ptr(), dc.data_ptr(),
                                              rest.data_ptr() if (rest is not None and rest.numel()) else None, 0,
                                              C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
             _lib.check(rc, "vegs_sh_grad_from_views")
     return rebuild
 
 
+def _slot_campos(view_campos, world: int, slots: int, device) -> torch.Tensor:
+    """Camera centres of a step's views (batch order) in all-gather order: view j is rendered by
+    rank j % world as its (j // world)-th view (shard_views), i.e. row (j % world) * slots + j // world."""
+    vc = torch.as_tensor(view_campos) if not isinstance(view_campos, (list, tuple)) else torch.stack(
+        [torch.as_tensor(c).reshape(3) for c in view_campos])
+    vc = vc.to(device=device, dtype=torch.float32).reshape(-1, 3)
+    V = int(vc.shape[0])
+    if V > world * slots:
+        raise ValueError(f"{V} views in the step but only {world} ranks x {slots} slots")
+    j = torch.arange(V, device=device)
+    out = torch.zeros(world * slots, 3, device=device, dtype=torch.float32)
+    out[(j % world) * slots + j // world] = vc
+    return out
+
+
 def allreduce_step(params: Dict[str, torch.Tensor], stats: DensificationStats, group=None,
                    flat: torch.Tensor = None, accumulate_into: DensificationStats = None,
                    per_tensor: bool = None, single_view_campos: torch.Tensor = None,
-                   sh_degree: int = 3) -> torch.Tensor:
+                   sh_degree: int = 3, sh_factor: "ShFactorCapture" = None, view_campos=None) -> torch.Tensor:
     """The reduction of a step whose gradients live in autograd's own `.grad` tensors (the plain
     drop-in module, either arm of bench.py): SUM over ranks of the five gradients and the two
     additive statistics, MAX of max_radii2D.
@@ -197,11 +259,15 @@ def allreduce_step(params: Dict[str, torch.Tensor], stats: DensificationStats, g
     no pack copy of the 1.15 GB SH gradient (0.35 ms at the 6 M scene), three collectives in all.
     Default: per tensor on NCCL, packed elsewhere (gloo pays per call).
 
-    `single_view_campos` ([world, 3], row r = camera centre of rank r's view; per-tensor route on
-    CUDA): promise that every rank rendered exactly ONE view this step.  The SH gradient is then
-    exchanged as its rank-one factor (_exchange_single_view_sh): 37 instead of 61 words per Gaussian
-    between the GPUs; `sh_degree` is the active degree the views were rendered with.  The result
-    equals the plain all-reduce to rounding (tests/test_gpu_multi.py).
+    SH gradient as its factor (per-tensor route on CUDA; `sh_degree` = the active degree the views
+    were rendered with; the result equals the plain all-reduce to rounding, tests/test_gpu_multi.py):
+    * `sh_factor` (a ShFactorCapture that watched this step's backward passes) + `view_campos`
+      (the camera centres of ALL the step's views, [V, 3] or a list, in batch order): the ranks
+      all-gather each view's dL/dRGB and rebuild the SH gradient (_exchange_sh_factor): 13 + 2 + 3 V
+      words per Gaussian between the GPUs instead of 61 + 2 for a V-view step;
+    * `single_view_campos` ([world, 3], row r = camera centre of rank r's view): the same without a
+      hook, on the promise that every rank rendered exactly ONE view this step - its own `.grad`
+      then still is that one outer product and the factor is read off its DC row.
 
     `stats` must hold THIS STEP's contribution only (fresh or zeroed at the start of the step): the
     SUM over ranks of a running accumulator would count the earlier steps world-size times.  Pass
@@ -209,8 +275,9 @@ def allreduce_step(params: Dict[str, torch.Tensor], stats: DensificationStats, g
     active = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
     if per_tensor is None:
         per_tensor = active and dist.get_backend(group) == "nccl" and flat is None
-    if single_view_campos is not None and active and not per_tensor:
-        raise ValueError("single_view_campos is a per-tensor-route option (per_tensor=True, no `flat` buffer)")
+    if (single_view_campos is not None or sh_factor is not None) and active and not per_tensor:
+        raise ValueError("the SH factor exchange (single_view_campos / sh_factor) is a per-tensor-route option "
+                         "(per_tensor=True, no `flat` buffer)")
     if per_tensor:
         if active:
             # the large tensors (the SH gradient is 48 of the 61 words per Gaussian) are reduced where
@@ -222,11 +289,22 @@ def allreduce_step(params: Dict[str, torch.Tensor], stats: DensificationStats, g
                 if params[k].grad is None:
                     params[k].grad = torch.zeros_like(params[k])
             sh_names = []
-            if single_view_campos is not None:
+            if single_view_campos is not None or sh_factor is not None:
                 sh_names = ["shs"] if "shs" in params else [k for k in ("shs_dc", "shs_rest") if k in params]
                 if not sh_names or not params["means3D"].is_cuda:
-                    raise ValueError("single_view_campos needs an SH parameter ('shs' or 'shs_dc' + 'shs_rest') on a CUDA device")
-                rebuild_sh = _exchange_single_view_sh(params, sh_names, single_view_campos, sh_degree, group)
+                    raise ValueError("the SH factor exchange needs an SH parameter ('shs' or 'shs_dc' + 'shs_rest') on a CUDA device")
+                world = dist.get_world_size(group)
+                if sh_factor is not None:
+                    if view_campos is None:
+                        raise ValueError("sh_factor needs view_campos (the camera centres of the step's views, batch order)")
+                    sh_factor.end_step()
+                    rebuild_sh = _exchange_sh_factor(params, sh_names, sh_factor.buf,
+                                                     _slot_campos(view_campos, world, sh_factor.buf.shape[0],
+                                                                  params["means3D"].device), sh_degree, group)
+                else:
+                    dc = params[sh_names[0]].grad
+                    rebuild_sh = _exchange_sh_factor(params, sh_names, (dc[:, 0, :] * (1.0 / SH_C0)).unsqueeze(0),
+                                                     single_view_campos, sh_degree, group)
             big = [k for k in names if params[k].numel() >= 8 * params["means3D"].numel() and k not in sh_names]
             small = [params[k].grad for k in names if k not in big and k not in sh_names]
             small += [stats.xyz_gradient_accum, stats.denom]
