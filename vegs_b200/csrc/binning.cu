@@ -139,7 +139,10 @@ tile_spine_kernel(uint32_t* __restrict__ chunksum, uint32_t* __restrict__ partba
     }
 }
 
-constexpr int kEmitSmall = 4;      // a Gaussian with at most this many tiles is emitted by its own thread
+#ifndef VEGS_EMIT_SMALL
+#define VEGS_EMIT_SMALL 4
+#endif
+constexpr int kEmitSmall = VEGS_EMIT_SMALL;   // a Gaussian with at most this many tiles is emitted by its own thread
 
 // One instance: the tile id as the sort key, the Gaussian id as the value.  With unit masks
 // (ids < 2^24, common.cuh) the top byte of the value says which of the tile's eight 8x4 compositing
