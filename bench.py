@@ -470,7 +470,12 @@ def main():
                                 frac=per[dom]["frac"], traffic=traffic, traffic_source=traffic_src,
                                 peak_source=peak_src,
                                 how="CUDA events recorded by the library after every launch on the launching stream, "
-                                    "one extra step after the timed region")
+                                    "one extra step after the timed region",
+                                note=("the dominant kernel is not HBM-bound: its algorithmic bytes are gathered "
+                                      "per tile-list entry; ncu shows 54 % issue-slot utilisation, no pipe above "
+                                      "30 %, barrier waits as the top stall (profiles/r02_ncu_full_composite.md, "
+                                      "DESIGN.md §8); the HBM-bound kernels are in `kernels`: preprocess_fwd and "
+                                      "preprocess_bwd") if dom.startswith("composite") else None)
         line["kernels"] = per
         line["kernel_ms_per_view_raw"] = {k: v[0] / nv for k, v in prof.items()}
         line["workload_stats"] = stats
