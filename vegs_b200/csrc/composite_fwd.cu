@@ -65,7 +65,10 @@ constexpr int kMinCtas = VEGS_FWD_MINCTAS;
 #else
 constexpr int kMinCtas = kSuper > 256 ? 1 : (kSuper == 256 ? 2 : (kSuper == 192 ? 3 : 4));
 #endif
-constexpr int kScanSub = 2;                 // list entries per thread and scan step
+#ifndef VEGS_FWD_SCANSUB
+#define VEGS_FWD_SCANSUB 2
+#endif
+constexpr int kScanSub = VEGS_FWD_SCANSUB;  // list entries per thread and scan step
 constexpr int kScanStep = kScanSub * kSuper;
 constexpr int kRow = kSuper + 1;             // row stride of the pixel x slot matrix
 constexpr int kRing = (kSuper & (kSuper - 1)) == 0 ? 4 * kSuper : 2 * kSuper + kScanStep;   // candidate ring (>= 2 * kSuper + kScanStep)
