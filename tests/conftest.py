@@ -39,12 +39,15 @@ def pytest_sessionfinish(session, exitstatus):
             out_dir = os.path.join(ROOT, "gpurun_out")
             os.makedirs(out_dir, exist_ok=True)
             path = os.path.join(out_dir, "r02_parity.json")
+            # start from the committed record (a 1-GPU run must not drop the multi-GPU sections and
+            # vice versa), then from what an earlier session of this run left
             old = {}
-            if os.path.exists(path):
-                try:
-                    old = json.load(open(path))
-                except ValueError:
-                    old = {}
+            for base in (os.path.join(ROOT, "profiles", "r02_parity.json"), path):
+                if os.path.exists(base):
+                    try:
+                        old.update(json.load(open(base)))
+                    except ValueError:
+                        pass
             old.update(util._PARITY_RECORD)
             json.dump(old, open(path, "w"), indent=1, sort_keys=True)
     except Exception as ex:  # noqa: BLE001 - never turn a green run red from the reporting hook
